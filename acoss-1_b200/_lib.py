@@ -1,0 +1,246 @@
+# -*- coding: utf-8 -*-
+"""
+ctypes binding of csrc/libacoss_b200.so (C-ABI: include/acoss_b200.h).
+
+There is NO CPU fallback: if the shared library is missing or no CUDA device is
+usable, every compute entry point raises.  (`load_library()` itself works without
+a GPU so that the CPU-only test-suite can check the exported symbols.)
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libacoss_b200.so")
+
+c_f32p = ctypes.POINTER(ctypes.c_float)
+c_f64p = ctypes.POINTER(ctypes.c_double)
+c_i32p = ctypes.POINTER(ctypes.c_int32)
+c_i64p = ctypes.POINTER(ctypes.c_int64)
+c_u8p = ctypes.POINTER(ctypes.c_uint8)
+c_vp = ctypes.c_void_p
+
+
+class CrpParams(ctypes.Structure):
+    _fields_ = [("m", ctypes.c_int32), ("tau", ctypes.c_int32), ("kappa", ctypes.c_float),
+                ("oti", ctypes.c_int32), ("dis_onset", ctypes.c_float), ("dis_extension", ctypes.c_float),
+                ("crp_mode", ctypes.c_int32)]
+
+
+class PairStats(ctypes.Structure):
+    _fields_ = [("ms_total", ctypes.c_double), ("ms_prep", ctypes.c_double), ("ms_crp", ctypes.c_double),
+                ("ms_dp", ctypes.c_double), ("dp_cells", ctypes.c_int64), ("crp_cells", ctypes.c_int64),
+                ("crp_bytes", ctypes.c_int64), ("n_launches", ctypes.c_int64), ("n_dp_launches", ctypes.c_int64),
+                ("n_batches", ctypes.c_int64), ("n_exact_cells", ctypes.c_int64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+# every symbol include/acoss_b200.h declares: (restype, argtypes)
+SYMBOLS = {
+    "acoss_ctx_create": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(c_vp)]),
+    "acoss_ctx_destroy": (None, [c_vp]),
+    "acoss_last_error": (ctypes.c_char_p, [c_vp]),
+    "acoss_version": (ctypes.c_char_p, []),
+    "acoss_ctx_stream": (c_vp, [c_vp]),
+    "acoss_ctx_synchronize": (ctypes.c_int, [c_vp]),
+    "acoss_upload_tracks": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
+    "acoss_median_downsample": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, c_f32p, c_i64p]),
+    "acoss_serra09_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_f32p, c_f32p]),
+    "acoss_serra09_pairs_dev": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_vp, c_vp]),
+    "acoss_get_pair_stats": (ctypes.c_int, [c_vp, ctypes.POINTER(PairStats)]),
+    "acoss_crp_pair": (ctypes.c_int, [c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(CrpParams), c_u8p,
+                                      c_i32p, c_i32p, c_f32p, c_f32p, c_i32p]),
+    "acoss_cover_similarity_from_crp": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, ctypes.c_int32,
+                                                       ctypes.c_float, ctypes.c_float, c_f32p]),
+    "acoss_scores_to_matrix_dev": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, c_vp]),
+    "acoss_normalize_by_length_dev": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp, ctypes.c_int32]),
+    "acoss_eval_statistics": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_i32p, c_i32p, c_i32p, c_i32p,
+                                             ctypes.c_int32, c_f64p, c_f64p]),
+    "acoss_np_pairwise_sum": (ctypes.c_double, [c_f64p, ctypes.c_int64]),
+    "acoss_sw_constrained_from_binary": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, c_f64p]),
+    "acoss_dev_alloc": (ctypes.c_int, [c_vp, ctypes.c_int64, ctypes.POINTER(c_vp)]),
+    "acoss_dev_free": (ctypes.c_int, [c_vp, c_vp]),
+    "acoss_memcpy_h2d": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64]),
+    "acoss_memcpy_d2h": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64]),
+}
+
+_LIB = None
+
+
+class AcossError(RuntimeError):
+    """Raised for any non-zero return code of the C-ABI (code in .code)."""
+
+    def __init__(self, code, msg):
+        RuntimeError.__init__(self, "acoss_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def load_library():
+    """dlopen the CUDA library and bind every declared symbol.  Raises if absent."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("acoss_b200: %s is missing; run __graft_entry__.build() "
+                              "(nvcc -gencode arch=compute_100a,code=sm_100a).  There is no CPU fallback." % LIB_PATH)
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = L
+    return _LIB
+
+
+def _np(a, dtype):
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def _ptr(a, ct):
+    return a.ctypes.data_as(ctypes.POINTER(ct)) if a is not None else None
+
+
+class Context(object):
+    """One context per GPU (acoss_ctx).  All methods raise AcossError on failure."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = c_vp()
+        rc = self.lib.acoss_ctx_create(int(device), ctypes.byref(h))
+        if rc != 0:
+            raise AcossError(rc, (self.lib.acoss_last_error(None) or b"").decode())
+        self.h = h
+        self.device = int(device)
+        self.lengths = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.acoss_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise AcossError(rc, (self.lib.acoss_last_error(self.h) or b"").decode())
+
+    def synchronize(self):
+        self._ck(self.lib.acoss_ctx_synchronize(self.h))
+
+    # ---- tracks ---------------------------------------------------------------
+    @staticmethod
+    def pack_tracks(tracks):
+        lens = np.array([t.shape[0] for t in tracks], dtype=np.int64)
+        offs = np.zeros(len(tracks) + 1, np.int64)
+        offs[1:] = np.cumsum(lens)
+        frames = np.empty((int(offs[-1]), 12), np.float32)
+        for t, o in zip(tracks, offs[:-1]):
+            frames[o:o + t.shape[0]] = t
+        return frames, offs
+
+    def upload_tracks(self, tracks=None, m=9, tau=1, frames=None, offsets=None):
+        if frames is None:
+            frames, offsets = self.pack_tracks(tracks)
+        frames = _np(frames, np.float32)
+        offsets = _np(offsets, np.int64)
+        self._ck(self.lib.acoss_upload_tracks(self.h, _ptr(frames, ctypes.c_float), _ptr(offsets, ctypes.c_int64),
+                                              len(offsets) - 1, int(m), int(tau)))
+        self.lengths = np.diff(offsets).astype(np.int32)
+        self.h2d_bytes = frames.nbytes + offsets.nbytes
+
+    def median_downsample(self, raw_tracks, fac):
+        frames, offs = self.pack_tracks([_np(t, np.float32) for t in raw_tracks])
+        n = len(raw_tracks)
+        out_offs = np.zeros(n + 1, np.int64)
+        total = int(sum((t.shape[0] + fac - 1) // fac for t in raw_tracks))
+        out = np.empty((total, 12), np.float32)
+        self._ck(self.lib.acoss_median_downsample(self.h, _ptr(frames, ctypes.c_float), _ptr(offs, ctypes.c_int64), n, int(fac),
+                                                  _ptr(out, ctypes.c_float), _ptr(out_offs, ctypes.c_int64)))
+        return [out[out_offs[i]:out_offs[i + 1]] for i in range(n)]
+
+    # ---- pairs ------------------------------------------------------------------
+    @staticmethod
+    def params(m=9, tau=1, kappa=0.095, oti=True, dis_onset=0.5, dis_extension=0.5, crp_mode=0):
+        return CrpParams(int(m), int(tau), float(kappa), int(bool(oti)), float(dis_onset), float(dis_extension), int(crp_mode))
+
+    def serra09_pairs(self, pairs, params=None, want_dmax=False, want_qmax=True):
+        """Host in / host out.  Returns (qmax|None, dmax|None)."""
+        params = params or self.params()
+        pairs = _np(pairs, np.int32).reshape(-1, 2)
+        P = pairs.shape[0]
+        q = np.zeros(P, np.float32) if want_qmax else None
+        d = np.zeros(P, np.float32) if want_dmax else None
+        self._ck(self.lib.acoss_serra09_pairs(self.h, _ptr(pairs, ctypes.c_int32), P, ctypes.byref(params),
+                                              _ptr(q, ctypes.c_float), _ptr(d, ctypes.c_float)))
+        return q, d
+
+    def serra09_pairs_dev(self, pairs, params, out_q_ptr, out_d_ptr):
+        """Host pairs in, device pointers out (ints; 0/None = not wanted).  Asynchronous."""
+        pairs = _np(pairs, np.int32).reshape(-1, 2)
+        self._ck(self.lib.acoss_serra09_pairs_dev(self.h, _ptr(pairs, ctypes.c_int32), pairs.shape[0], ctypes.byref(params),
+                                                  c_vp(out_q_ptr or 0), c_vp(out_d_ptr or 0)))
+
+    def pair_stats(self):
+        s = PairStats()
+        self._ck(self.lib.acoss_get_pair_stats(self.h, ctypes.byref(s)))
+        return s.as_dict()
+
+    def crp_pair(self, q, r, params=None):
+        """(crp uint8 (M,N), thr_q, thr_r, oti) of one uploaded pair (test hook)."""
+        params = params or self.params()
+        nq, nr = int(self.lengths[q]), int(self.lengths[r])
+        buf = np.zeros(max(nq, 1) * max(nr, 1), np.uint8)
+        tq = np.zeros(max(nq, 1), np.float32)
+        tr = np.zeros(max(nr, 1), np.float32)
+        M, N, o = ctypes.c_int32(0), ctypes.c_int32(0), ctypes.c_int32(0)
+        self._ck(self.lib.acoss_crp_pair(self.h, int(q), int(r), ctypes.byref(params), _ptr(buf, ctypes.c_uint8),
+                                         ctypes.byref(M), ctypes.byref(N), _ptr(tq, ctypes.c_float), _ptr(tr, ctypes.c_float),
+                                         ctypes.byref(o)))
+        return buf[:M.value * N.value].reshape(M.value, N.value).copy(), tq[:M.value].copy(), tr[:N.value].copy(), o.value
+
+    @staticmethod
+    def _pack_mats(mats):
+        mats = [_np(x, np.uint8) for x in mats]
+        Ms = np.array([x.shape[0] for x in mats], np.int32)
+        Ns = np.array([x.shape[1] for x in mats], np.int32)
+        flat = np.concatenate([x.ravel() for x in mats]) if mats else np.zeros(0, np.uint8)
+        return _np(flat, np.uint8), Ms, Ns
+
+    def cover_similarity_from_crp(self, crps, alignment="serra09", dis_onset=0.5, dis_extension=0.5):
+        flat, Ms, Ns = self._pack_mats(crps)
+        out = np.zeros(len(crps), np.float32)
+        a = {"serra09": 0, "chen17": 1}[alignment]
+        self._ck(self.lib.acoss_cover_similarity_from_crp(self.h, _ptr(flat, ctypes.c_uint8), _ptr(Ms, ctypes.c_int32),
+                                                          _ptr(Ns, ctypes.c_int32), len(crps), a, dis_onset, dis_extension,
+                                                          _ptr(out, ctypes.c_float)))
+        return out
+
+    def sw_constrained(self, mats):
+        flat, Ms, Ns = self._pack_mats(mats)
+        out = np.zeros(len(mats), np.float64)
+        self._ck(self.lib.acoss_sw_constrained_from_binary(self.h, _ptr(flat, ctypes.c_uint8), _ptr(Ms, ctypes.c_int32),
+                                                           _ptr(Ns, ctypes.c_int32), len(mats), _ptr(out, ctypes.c_double)))
+        return out
+
+    # ---- N x N stage (device pointers as ints) -----------------------------------
+    def scores_to_matrix_dev(self, pairs_ptr, scores_ptr, n_pairs, n, symmetric, D_ptr):
+        self._ck(self.lib.acoss_scores_to_matrix_dev(self.h, c_vp(pairs_ptr), c_vp(scores_ptr), int(n_pairs), int(n),
+                                                     int(bool(symmetric)), c_vp(D_ptr)))
+
+    def normalize_by_length_dev(self, D_ptr, n, lengths_ptr, mode):
+        self._ck(self.lib.acoss_normalize_by_length_dev(self.h, c_vp(D_ptr), int(n), c_vp(lengths_ptr), int(mode)))
+
+    def eval_statistics(self, D_ptr, n, order, csize, cstart, tops):
+        order, csize, cstart, tops = (_np(x, np.int32) for x in (order, csize, cstart, tops))
+        out = np.zeros(4 + len(tops), np.float64)
+        ranks = np.zeros(n, np.float64)
+        self._ck(self.lib.acoss_eval_statistics(self.h, c_vp(D_ptr), int(n), _ptr(order, ctypes.c_int32), _ptr(csize, ctypes.c_int32),
+                                                _ptr(cstart, ctypes.c_int32), _ptr(tops, ctypes.c_int32), len(tops),
+                                                _ptr(out, ctypes.c_double), _ptr(ranks, ctypes.c_double)))
+        return out, ranks

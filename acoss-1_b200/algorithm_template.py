@@ -1,0 +1,291 @@
+# -*- coding: utf-8 -*-
+"""
+`CoverAlgorithm`: host-side mirror of the reference's plugin base class
+(acoss/algorithms/algorithm_template.py:17-291) -- same constructor, attributes
+(`filepaths`, `cliques`, `N`, `Ds`), method names, return values and side effects,
+so that Serra09 / LateFusionChen / ... subclasses are drop-in.  What changes is
+underneath: `similarity(idxs)` is batched and runs on the GPU through the C-ABI
+(include/acoss_b200.h), `all_pairwise` hands the whole pair grid to it (sharded
+over ranks when torch.distributed is initialised) and `getEvalStatistics` counts
+ranks on the device.  There is no CPU fallback.
+
+Deliberate repairs of reference defects: Q3 (the
+`progressbar` NameError in the parallel branch), Q4 (`cleanup_memmap` now removes
+the files).  Everything that affects numbers is preserved (Q10 formulas).
+"""
+import os
+import warnings
+
+import numpy as np
+
+from . import featio
+from .utils import create_dataset_filepaths
+
+__all__ = ['CoverAlgorithm']
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def dist_info():
+    """(rank, world) of torch.distributed if initialised, else (0, 1)."""
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank(), dist.get_world_size()
+    except Exception:
+        pass
+    return 0, 1
+
+
+def shard_pairs(pairs, cost, rank, world):
+    """Deal the pair list to ranks so that every rank gets the same total cost:
+    sort by cost (descending, stable) and take every world-th pair.  Returns the
+    indices (into `pairs`) owned by `rank`.  No data-path collective is needed:
+    pairs are independent."""
+    if world == 1:
+        return np.arange(len(pairs), dtype=np.int64)
+    order = np.argsort(-np.asarray(cost, dtype=np.int64), kind="stable")
+    return np.sort(order[rank::world])
+
+
+def all_gather_scores(local_idx, local_vals, n_total, device=None):
+    """All-gather of the per-rank score vectors (the one collective of the path).
+    local_idx: indices into the global pair list, local_vals: (k, len(local_idx)) float32.
+    Returns (k, n_total) float32 on every rank.  NCCL when the process group is NCCL
+    (tensors on `device`), gloo otherwise."""
+    import torch
+    import torch.distributed as dist
+    rank, world = dist_info()
+    k = local_vals.shape[0]
+    if world == 1:
+        out = np.zeros((k, n_total), np.float32)
+        out[:, local_idx] = local_vals
+        return out
+    use_cuda = dist.get_backend() == "nccl"
+    dev = torch.device("cuda", device if device is not None else torch.cuda.current_device()) if use_cuda else torch.device("cpu")
+    cap = (n_total + world - 1) // world + 1
+    buf_i = torch.full((cap,), -1, dtype=torch.int64)
+    buf_i[:len(local_idx)] = torch.from_numpy(np.asarray(local_idx, dtype=np.int64))
+    buf_v = torch.zeros((k, cap), dtype=torch.float32)
+    buf_v[:, :len(local_idx)] = torch.from_numpy(np.ascontiguousarray(local_vals, dtype=np.float32))
+    buf_i, buf_v = buf_i.to(dev), buf_v.to(dev)
+    all_i = [torch.empty_like(buf_i) for _ in range(world)]
+    all_v = [torch.empty_like(buf_v) for _ in range(world)]
+    dist.all_gather(all_i, buf_i)
+    dist.all_gather(all_v, buf_v)
+    out = np.zeros((k, n_total), np.float32)
+    for gi, gv in zip(all_i, all_v):
+        gi = gi.cpu().numpy()
+        gv = gv.cpu().numpy()
+        ok = gi >= 0
+        out[:, gi[ok]] = gv[:, ok]
+    return out
+
+
+class CoverAlgorithm(object):
+    """
+    Attributes
+    ----------
+    filepaths: list(string)
+        List of paths to all files in the dataset
+    cliques: {string: set}
+        A dictionary of all cover cliques, where the cliques index into filepaths
+    Ds: {string similarity type: ndarray(num files, num files)}
+        A dictionary of pairwise similarity matrices, whose indices index into filepaths.
+    """
+
+    def __init__(self, dataset_csv, name="Serra09", datapath="features_benchmark", shortname="full",
+                 cachedir="cache", similarity_types=["main"], device=None):
+        self.name = name
+        self.shortname = shortname
+        self.cachedir = cachedir
+        self.filepaths = create_dataset_filepaths(dataset_csv, root_audio_dir=datapath, file_format=".h5")
+        self.cliques = {}
+        self.N = len(self.filepaths)
+        if not os.path.exists(cachedir):
+            os.makedirs(cachedir, exist_ok=True)
+        self.Ds = {}
+        rank, world = dist_info()
+        self._memmap_suffix = "" if world == 1 else ".rank%d" % rank
+        for s in similarity_types:
+            self.Ds[s] = np.memmap('%s_%s_dmat%s' % (self.get_cacheprefix(), s, self._memmap_suffix),
+                                   shape=(self.N, self.N), mode='w+', dtype='float32')
+        self._device = device
+        self._ctx = None
+        self.last_stats = {}
+        print("Initialized %s algorithm on %i songs in dataset %s" % (name, self.N, shortname))
+
+    # ---- device plumbing --------------------------------------------------------
+    def device_index(self):
+        if self._device is None:
+            self._device = int(os.environ.get("LOCAL_RANK", "0"))
+        return self._device
+
+    def context(self):
+        """The per-GPU C-ABI context (created lazily; raises if the CUDA library or the
+        device is missing -- there is no CPU path)."""
+        if self._ctx is None:
+            from ._lib import Context
+            self._ctx = Context(self.device_index())
+        return self._ctx
+
+    def get_cacheprefix(self):
+        """Return a descriptive file prefix to use for caching features and distance matrices"""
+        return "%s/%s_%s" % (self.cachedir, self.name, self.shortname)
+
+    def load_features(self, i):
+        """Load the fields from the h5 file for a particular song, and also keep track of
+        which cover clique it's in by saving into self.cliques as a side effect
+        (algorithm_template.py:71-95)."""
+        feats = featio.load(self.filepaths[i])
+        if not feats['label'] in self.cliques:
+            self.cliques[feats['label']] = set([])
+        self.cliques[feats['label']].add(i)
+        return feats
+
+    def get_all_clique_ids(self, verbose=False):
+        """Load all h5 files to get clique information as a side effect (cached in
+        `<prefix>_clique_info.txt`, algorithm_template.py:97-119)."""
+        filepath = "%s_clique_info.txt" % self.get_cacheprefix()
+        if not os.path.exists(filepath):
+            fout = open(filepath, "w")
+            for i in range(len(self.filepaths)):
+                feats = CoverAlgorithm.load_features(self, i)
+                if verbose:
+                    print(i)
+                fout.write("%i,%s\n" % (i, feats['label']))
+            fout.close()
+        else:
+            fin = open(filepath)
+            for line in fin.readlines():
+                i, label = line.split(",")
+                label = label.strip()
+                if not label in self.cliques:
+                    self.cliques[label] = set([])
+                self.cliques[label].add(int(i))
+            fin.close()
+
+    def similarity(self, idxs):
+        """Given (P, 2) song index pairs, store a number in Ds[type][i, j] which is high if
+        the songs are similar (algorithm_template.py:121-140).  Base class: zeros."""
+        idxs = np.asarray(idxs).reshape(-1, 2)
+        self.Ds["main"][idxs[:, 0], idxs[:, 1]] = 0.0
+
+    def pair_cost(self, idxs):
+        """Relative cost of each pair, used to balance the shards of a multi-GPU run."""
+        return np.ones(len(idxs), dtype=np.int64)
+
+    @staticmethod
+    def enumerate_pairs(n, symmetric):
+        """combinations(range(n), 2) / permutations(range(n), 2) in itertools order
+        (algorithm_template.py:168-171) as an (P, 2) int32 array."""
+        if symmetric:
+            i, j = np.triu_indices(n, k=1)
+        else:
+            i, j = np.nonzero(~np.eye(n, dtype=bool))
+        return np.stack([i, j], axis=1).astype(np.int32)
+
+    def all_pairwise(self, parallel=0, n_cores=12, symmetric=False, precomputed=False):
+        """Do all pairwise comparisons between songs (algorithm_template.py:142-193).
+        `parallel` / `n_cores` are accepted for compatibility; the pair grid is handed to
+        the GPU in one batched `similarity` call per rank.  With torch.distributed
+        initialised the grid is sharded by cost across ranks and the score vectors are
+        all-gathered (NCCL) so that every rank ends with the full matrices."""
+        h5filename = "%s_Ds.h5" % self.get_cacheprefix()
+        if precomputed:
+            self.Ds = featio.load(h5filename)
+            self.get_all_clique_ids()
+            return
+        all_pairs = self.enumerate_pairs(len(self.filepaths), symmetric)
+        rank, world = dist_info()
+        mine = shard_pairs(all_pairs, self.pair_cost(all_pairs) if world > 1 else None, rank, world)
+        self.similarity(all_pairs[mine])
+        if world > 1:
+            keys = list(self.Ds.keys())
+            local = np.stack([np.asarray(self.Ds[s][all_pairs[mine, 0], all_pairs[mine, 1]]) for s in keys])
+            full = all_gather_scores(mine, local, len(all_pairs), self.device_index())
+            for k, s in enumerate(keys):
+                self.Ds[s][all_pairs[:, 0], all_pairs[:, 1]] = full[k]
+        if len(self.cliques) == 0 or sum(len(c) for c in self.cliques.values()) < self.N:
+            self.get_all_clique_ids()
+        if symmetric:
+            for similarity_type in self.Ds:
+                self.Ds[similarity_type] += self.Ds[similarity_type].T
+        if rank == 0:
+            featio.save(h5filename, {k: np.array(v) for k, v in self.Ds.items()})
+
+    def cleanup_memmap(self):
+        """Remove all memmap variables for song-level similarity matrices
+        (algorithm_template.py:195-204; repaired)."""
+        try:
+            for s in list(self.Ds):
+                path = '%s_%s_dmat%s' % (self.get_cacheprefix(), s, self._memmap_suffix)
+                if isinstance(self.Ds[s], np.memmap):
+                    self.Ds[s] = np.array(self.Ds[s])
+                if os.path.exists(path):
+                    os.remove(path)
+        except Exception:
+            print('Could not clean-up automatically.')
+
+    def clique_layout(self):
+        """Clique-contiguous order exactly as getEvalStatistics builds it
+        (algorithm_template.py:220-228): cliques in dict order, sorted by size descending
+        with np.argsort(-Ks).  Returns (order, clique_size per position, clique_start per position)."""
+        from itertools import chain
+        cliques = [list(self.cliques[s]) for s in self.cliques]
+        Ks = np.array([len(c) for c in cliques])
+        idx = np.argsort(-Ks)
+        Ks = Ks[idx]
+        cliques = [cliques[i] for i in idx]
+        order = np.array(list(chain(*cliques)), dtype=np.int32)
+        csize = np.repeat(Ks, Ks).astype(np.int32)
+        starts = np.concatenate([[0], np.cumsum(Ks)[:-1]])
+        cstart = np.repeat(starts, Ks).astype(np.int32)
+        return order, csize, cstart
+
+    def getEvalStatistics(self, similarity_type, topsidx=[1, 10, 100, 1000]):
+        """Compute MR, MRR, MAP, Median Rank, and Top X using a particular similarity measure
+        (algorithm_template.py:206-291).  The N x N rank counting runs on the device; ties are
+        ranked by position in the clique-contiguous order (the reference's np.argsort is
+        unstable under ties)."""
+        torch = _torch()
+        ctx = self.context()
+        D = np.array(self.Ds[similarity_type], dtype=np.float32)
+        N = D.shape[0]
+        order, csize, cstart = self.clique_layout()
+        if len(order) != N:
+            raise RuntimeError("clique information covers %d of %d songs; call get_all_clique_ids()" % (len(order), N))
+        dev = torch.device("cuda", self.device_index())
+        D_dev = torch.from_numpy(D).to(dev)
+        torch.cuda.synchronize(dev)
+        out, ranks = ctx.eval_statistics(D_dev.data_ptr(), N, order, csize, cstart, np.array(topsidx, np.int32))
+        MR, MRR, MDR, MAP = (float(x) for x in out[:4])
+        tops = np.array(out[4:], dtype=np.float64)
+        if np.isnan(ranks[:int(np.sum(csize >= 2))]).any():
+            warnings.warn("Recalling 0 songs for a clique")
+        print(ranks[np.isnan(ranks) == 0])
+        print("%s %s STATS\n-------------------------\nMR = %.3g\nMRR = %.3g\nMDR = %.3g\nMAP = %.3g"
+              % (self.name, similarity_type, MR, MRR, MDR, MAP))
+        for i in range(len(tops)):
+            print("Top-%i: %i" % (topsidx[i], tops[i]))
+        # Output to CSV file (same columns as the reference, :277-290)
+        if dist_info()[0] == 0:
+            resultsfile = "results_%s_%s.csv" % (self.shortname, self.name)
+            if not os.path.exists(resultsfile):
+                fout = open(resultsfile, "w")
+                fout.write("name, MR, MRR, MDR, MAP")
+                for t in topsidx:
+                    fout.write(",Top-%i" % t)
+                fout.write("\n")
+                fout.close()
+            fout = open(resultsfile, "a")
+            fout.write("%s_%s," % (self.name, similarity_type))
+            fout.write("%.3g, %.3g, %.3g, %.3g" % (MR, MRR, MDR, MAP))
+            for t in tops:
+                fout.write(", %.3g" % t)
+            fout.write("\n")
+            fout.close()
+        return MR, MRR, MDR, MAP, tops

@@ -1,0 +1,249 @@
+// acoss_b200.cu -- context + C-ABI of the B200-native acoss hot path (sm_100a).
+// Interface contract: include/acoss_b200.h.  No CPU fallback anywhere in this
+// file: every compute entry point launches the CUDA kernels of kernels_*.cuh.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "../../include/acoss_b200.h"
+#include "common.cuh"
+#include "kernels_prep.cuh"
+#include "kernels_crp.cuh"
+#include "kernels_dp.cuh"
+#include "kernels_eval.cuh"
+
+static std::string g_create_error;
+
+// growable device buffer owned by the context
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { e = cudaMalloc(&p, bytes); want = bytes; }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct acoss_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    // track store
+    int n_tracks = 0, m = 0, tau = 0;
+    std::vector<int64_t> h_offs;      // frame offsets
+    std::vector<int32_t> h_emb;       // embedded rows per track
+    std::vector<int64_t> h_sd_off;    // self-dot table offsets
+    DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma;
+    // per-call scratch
+    DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2;
+    cudaEvent_t ev[8] = {};
+    acoss_pair_stats stats = {};
+    size_t crp_budget = (size_t)8 << 30;
+    int max_smem = 0;
+    int num_sms = ACOSS_NUM_SMS;
+
+    void set_error(const std::string& s) { err = s; }
+};
+
+#define CK(expr) ACOSS_CUDA_CHECK_RET(ctx, expr)
+#define CK_LAUNCH() CK(cudaGetLastError())
+
+extern "C" const char* acoss_version(void) { return "acoss_b200 0.1 sm_100a"; }
+
+extern "C" const char* acoss_last_error(const acoss_ctx* ctx)
+{
+    return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int acoss_ctx_create(int device, acoss_ctx** out)
+{
+    if (!out) return ACOSS_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no usable CUDA device: ") + cudaGetErrorString(e);
+        return ACOSS_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return ACOSS_ERR_ARG; }
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); return ACOSS_ERR_CUDA; }
+    acoss_ctx* ctx = new acoss_ctx();
+    ctx->device = device;
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return ACOSS_ERR_CUDA; }
+    for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+    cudaDeviceGetAttribute(&ctx->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
+    if (const char* s = getenv("ACOSS_CRP_BUDGET_MB")) {
+        long mb = atol(s);
+        if (mb > 0) ctx->crp_budget = (size_t)mb << 20;
+    }
+    *out = ctx;
+    return ACOSS_OK;
+}
+
+extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
+                      &ctx->d_gchroma, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
+                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2};
+    for (DevBuf* b : bufs) b->release();
+    for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" void* acoss_ctx_stream(acoss_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" int acoss_ctx_synchronize(acoss_ctx* ctx)
+{
+    if (!ctx) return ACOSS_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ACOSS_OK;
+}
+
+static int embedded_len(int n, int m, int tau)
+{
+    if (m == 1) return n;
+    int inc = m * tau;
+    if (n < inc + 1) return 0;
+    return (n - inc + tau - 1) / tau;
+}
+
+static int reserve(acoss_ctx* ctx, DevBuf& b, size_t bytes)
+{
+    cudaError_t e = b.reserve(bytes);
+    if (e != cudaSuccess) {
+        ctx->set_error(std::string("device allocation of ") + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(e));
+        cudaGetLastError();
+        return ACOSS_ERR_NOMEM;
+    }
+    return ACOSS_OK;
+}
+#define RESERVE(buf, bytes) do { int _r = reserve(ctx, buf, bytes); if (_r) return _r; } while (0)
+
+// ---------------------------------------------------------------------------
+// track store
+// ---------------------------------------------------------------------------
+extern "C" int acoss_upload_tracks(acoss_ctx* ctx, const float* frames_host, const int64_t* offsets_host,
+                                   int32_t n_tracks, int32_t m, int32_t tau)
+{
+    if (!ctx) return ACOSS_ERR_ARG;
+    if (!frames_host || !offsets_host || n_tracks <= 0 || m < 1 || m > 32 || tau < 1) {
+        ctx->set_error("acoss_upload_tracks: bad argument");
+        return ACOSS_ERR_ARG;
+    }
+    CK(cudaSetDevice(ctx->device));
+    ctx->n_tracks = n_tracks; ctx->m = m; ctx->tau = tau;
+    ctx->h_offs.assign(offsets_host, offsets_host + n_tracks + 1);
+    ctx->h_emb.resize(n_tracks);
+    ctx->h_sd_off.resize(n_tracks + 1);
+    int64_t sd = 0;
+    int max_emb = 0;
+    for (int t = 0; t < n_tracks; ++t) {
+        int64_t n = ctx->h_offs[t + 1] - ctx->h_offs[t];
+        if (n < 0 || n > (int64_t)1 << 30) { ctx->set_error("acoss_upload_tracks: bad offsets"); return ACOSS_ERR_ARG; }
+        int M = embedded_len((int)n, m, tau);
+        ctx->h_emb[t] = M;       // 0 = too short; reported when such a track is used in a pair
+        ctx->h_sd_off[t] = sd;
+        sd += (int64_t)ACOSS_NBINS * M;
+        max_emb = std::max(max_emb, M);
+    }
+    ctx->h_sd_off[n_tracks] = sd;
+    const int64_t total = ctx->h_offs[n_tracks];
+    RESERVE(ctx->d_frames, sizeof(float) * ACOSS_NBINS * (size_t)std::max<int64_t>(total, 1));
+    RESERVE(ctx->d_offs, sizeof(int64_t) * (n_tracks + 1));
+    RESERVE(ctx->d_emb, sizeof(int32_t) * n_tracks);
+    RESERVE(ctx->d_sd_off, sizeof(int64_t) * (n_tracks + 1));
+    RESERVE(ctx->d_selfdot, sizeof(float) * (size_t)std::max<int64_t>(sd, 1));
+    RESERVE(ctx->d_gchroma, sizeof(float) * ACOSS_NBINS * n_tracks);
+    cudaStream_t st = ctx->stream;
+    CK(cudaMemcpyAsync(ctx->d_frames.p, frames_host, sizeof(float) * ACOSS_NBINS * (size_t)total, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_offs.p, ctx->h_offs.data(), sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_emb.p, ctx->h_emb.data(), sizeof(int32_t) * n_tracks, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_sd_off.p, ctx->h_sd_off.data(), sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st));
+    {
+        int threads = 128, warps_per_block = threads / 32;
+        int blocks = (n_tracks + warps_per_block - 1) / warps_per_block;
+        global_chroma_kernel<<<blocks, threads, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(),
+                                                         n_tracks, ctx->d_gchroma.as<float>());
+        CK_LAUNCH();
+    }
+    if (max_emb > 0) {
+        dim3 grid((max_emb * ACOSS_NBINS + 127) / 128, n_tracks);
+        selfdot_kernel<<<grid, 128, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(),
+                                             ctx->d_emb.as<int32_t>(), ctx->d_sd_off.as<int64_t>(), m, tau,
+                                             ctx->d_selfdot.as<float>());
+        CK_LAUNCH();
+    }
+    CK(cudaStreamSynchronize(st));   // host buffers may be released by the caller
+    return ACOSS_OK;
+}
+
+extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_host, const int64_t* raw_offsets_host,
+                                       int32_t n_tracks, int32_t fac, float* out_frames_host, int64_t* out_offsets_host)
+{
+    if (!ctx) return ACOSS_ERR_ARG;
+    if (!raw_frames_host || !raw_offsets_host || !out_frames_host || !out_offsets_host || n_tracks <= 0 || fac < 1 || fac > 256) {
+        ctx->set_error("acoss_median_downsample: bad argument (1 <= fac <= 256)");
+        return ACOSS_ERR_ARG;
+    }
+    CK(cudaSetDevice(ctx->device));
+    std::vector<int64_t> oo(n_tracks + 1, 0);
+    int64_t max_out = 0;
+    for (int t = 0; t < n_tracks; ++t) {
+        int64_t T = raw_offsets_host[t + 1] - raw_offsets_host[t];
+        int64_t no = (T + fac - 1) / fac;
+        oo[t + 1] = oo[t] + no;
+        max_out = std::max(max_out, no);
+    }
+    const int64_t total_raw = raw_offsets_host[n_tracks], total_out = oo[n_tracks];
+    DevBuf raw, roff, ooff, outb;
+    auto cleanup = [&]() { raw.release(); roff.release(); ooff.release(); outb.release(); };
+    if (raw.reserve(sizeof(float) * ACOSS_NBINS * (size_t)std::max<int64_t>(total_raw, 1)) != cudaSuccess ||
+        roff.reserve(sizeof(int64_t) * (n_tracks + 1)) != cudaSuccess ||
+        ooff.reserve(sizeof(int64_t) * (n_tracks + 1)) != cudaSuccess ||
+        outb.reserve(sizeof(float) * ACOSS_NBINS * (size_t)std::max<int64_t>(total_out, 1)) != cudaSuccess) {
+        cleanup(); cudaGetLastError();
+        ctx->set_error("acoss_median_downsample: device allocation failed");
+        return ACOSS_ERR_NOMEM;
+    }
+    cudaStream_t st = ctx->stream;
+    cudaMemcpyAsync(raw.p, raw_frames_host, sizeof(float) * ACOSS_NBINS * (size_t)total_raw, cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(roff.p, raw_offsets_host, sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(ooff.p, oo.data(), sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st);
+    if (max_out > 0) {
+        dim3 grid((unsigned)((max_out * ACOSS_NBINS + 127) / 128), n_tracks);
+        median_downsample_kernel<256><<<grid, 128, 0, st>>>(raw.as<float>(), roff.as<int64_t>(), ooff.as<int64_t>(),
+                                                            n_tracks, fac, outb.as<float>());
+    }
+    cudaMemcpyAsync(out_frames_host, outb.p, sizeof(float) * ACOSS_NBINS * (size_t)total_out, cudaMemcpyDeviceToHost, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    cleanup();
+    if (e != cudaSuccess) { ctx->set_error(std::string("acoss_median_downsample: ") + cudaGetErrorString(e)); return ACOSS_ERR_CUDA; }
+    memcpy(out_offsets_host, oo.data(), sizeof(int64_t) * (n_tracks + 1));
+    return ACOSS_OK;
+}
+
+#include "api_pairs.inc"
+#include "api_matrix.inc"

@@ -1,0 +1,344 @@
+// kernels_dp.cuh -- Qmax / Dmax / constrained Smith-Waterman recurrences (sm_100a).
+//
+// Replaces essentia CoverSongSimilarity(alignmentType='serra09'|'chen17',
+// distanceType='symmetric')(csm)[1] (acoss/algorithms/rqa_serra09.py:64,67,
+// latefusion_chen.py:67-71; semantics SURVEY Appendix A D8/D9, restated in
+// oracle/acoss_oracle.c:oracle_cover_similarity) and
+// smith_waterman_constrained (acoss/algorithms/utils/alignment_tools.py:25-46).
+//
+// Key observation: cell (i, j) depends on (i-1, j-1), (i-2, j-1), (i-1, j-2) only,
+// i.e. on the two previous ROWS.  A row is therefore fully data-parallel; the
+// only serial dimension is i.  One warp owns one pair and keeps rows i-1 and
+// i-2 of the score matrix entirely in registers:
+//   * scores are exact integers in half units (gamma_o = gamma_e = 0.5 =>
+//     Q in (1/2)Z): R=1 -> +2, R=0 -> max(0, . - 1); two cells per 32-bit
+//     register as int16x2, updated with the DPX instructions
+//     (__vimax3_s16x2 / __viaddmax_s16x2);
+//   * a lane owns "groups" of 2G consecutive cells; inside a group register p
+//     holds cells (p, p+G), so the "column j-1" and "column j-2" views of a row
+//     are register renames except at p = 0/1, where one PRMT + one SHFL fetch
+//     the neighbour group's edge;
+//   * the CRP row arrives as one coalesced 2G-byte load per lane and chunk
+//     (chunk = 32 lanes x 2G cells, 512 B contiguous for G = 8), in the "delta"
+//     byte code (0x02 / 0xFF): one PRMT with sign replication expands two bytes
+//     into the packed int16x2 increment.
+// HBM traffic = the CRP bytes, read exactly once, fully coalesced: the kernel is
+// bound by HBM bandwidth at 1 B/cell.
+#pragma once
+#include "common.cuh"
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+// ---- coalesced chunk loads of 2G delta bytes per lane ---------------------------
+template <int G> struct RowBytes;
+template <> struct RowBytes<8> {
+    uint4 v;
+    __device__ __forceinline__ void load(const uint8_t* p) { v = __ldg(reinterpret_cast<const uint4*>(p)); }
+    __device__ __forceinline__ void fill(uint32_t w) { v = make_uint4(w, w, w, w); }
+    template <int P> __device__ __forceinline__ uint32_t delta() const {
+        const uint32_t x = (P >> 2) == 0 ? v.x : v.y;
+        const uint32_t y = (P >> 2) == 0 ? v.z : v.w;
+        constexpr uint32_t b = P & 3;
+        return prmt(x, y, b | ((b | 8) << 4) | ((4 + b) << 8) | (((4 + b) | 8) << 12));
+    }
+};
+template <> struct RowBytes<4> {
+    uint2 v;
+    __device__ __forceinline__ void load(const uint8_t* p) { v = __ldg(reinterpret_cast<const uint2*>(p)); }
+    __device__ __forceinline__ void fill(uint32_t w) { v = make_uint2(w, w); }
+    template <int P> __device__ __forceinline__ uint32_t delta() const {
+        constexpr uint32_t b = P;
+        return prmt(v.x, v.y, b | ((b | 8) << 4) | ((4 + b) << 8) | (((4 + b) | 8) << 12));
+    }
+};
+template <> struct RowBytes<2> {
+    uint32_t v;
+    __device__ __forceinline__ void load(const uint8_t* p) { v = __ldg(reinterpret_cast<const uint32_t*>(p)); }
+    __device__ __forceinline__ void fill(uint32_t w) { v = w; }
+    template <int P> __device__ __forceinline__ uint32_t delta() const {
+        constexpr uint32_t b = P;
+        return prmt(v, v, b | ((b | 8) << 4) | ((2 + b) << 8) | (((2 + b) | 8) << 12));
+    }
+};
+
+// bonus of the chen17 recurrence: +R (= +2 half units) from the packed delta
+// (0x0002 -> 2, 0xFFFF -> 0):  delta & ~(delta >> 1) & 0x00020002
+__device__ __forceinline__ uint32_t delta_to_bonus(uint32_t dl)
+{
+    return dl & ~(dl >> 1) & 0x00020002u;
+}
+
+template <int G, int P> struct StepUnroll;
+
+// One warp per pair.  ALIGN: 0 = serra09 (Qmax), 1 = chen17 (Dmax).
+// Requirements: pitch % (64*G) == 0, N <= NCH*64*G, min(M,N) small enough for
+// int16 half units (host checks: 4*min(M,N) < 32000).
+template <int G, int NCH, int ALIGN>
+__global__ void __launch_bounds__(128)
+dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
+                 const uint8_t* __restrict__ crp, float* __restrict__ out)
+{
+    constexpr int CHUNK = 64 * G;       // cells (= bytes) per chunk
+    constexpr int LB = 2 * G;           // bytes per lane and chunk
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const uint32_t zmask = (lane == 0) ? 0xFFFF0000u : 0xFFFFFFFFu;   // clears cells j = 0, 1
+
+    for (int64_t pidx = warp0; pidx < n_pairs; pidx += nwarps) {
+        const PairDesc pd = descs[pidx];
+        const int M = pd.M, N = pd.N, pitch = pd.pitch;
+        const int nch = (N + CHUNK - 1) / CHUNK;
+        const uint8_t* base = crp + pd.crp_off + (int64_t)lane * LB;
+
+        uint32_t A[NCH][G], B[NCH][G], carry[NCH];     // rows i-1, i-2; carried (i-2) edge
+        uint32_t Bon[NCH][G];                          // chen17: +R of row i-1 (unshifted)
+        uint32_t rm = 0;
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+            carry[ch] = 0;
+#pragma unroll
+            for (int p = 0; p < G; ++p) { A[ch][p] = 0; B[ch][p] = 0; Bon[ch][p] = 0; }
+        }
+        // valid-column masks of the last chunk (chen17 only: a padded column can
+        // receive the +R bonus of the last valid column)
+        uint32_t vmask[ALIGN ? G : 1];
+        if (ALIGN) {
+            const int c0 = (nch - 1) * CHUNK + lane * LB;
+#pragma unroll
+            for (int p = 0; p < G; ++p)
+                vmask[p] = ((c0 + p < N) ? 0x0000FFFFu : 0u) | ((c0 + p + G < N) ? 0xFFFF0000u : 0u);
+        }
+
+        RowBytes<G> cur[NCH];
+        if (M > 2) {
+            if (ALIGN) {
+                // bonus of row 1
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch)
+                    if (ch < nch) {
+                        RowBytes<G> r1;
+                        r1.load(base + (int64_t)1 * pitch + ch * CHUNK);
+                        StepUnroll<G, G - 1>::bonus(r1, Bon[ch]);
+                    }
+            }
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                if (ch < nch) cur[ch].load(base + (int64_t)2 * pitch + ch * CHUNK);
+                else cur[ch].fill(0xFFFFFFFFu);
+            }
+        }
+        for (int i = 2; i < M; ++i) {
+            RowBytes<G> nxt[NCH];
+            const bool more = (i + 1 < M);
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                if (more && ch < nch) nxt[ch].load(base + (int64_t)(i + 1) * pitch + ch * CHUNK);
+                else nxt[ch].fill(0xFFFFFFFFu);
+            }
+            // L2 prefetch a few rows ahead (one 128 B line per 128/LB lanes)
+            if (i + 6 < M) {
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch)
+                    if (ch < nch && (lane * LB) % 128 == 0)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (int64_t)(i + 6) * pitch + ch * CHUNK));
+            }
+            // chunks in DESCENDING order so that A[ch-1] still holds row i-1
+#pragma unroll
+            for (int ch = NCH - 1; ch >= 0; --ch) {
+                if (ch < nch) {
+                    // left neighbour group's edge registers of row i-1
+                    uint32_t g1 = A[ch][G - 1], g2 = A[ch][G - 2];
+                    if (lane == 31) {
+                        g1 = (ch > 0) ? A[ch > 0 ? ch - 1 : 0][G - 1] : 0u;
+                        g2 = (ch > 0) ? A[ch > 0 ? ch - 1 : 0][G - 2] : 0u;
+                    }
+                    // lane 31 of chunk ch-1 is the left neighbour of lane 0 of chunk ch;
+                    // for ch == 0 lane 0 has no left neighbour (columns < 0 are zero)
+                    uint32_t n1 = __shfl_sync(0xffffffffu, g1, (lane + 31) & 31);
+                    uint32_t n2 = __shfl_sync(0xffffffffu, g2, (lane + 31) & 31);
+                    // (lane 31's own value for lane 0's use was replaced above; lanes 1..31 read
+                    //  lanes 0..30, which hold their own A[ch])
+                    const uint32_t s1_0 = prmt(n1, A[ch][G - 1], 0x5432);   // (nbr cell 2G-1, own cell G-1)
+                    const uint32_t s2_0 = prmt(n2, A[ch][G - 2], 0x5432);   // (nbr cell 2G-2, own cell G-2)
+                    uint32_t dsh = 0;   // chen17: packed delta of (i, j-1) for p = 0
+                    if (ALIGN) {
+                        // current row's delta of the left neighbour's last register
+                        uint32_t dl_last = cur[ch].template delta<G - 1>();
+                        uint32_t dsrc = dl_last;
+                        if (lane == 31) dsrc = (ch > 0) ? cur[ch > 0 ? ch - 1 : 0].template delta<G - 1>() : 0xFFFFFFFFu;
+                        uint32_t nd = __shfl_sync(0xffffffffu, dsrc, (lane + 31) & 31);
+                        dsh = prmt(nd, dl_last, 0x5432);
+                    }
+                    uint32_t Nw[G];
+                    StepUnroll<G, G - 1>::template run<ALIGN>(A[ch], B[ch], cur[ch], s1_0, s2_0, carry[ch],
+                                                              Bon[ch], dsh, Nw);
+                    if (ch == 0) { Nw[0] &= zmask; Nw[1] &= zmask; }
+#pragma unroll
+                    for (int p = 0; p < G; ++p) { B[ch][p] = A[ch][p]; A[ch][p] = Nw[p]; }
+                    carry[ch] = s1_0;
+                    if (ALIGN) {
+                        StepUnroll<G, G - 1>::bonus(cur[ch], Bon[ch]);
+                        if (ch == nch - 1) {
+#pragma unroll
+                            for (int p = 0; p < G; ++p) Nw[p] &= vmask[p];
+                        }
+                    }
+#pragma unroll
+                    for (int p = 0; p < G; p += 2) rm = __vimax3_s16x2(rm, Nw[p], Nw[p + 1]);
+                }
+            }
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) cur[ch] = nxt[ch];
+        }
+        int best = max((int)(rm & 0xFFFFu), (int)(rm >> 16));
+        best = __reduce_max_sync(0xffffffffu, best);
+        if (lane == 0) out[pd.out_idx] = 0.5f * (float)best;
+    }
+}
+
+// Fully unrolled per-register update, P = G-1 .. 0 (recursion keeps every
+// register index a compile-time constant).
+template <int G, int P> struct StepUnroll {
+    template <int ALIGN>
+    __device__ __forceinline__ static void run(const uint32_t (&A)[G], const uint32_t (&B)[G],
+                                               const RowBytes<G>& row, uint32_t s1_0, uint32_t s2_0,
+                                               uint32_t carry, const uint32_t (&Bon)[G],
+                                               uint32_t dsh, uint32_t (&Nw)[G])
+    {
+        const uint32_t a1 = (P >= 1) ? A[P >= 1 ? P - 1 : 0] : s1_0;                 // row i-1, col j-1
+        const uint32_t b1 = (P >= 1) ? B[P >= 1 ? P - 1 : 0] : carry;                // row i-2, col j-1
+        const uint32_t a2 = (P >= 2) ? A[P >= 2 ? P - 2 : 0] : (P == 1 ? s1_0 : s2_0); // row i-1, col j-2
+        const uint32_t dl = row.template delta<P>();
+        uint32_t m;
+        if (ALIGN) {
+            // chen17: (i-2,j-1) + R(i-1,j)  and  (i-1,j-2) + R(i,j-1)
+            const uint32_t dprev = (P >= 1) ? row.template delta<(P >= 1 ? P - 1 : 0)>() : dsh;
+            const uint32_t b1b = b1 + Bon[P];
+            const uint32_t a2b = a2 + delta_to_bonus(dprev);
+            m = __vimax3_s16x2(a1, b1b, a2b);
+        } else {
+            m = __vimax3_s16x2(a1, b1, a2);
+        }
+        Nw[P] = __viaddmax_s16x2(m, dl, 0u);    // R=1: m+2 ; R=0: max(m-1, 0)
+        StepUnroll<G, P - 1>::template run<ALIGN>(A, B, row, s1_0, s2_0, carry, Bon, dsh, Nw);
+    }
+    __device__ __forceinline__ static void bonus(const RowBytes<G>& row, uint32_t (&Bon)[G])
+    {
+        Bon[P] = delta_to_bonus(row.template delta<P>());
+        StepUnroll<G, P - 1>::bonus(row, Bon);
+    }
+};
+template <int G> struct StepUnroll<G, -1> {
+    template <int ALIGN>
+    __device__ __forceinline__ static void run(const uint32_t (&)[G], const uint32_t (&)[G], const RowBytes<G>&,
+                                               uint32_t, uint32_t, uint32_t, const uint32_t (&)[G],
+                                               uint32_t, uint32_t (&)[G]) {}
+    __device__ __forceinline__ static void bonus(const RowBytes<G>&, uint32_t (&)[G]) {}
+};
+
+// ---- generic fallback: any N, any gammas, fp32 like the oracle -------------------
+// One warp per pair; rows i-1 / i-2 of the score matrix and the needed CRP rows in
+// shared memory.  Used for tracks longer than the register kernel supports and for
+// disOnset != disExtension or values other than 0.5.  CRP in delta code.
+__global__ void __launch_bounds__(32)
+dp_generic_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
+                  const uint8_t* __restrict__ crp, int alignment,
+                  float g_onset, float g_ext, int maxN, float* __restrict__ out)
+{
+    extern __shared__ float sm[];
+    float* S1 = sm;                 // row i-1
+    float* S2 = S1 + maxN;          // row i-2
+    float* S0 = S2 + maxN;          // row i
+    const int lane = threadIdx.x;
+    for (int64_t pidx = blockIdx.x; pidx < n_pairs; pidx += gridDim.x) {
+        const PairDesc pd = descs[pidx];
+        const int M = pd.M, N = pd.N;
+        const uint8_t* R = crp + pd.crp_off;
+        const int64_t pitch = pd.pitch;
+        for (int j = lane; j < N; j += 32) { S1[j] = 0.f; S2[j] = 0.f; S0[j] = 0.f; }
+        __syncwarp();
+        float best = 0.f;
+        for (int i = 2; i < M; ++i) {
+            const uint8_t* r0 = R + (int64_t)i * pitch;
+            const uint8_t* r1 = r0 - pitch;
+            const uint8_t* r2 = r1 - pitch;
+            for (int j = 2 + lane; j < N; j += 32) {
+                float p1 = S1[j - 1], p2 = S2[j - 1], p3 = S1[j - 2];
+                if (alignment == 1) {
+                    p2 += (r1[j] == CRP_DELTA_ONE) ? 1.f : 0.f;
+                    p3 += (r0[j - 1] == CRP_DELTA_ONE) ? 1.f : 0.f;
+                }
+                float v;
+                if (r0[j] == CRP_DELTA_ONE) {
+                    v = fmaxf(p1, fmaxf(p2, p3)) + 1.0f;
+                } else {
+                    float c1 = p1 - ((r1[j - 1] == CRP_DELTA_ONE) ? g_onset : g_ext);
+                    float c2 = p2 - ((r2[j - 1] == CRP_DELTA_ONE) ? g_onset : g_ext);
+                    float c3 = p3 - ((r1[j - 2] == CRP_DELTA_ONE) ? g_onset : g_ext);
+                    v = fmaxf(fmaxf(0.f, c1), fmaxf(c2, c3));
+                }
+                S0[j] = v;
+                best = fmaxf(best, v);
+            }
+            __syncwarp();
+            float* t = S2; S2 = S1; S1 = S0; S0 = t;
+            // S0 (old i-2 row) keeps stale values at j >= 2, all overwritten next row; j < 2 stay 0
+        }
+        for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+        if (lane == 0) out[pd.out_idx] = best;
+        __syncwarp();
+    }
+}
+
+// ---- constrained Smith-Waterman (alignment_tools.py:25-46), integer tenths ----------
+// S[i][j] = max(0, S[i-1][j-1]+mv+dl(B[i-2][j-2]), S[i-2][j-1]+mv+dl(B[i-3][j-2]),
+//               S[i-1][j-2]+mv+dl(B[i-2][j-3])),  mv = +1/-1 by B[i-1][j-1],
+// dl(v) = 0 if v > 0 else -0.7 (Q7: the gap_opening branch is unreachable).
+// All increments are multiples of 0.1: {+1, +0.3, -1, -1.7} -> exact int32 tenths.
+// Same dependency shape as Qmax (two previous rows) => same row-parallel scheme;
+// one warp per matrix, rows in shared memory.  Input: plain 0/1 bytes.
+__global__ void __launch_bounds__(32)
+sw_constrained_kernel(const uint8_t* __restrict__ mats, const int64_t* __restrict__ mat_off,
+                      const int32_t* __restrict__ Ms, const int32_t* __restrict__ Ns,
+                      int n, int maxN, double* __restrict__ out)
+{
+    extern __shared__ int smi[];
+    int* S1 = smi;
+    int* S2 = S1 + maxN;
+    int* S0 = S2 + maxN;
+    const int lane = threadIdx.x;
+    for (int k = blockIdx.x; k < n; k += gridDim.x) {
+        const int M = Ms[k], N = Ns[k];
+        const uint8_t* Bm = mats + mat_off[k];
+        int best = 0;
+        if (M >= 4 && N >= 4) {
+            for (int j = lane; j < N; j += 32) { S1[j] = 0; S2[j] = 0; S0[j] = 0; }
+            __syncwarp();
+            for (int i = 3; i < M; ++i) {
+                const uint8_t* b1 = Bm + (int64_t)(i - 1) * N;
+                const uint8_t* b2 = b1 - N;
+                const uint8_t* b3 = b2 - N;
+                for (int j = 3 + lane; j < N; j += 32) {
+                    int mv = b1[j - 1] ? 10 : -10;
+                    int d1 = S1[j - 1] + mv + (b2[j - 2] ? 0 : -7);
+                    int d2 = S2[j - 1] + mv + (b3[j - 2] ? 0 : -7);
+                    int d3 = S1[j - 2] + mv + (b2[j - 3] ? 0 : -7);
+                    int v = max(max(d1, d2), max(d3, 0));
+                    S0[j] = v;
+                    best = max(best, v);
+                }
+                __syncwarp();
+                int* t = S2; S2 = S1; S1 = S0; S0 = t;
+            }
+            best = __reduce_max_sync(0xffffffffu, best);
+        }
+        if (lane == 0) out[k] = (double)best / 10.0;
+        __syncwarp();
+    }
+}

@@ -1,0 +1,113 @@
+# -*- coding: utf-8 -*-
+"""
+Serra, J., Serra, X., & Andrzejak, R. G. (2009). Cross recurrence quantification for cover
+song identification.  New Journal of Physics, 11(9), 093017.
+
+Host-side mirror of the reference's `Serra09` (acoss/algorithms/rqa_serra09.py:31-83):
+same constructor keywords, `load_features`, `similarity(idxs)`, `normalize_by_length`.
+The per-pair essentia calls (ChromaCrossSimilarity + CoverSongSimilarity, :60-67) are
+replaced by one batched GPU call through the C-ABI (acoss_serra09_pairs).
+"""
+import numpy as np
+
+from .algorithm_template import CoverAlgorithm, _torch
+
+__all__ = ['Serra09']
+
+
+class ChromaPairAlgorithm(CoverAlgorithm):
+    """Shared plumbing of Serra09 and ChenFusion: median-downsampled chroma per track,
+    uploaded once, pairs evaluated in batches on the device."""
+
+    def _init_chroma(self, chroma_type, oti, kappa, tau, m, downsample_fac):
+        self.oti = oti
+        self.tau = tau
+        self.m = m
+        self.chroma_type = chroma_type
+        self.kappa = kappa
+        self.downsample_fac = downsample_fac
+        self.all_feats = {}  # For caching features (downsampled chroma)
+        self._uploaded = False
+
+    def _downsample(self, chromas):
+        """librosa.util.sync(chroma.T, arange(0, T, fac), aggregate=np.median).T on the device
+        (reference: rqa_serra09.py:51)."""
+        chromas = [np.ascontiguousarray(c, dtype=np.float32) for c in chromas]
+        if self.downsample_fac == 1:
+            return chromas
+        return [np.array(x) for x in self.context().median_downsample(chromas, self.downsample_fac)]
+
+    def load_features(self, i):
+        if not i in self.all_feats:
+            feats = CoverAlgorithm.load_features(self, i)
+            chroma = feats[self.chroma_type]
+            self.all_feats[i] = self._downsample([chroma])[0]
+        return self.all_feats[i]
+
+    def preload(self):
+        """Load + downsample every track in one device batch and upload the track store."""
+        if self._uploaded:
+            return
+        missing = [i for i in range(self.N) if i not in self.all_feats]
+        if missing:
+            raw = [CoverAlgorithm.load_features(self, i)[self.chroma_type] for i in missing]
+            for i, x in zip(missing, self._downsample(raw)):
+                self.all_feats[i] = x
+        self.context().upload_tracks([self.all_feats[i] for i in range(self.N)], m=self.m, tau=self.tau)
+        self._uploaded = True
+
+    def crp_params(self):
+        return self.context().params(m=self.m, tau=self.tau, kappa=self.kappa, oti=self.oti)
+
+    def pair_cost(self, idxs):
+        self.preload()
+        n = np.array([self.all_feats[i].shape[0] for i in range(self.N)], dtype=np.int64)
+        return n[idxs[:, 0]] * n[idxs[:, 1]]
+
+    def _normalize(self, mode):
+        torch = _torch()
+        self.preload()
+        dev = torch.device("cuda", self.device_index())
+        lengths = torch.from_numpy(np.array([self.all_feats[j].shape[0] for j in range(self.N)], dtype=np.int32)).to(dev)
+        for key in self.Ds:
+            D = torch.from_numpy(np.array(self.Ds[key], dtype=np.float32)).to(dev)
+            torch.cuda.synchronize(dev)
+            self.context().normalize_by_length_dev(D.data_ptr(), self.N, lengths.data_ptr(), mode)
+            self.context().synchronize()
+            self.Ds[key][:, :] = D.cpu().numpy()
+
+
+class Serra09(ChromaPairAlgorithm):
+    """
+    Attributes
+    ----------
+    Same as CoverAlgorithms, plus
+    chroma_type: string
+        Type of chroma to use (key into features)
+    downsample_fac: int
+        The factor by which to downsample the HPCPs with median aggregation
+    all_feats: {int: ndarray}
+        Cached features
+    """
+
+    def __init__(self, dataset_csv, datapath, chroma_type='hpcp', shortname='benchmark',
+                 oti=True, kappa=0.095, tau=1, m=9, downsample_fac=40, cachedir="cache", device=None):
+        self._init_chroma(chroma_type, oti, kappa, tau, m, downsample_fac)
+        CoverAlgorithm.__init__(self, dataset_csv=dataset_csv, name="Serra09", datapath=datapath,
+                                shortname=shortname, cachedir=cachedir, device=device)
+
+    def similarity(self, idxs):
+        idxs = np.asarray(idxs).reshape(-1, 2)
+        if len(idxs) == 0:
+            return
+        self.preload()
+        ctx = self.context()
+        qmax, _ = ctx.serra09_pairs(idxs, self.crp_params())
+        self.last_stats = ctx.pair_stats()
+        for key in self.Ds.keys():
+            self.Ds[key][idxs[:, 0], idxs[:, 1]] = qmax
+
+    def normalize_by_length(self):
+        """Do a non-symmetric normalization by length: Ds[i, j] /= sqrt(len_j)
+        (rqa_serra09.py:71-83)."""
+        self._normalize(0)

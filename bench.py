@@ -1,0 +1,427 @@
+#!/usr/bin/env python
+# -*- coding: utf-8 -*-
+"""
+bench.py -- Serra09 (OTI + CRP + Qmax) all-pairs throughput on a synthetic Da-TACOS-benchmark-shape
+set (BASELINE.json configs[1]; SURVEY.md section 8(d) "C2"), one process per GPU.
+
+    python bench.py --gpus 1 --steps 3 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the reference's CPU path (oracle port) on host cores
+
+A "step" = one pass of the hot path over the whole pair grid: OTI -> cross-similarity ->
+percentile thresholds -> binary CRP -> Qmax -> (all-gather of score vectors, N > 1) ->
+N x N scatter/mirror -> length normalisation -> MR/MRR/MDR/MAP/Top-k.  The pair grid of the
+FIXED 1000-track job is sharded across ranks by cost (strong scaling).  Rank 0 prints one JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "serra09_allpairs_comparisons_per_sec"
+UNIT = "pairs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--shape", default="datacos1000", help="synth.SHAPES key (default: 1000 tracks)")
+    ap.add_argument("--regime", default="L", choices=["S", "R", "L"],
+                    help="track-length regime (SURVEY 8(d)); L = n~U[1600,2400] frames at the DP stage")
+    ap.add_argument("--scale", type=float, default=1.0, help="DEBUG ONLY: shrink the number of works")
+    ap.add_argument("--crp-mode", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true", help="DEBUG ONLY: skip the end-to-end leg")
+    ap.add_argument("--no-cpu", action="store_true", help="DEBUG ONLY: skip the cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), bf16=float(d["bf16_tflops"]), bf16_sus=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    src="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+def make_workload(args):
+    """Downsampled chroma of every track (what Serra09.load_features returns) + labels."""
+    from acoss_b200 import synth
+    ds = synth.make_named(args.shape, args.regime, scale=args.scale)
+    fac = ds["fac"]
+    return ds, fac
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.path = os.path.join(tempfile.gettempdir(), "acoss_clocks_%d_%d.csv" % (os.getpid(), index))
+        self.proc = None
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+            self.f.close()
+            sm, mx, reasons = [], [], set()
+            for line in open(self.path):
+                p = [x.strip() for x in line.split(",")]
+                if len(p) < 9:
+                    continue
+                try:
+                    sm.append(float(p[1])); mx.append(float(p[2]))
+                except ValueError:
+                    continue
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], p[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            if sm:
+                out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+            os.remove(self.path)
+        except Exception:
+            pass
+        return out
+
+
+def cpu_baseline_sample(tracks, all_pairs, target_seconds, seed=0):
+    """The oracle port (single-threaded per pair like essentia) fanned out over all host threads
+    on a bounded random sample of the workload's pairs."""
+    from oracle import oracle as O
+    O.build()
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(seed)
+    probe = all_pairs[rng.choice(len(all_pairs), size=min(len(all_pairs), cores), replace=False)]
+    t0 = time.perf_counter()
+    O.serra09_pairs(tracks, probe, n_threads=cores)
+    t_probe = time.perf_counter() - t0
+    per_round = max(t_probe, 1e-4)                      # seconds per `cores` pairs
+    n = int(min(len(all_pairs), max(cores, cores * round(target_seconds / per_round))))
+    sample = all_pairs[rng.choice(len(all_pairs), size=n, replace=False)]
+    t0 = time.perf_counter()
+    q, _, cells = O.serra09_pairs(tracks, sample, n_threads=cores)
+    dt = time.perf_counter() - t0
+    return dict(value=n / dt, unit=UNIT, cores=cores, kind="port",
+                sample="%d random pairs of the %d-pair grid (%.1f s, %d threads, oracle/acoss_oracle.c -O2 "
+                       "-ffp-contract=off); %.4f GCUPS" % (n, len(all_pairs), dt, cores, cells / dt / 1e9),
+                seconds=dt, gcups=cells / dt / 1e9)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (oracle port: essentia is
+    not installable here) with all host threads; each step = a bounded sample of the workload."""
+    if rank != 0:
+        return
+    ds, fac = make_workload(args)
+    from oracle import oracle as O
+    tracks = [O.sync_median(h, fac) if fac > 1 else h for h in ds["hpcp"]]
+    n = len(tracks)
+    i, j = np.triu_indices(n, 1)
+    all_pairs = np.stack([i, j], 1).astype(np.int32)
+    per_step = max(2.0, min(30.0, 150.0 / max(1, args.steps + args.warmup)))
+    vals, last = [], None
+    for s in range(args.warmup + args.steps):
+        last = cpu_baseline_sample(tracks, all_pairs, per_step, seed=s)
+        if s >= args.warmup:
+            vals.append(last)
+    tot_pairs = sum(v["value"] * v["seconds"] for v in vals)
+    tot_s = sum(v["seconds"] for v in vals)
+    value = tot_pairs / tot_s
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / max(1, len(vals)), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, n, len(all_pairs)),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def workload_config(args, n_tracks, n_pairs):
+    return {"workload": "C2-%s: Serra09 (OTI+CRP+Qmax) all-pairs, %d synthetic Da-TACOS-benchmark-shape HPCP tracks "
+                        "(%s), %d pairs, m=9 tau=1 kappa=0.095" % (
+                            args.regime, n_tracks,
+                            {"L": "n~U[1600,2400] frames at the DP stage, downsample_fac=1",
+                             "R": "raw T~U[15000,25000], downsample_fac=40",
+                             "S": "raw T~U[1600,2400], downsample_fac=40"}[args.regime], n_pairs),
+            "shape": args.shape, "regime": args.regime, "tracks": n_tracks, "pairs": n_pairs,
+            "l2_policy": "inputs larger than L2: every step re-streams the CRP working set (GBs) through HBM",
+            "debug_scale": args.scale}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import acoss_b200
+    from acoss_b200.algorithm_template import shard_pairs
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    ctx = acoss_b200.Context(local_rank)          # raises if the CUDA library / device is missing
+    ds, fac = make_workload(args)
+    raw = ds["hpcp"]
+    tracks = ctx.median_downsample(raw, fac) if fac > 1 else raw
+    tracks = [np.ascontiguousarray(t, np.float32) for t in tracks]
+    n = len(tracks)
+    lengths_np = np.array([t.shape[0] for t in tracks], np.int32)
+    i, j = np.triu_indices(n, 1)
+    all_pairs = np.stack([i, j], 1).astype(np.int32)
+    P = len(all_pairs)
+    cost = lengths_np[all_pairs[:, 0]].astype(np.int64) * lengths_np[all_pairs[:, 1]]
+    mine = shard_pairs(all_pairs, cost, rank, world)
+    my_pairs = np.ascontiguousarray(all_pairs[mine])
+    prm = ctx.params(crp_mode=args.crp_mode)
+
+    # clique layout for the device evaluation (same construction as getEvalStatistics)
+    cl = {}
+    for k, l in enumerate(ds["labels"]):
+        cl.setdefault(l, []).append(k)
+    cliques = list(cl.values())
+    Ks = np.array([len(c) for c in cliques])
+    o = np.argsort(-Ks)
+    cliques = [cliques[k] for k in o]
+    Ks = Ks[o]
+    order = np.concatenate(cliques).astype(np.int32)
+    csize = np.repeat(Ks, Ks).astype(np.int32)
+    cstart = np.repeat(np.concatenate([[0], np.cumsum(Ks)[:-1]]), Ks).astype(np.int32)
+    tops = np.array([1, 10, 100, 1000], np.int32)
+
+    # ---- resident state: features in HBM before the timed region
+    frames, offs = ctx.pack_tracks(tracks)
+    ctx.upload_tracks(frames=frames, offsets=offs)
+    stream = torch.cuda.ExternalStream(ctx.lib.acoss_ctx_stream(ctx.h), device=dev)
+    cap = (P + world - 1) // world + 1
+    d_scores_local = torch.zeros(cap, dtype=torch.float32, device=dev)
+    d_idx_local = torch.full((cap,), -1, dtype=torch.int64, device=dev)
+    d_idx_local[:len(mine)] = torch.from_numpy(mine).to(dev)
+    d_pairs_all = torch.from_numpy(all_pairs).to(dev)
+    d_scores_all = torch.zeros(P, dtype=torch.float32, device=dev)
+    d_D = torch.zeros((n, n), dtype=torch.float32, device=dev)
+    d_len = torch.from_numpy(lengths_np).to(dev)
+    if world > 1:
+        g_scores = [torch.empty_like(d_scores_local) for _ in range(world)]
+        g_idx = [torch.empty_like(d_idx_local) for _ in range(world)]
+        dist.all_gather(g_idx, d_idx_local)          # the pair->rank map is static: gathered once
+    torch.cuda.synchronize(dev)
+    stats_acc = []
+    launches = [0]
+    result = {}
+
+    def step_resident():
+        ctx.serra09_pairs_dev(my_pairs, prm, d_scores_local.data_ptr(), 0)     # syncs its stream at the end
+        st = ctx.pair_stats()
+        launches[0] += st["n_launches"]
+        if world > 1:
+            dist.all_gather(g_scores, d_scores_local)
+            for gi, gs in zip(g_idx, g_scores):
+                ok = gi >= 0
+                d_scores_all[gi[ok]] = gs[ok]
+            launches[0] += 2 * world
+            torch.cuda.synchronize(dev)
+            src = d_scores_all
+        else:
+            src = d_scores_local      # `mine` is the identity permutation for world == 1
+        ctx.scores_to_matrix_dev(d_pairs_all.data_ptr(), src.data_ptr(), P, n, True, d_D.data_ptr())
+        ctx.normalize_by_length_dev(d_D.data_ptr(), n, d_len.data_ptr(), 0)
+        out, ranks = ctx.eval_statistics(d_D.data_ptr(), n, order, csize, cstart, tops)
+        launches[0] += 3
+        result["eval"] = out
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        ctx.synchronize()
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    launches[0] = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        stats_acc.append(step_resident())
+    e1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    dev_ms = e0.elapsed_time(e1)
+    n_launch = launches[0]
+    # max over ranks of the device-event time of the timed region
+    t = torch.tensor([dev_ms, wall * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms = float(t[0]), float(t[1])
+    ms_per_step = dev_ms / args.steps
+    value = P / (ms_per_step * 1e-3)
+
+    # ---- end-to-end leg: reference-facing class API with HOST buffers, H2D/D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, ctx, ds, tracks, all_pairs, mine, world, rank, local_rank)
+
+    # ---- per-kernel roofline (this rank; DP kernel = HBM-bound at 1 B/cell)
+    pk = peaks()
+    ms_dp = float(np.mean([s["ms_dp"] for s in stats_acc]))
+    ms_crp = float(np.mean([s["ms_crp"] for s in stats_acc]))
+    ms_tot = float(np.mean([s["ms_total"] for s in stats_acc]))
+    st = stats_acc[-1]
+    n_dp_launch = max(1, st["n_dp_launches"])
+    dp_bytes = st["crp_bytes"] + 4 * len(mine)              # algorithmic: M*pitch CRP bytes read once + 4 B score
+    dp_gbs = dp_bytes / (ms_dp * 1e-3) / 1e9
+    gcups = st["dp_cells"] / (ms_dp * 1e-3) / 1e9
+    crp_flop = 2.0 * 108 * st["crp_cells"] + 5.0 * st["crp_cells"]
+    crp_tflops = crp_flop / (ms_crp * 1e-3) / 1e12
+    kernels = [
+        {"kernel": "dp_rowpar_kernel (Qmax)", "bound": "hbm", "achieved": dp_gbs, "peak": pk["hbm"], "unit": "GB/s",
+         "frac": dp_gbs / pk["hbm"], "traffic": None, "ms_per_step": ms_dp, "launches_per_step": n_dp_launch,
+         "gcups": gcups, "share_of_step": ms_dp / ms_tot},
+        {"kernel": "crp_strip kernels (cross-similarity + thresholds + binarise)", "bound": "tensor", "achieved": crp_tflops,
+         "peak": pk["bf16_sus"], "unit": "TFLOP/s", "frac": crp_tflops / pk["bf16_sus"], "traffic": None,
+         "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
+         "note": "algorithmic flop = (2*108+5)*M*N per pair; runs on the fp32 CUDA cores (bit-exact op order), see DESIGN.md"},
+    ]
+    dominant = max(kernels, key=lambda k: k["ms_per_step"])
+    roofline = {k: dominant[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}
+    roofline["kernel"] = dominant["kernel"]
+    roofline["peak_source"] = pk["src"]
+
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cpu = cpu_baseline_sample(tracks, all_pairs, args.cpu_seconds)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    ev = result["eval"]
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(args, n, P),
+            "dp_gcups": gcups * world if world > 1 else gcups, "wall_ms_per_step": wall_ms / args.steps,
+            "roofline": roofline, "roofline_kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(n_launch), "clocks": clocks,
+            "eval": {"MR": ev[0], "MRR": ev[1], "MDR": ev[2], "MAP": ev[3], "Top-1": ev[4]},
+            "batches_per_step": int(st["n_batches"])}
+    print(json.dumps(line))
+
+
+def run_e2e(args, ctx, ds, tracks, all_pairs, mine, world, rank, local_rank):
+    """Same metric through the reference-facing call: host numpy features in, host score matrix and
+    eval tuple out.  Every step: H2D of all features + pair list, D2H of the scores, N x N matrix
+    round trip for the normalisation and the evaluation (what Serra09.all_pairwise /
+    normalize_by_length / getEvalStatistics do)."""
+    import contextlib
+    import io
+    import torch
+    import torch.distributed as dist
+    import acoss_b200
+    from acoss_b200 import synth
+    dev = torch.device("cuda", local_rank)
+    tmp = tempfile.mkdtemp(prefix="acoss_bench_r%d_" % rank)
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        # feature files are not re-read inside the timed region (disk is out of scope): the class's
+        # host-side cache is primed, the device upload is forced every step
+        csv = os.path.join(tmp, "ds.csv")
+        with open(csv, "w") as f:
+            f.write("work_id,track_id\n")
+            for w, t in zip(ds["work_ids"], ds["track_ids"]):
+                f.write("%s,%s\n" % (w, t))
+        sink = io.StringIO()
+        with contextlib.redirect_stdout(sink):
+            s = acoss_b200.Serra09(csv, os.path.join(tmp, "feat") + "/", shortname="bench", downsample_fac=ds["fac"],
+                                   cachedir=os.path.join(tmp, "cache"), device=local_rank)
+        s._ctx = ctx
+        for k, t in enumerate(tracks):
+            s.all_feats[k] = t
+            s.cliques.setdefault(ds["labels"][k], set([])).add(k)
+        n = len(tracks)
+        h2d = sum(t.nbytes for t in tracks) + 8 * (n + 1) + all_pairs[mine].nbytes + 2 * 4 * n * n + 4 * n
+        d2h = 4 * len(mine) + 4 * n * n + 8 * n
+        times = []
+        for it in range(1 + args.steps):          # 1 warm-up
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            with contextlib.redirect_stdout(sink):
+                s._uploaded = False
+                s.Ds["main"][:, :] = 0
+                s.all_pairwise(1, symmetric=True)
+                s.normalize_by_length()
+                res = s.getEvalStatistics("main")
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                dist.barrier()
+            if it > 0:
+                times.append(time.perf_counter() - t0)
+        tt = torch.tensor([float(np.mean(times))], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        sec = float(tt[0])
+        s.cleanup_memmap()
+        return {"value": len(all_pairs) / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": sec * 1e3, "api": "Serra09.all_pairwise + normalize_by_length + getEvalStatistics",
+                "MAP": res[3]}
+    finally:
+        os.chdir(cwd)
+        import shutil
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

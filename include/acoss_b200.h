@@ -1,0 +1,201 @@
+/*
+ * acoss_b200.h -- C-ABI of the B200-native all-pairs cover-song-similarity hot path.
+ *
+ * This is the drop-in boundary.  The reference (acoss,
+ * pure Python) reaches its per-pair arithmetic through two essentia Algorithm
+ * objects and a handful of numpy/numba free functions; a maintainer binds this
+ * library with ctypes at exactly those call sites.  Every
+ * entry point cites the reference interface it replaces (paths relative to the
+ * reference repository root).
+ *
+ * Conventions: extern "C"; plain pointers and sizes; int return (0 = ok, <0 =
+ * ACOSS_ERR_*; text via acoss_last_error); caller-owned input/output buffers;
+ * the context owns all device memory; one context per GPU; no exceptions cross
+ * the ABI; no CPU fallback -- every compute entry point fails with
+ * ACOSS_ERR_CUDA if the device is unusable.
+ *
+ * Pointer residency is part of each signature: "_host" parameters are ordinary
+ * host memory (numpy buffers); "_dev" parameters are device pointers valid on
+ * the context's device (e.g. torch tensors' data_ptr()).
+ */
+#ifndef ACOSS_B200_H
+#define ACOSS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct acoss_ctx acoss_ctx;
+
+enum {
+    ACOSS_OK = 0,
+    ACOSS_ERR_ARG = -1,         /* bad argument (null pointer, bad size, unknown enum) */
+    ACOSS_ERR_CUDA = -2,        /* CUDA runtime / launch failure, no usable device     */
+    ACOSS_ERR_TOO_SHORT = -3,   /* a track is too short to stack m frames (essentia raises) */
+    ACOSS_ERR_TOO_LONG = -4,    /* a track exceeds the on-chip strip budget            */
+    ACOSS_ERR_NOMEM = -5,       /* device allocation failed                            */
+    ACOSS_ERR_STATE = -6        /* call order (e.g. pairs before upload)               */
+};
+
+/* Parameters of the Serra09 / LateFusionChen pair kernel.  Replaces the keyword
+ * arguments of essentia ChromaCrossSimilarity(frameStackSize, frameStackStride,
+ * binarizePercentile, oti) and CoverSongSimilarity(disOnset, disExtension) as
+ * used at acoss/algorithms/rqa_serra09.py:60-64 and latefusion_chen.py:63-68. */
+typedef struct acoss_crp_params {
+    int32_t m;              /* frameStackSize, default 9                      */
+    int32_t tau;            /* frameStackStride, default 1                    */
+    float   kappa;          /* binarizePercentile, default 0.095              */
+    int32_t oti;            /* 1 = transpose reference by OTI (default)       */
+    float   dis_onset;      /* CoverSongSimilarity disOnset, default 0.5      */
+    float   dis_extension;  /* CoverSongSimilarity disExtension, default 0.5  */
+    int32_t crp_mode;       /* 0 = auto, 1 = exact-everywhere strips,
+                               2 = approximate + rigorous band + exact recheck */
+} acoss_crp_params;
+
+/* Timing / accounting of the last pair call (device time by CUDA events on the
+ * context's stream).  bench.py's roofline block is computed from these. */
+typedef struct acoss_pair_stats {
+    double  ms_total;        /* whole call, device events                      */
+    double  ms_prep;         /* OTI + descriptors                              */
+    double  ms_crp;          /* cross-similarity + thresholds + binarise       */
+    double  ms_dp;           /* Qmax/Dmax kernels only                         */
+    int64_t dp_cells;        /* sum (M-2)*(N-2) per DP run                     */
+    int64_t crp_cells;       /* sum M*N                                        */
+    int64_t crp_bytes;       /* bytes of CRP written to / read from HBM        */
+    int64_t n_launches;      /* kernels launched by this call                  */
+    int64_t n_dp_launches;
+    int64_t n_batches;
+    int64_t n_exact_cells;   /* cells recomputed exactly (band mode)           */
+} acoss_pair_stats;
+
+/* ---- context ------------------------------------------------------------- */
+
+/* Creates a context on CUDA device `device` (cudaSetDevice + stream).  */
+int acoss_ctx_create(int device, acoss_ctx **out);
+void acoss_ctx_destroy(acoss_ctx *ctx);
+/* Last error text of this context (or of the failed create when ctx == NULL). */
+const char *acoss_last_error(const acoss_ctx *ctx);
+/* Library identification: "acoss_b200 <version> sm_100a". */
+const char *acoss_version(void);
+/* The CUDA stream all work of this context is ordered on (cudaStream_t). */
+void *acoss_ctx_stream(acoss_ctx *ctx);
+/* Blocks until all work queued on the context's stream has finished. */
+int acoss_ctx_synchronize(acoss_ctx *ctx);
+
+/* ---- track store --------------------------------------------------------- */
+
+/* Uploads the (already median-downsampled) 12-bin chroma of all tracks:
+ * frames_host = concatenation of (n_t, 12) float32 arrays, offsets_host[n_tracks+1]
+ * = frame offsets.  Replaces the per-object feature cache Serra09.all_feats
+ * (rqa_serra09.py:44-53, latefusion_chen.py:46-56).  Also computes, on the
+ * device, each track's global chroma (essentia globalAverageChroma) and the
+ * exact self dot products of its delay-embedded rows for all 12 rotations. */
+int acoss_upload_tracks(acoss_ctx *ctx, const float *frames_host,
+                        const int64_t *offsets_host, int32_t n_tracks,
+                        int32_t m, int32_t tau);
+
+/* Median downsampling on the device: librosa.util.sync(chroma.T,
+ * arange(0, T, fac), aggregate=np.median).T for every track
+ * (rqa_serra09.py:51).  raw offsets in raw frames; out_offsets_host[n_tracks+1]
+ * and out_frames_host (sum ceil(T/fac), 12) are written. */
+int acoss_median_downsample(acoss_ctx *ctx, const float *raw_frames_host,
+                            const int64_t *raw_offsets_host, int32_t n_tracks,
+                            int32_t fac, float *out_frames_host,
+                            int64_t *out_offsets_host);
+
+/* ---- Serra09 / LateFusionChen pairs -------------------------------------- */
+
+/* For every pair (query, reference) in pairs_host[(P,2) int32]:
+ *   csm = ChromaCrossSimilarity(m, tau, kappa, oti)(feat[query], feat[reference])
+ *   qmax = CoverSongSimilarity('serra09','symmetric')(csm)[1]
+ *   dmax = CoverSongSimilarity('chen17','symmetric')(csm)[1]     (if out_dmax != NULL)
+ * i.e. the body of Serra09.similarity (rqa_serra09.py:55-69) and
+ * ChenFusion.similarity (latefusion_chen.py:58-73), batched.  Outputs are the
+ * raw maxima of the score matrices (float32, P each).  Host buffers. */
+int acoss_serra09_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pairs,
+                        const acoss_crp_params *params,
+                        float *out_qmax_host, float *out_dmax_host);
+
+/* Same, outputs written to device memory (asynchronously on the context's
+ * stream; inputs still host). */
+int acoss_serra09_pairs_dev(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pairs,
+                            const acoss_crp_params *params,
+                            float *out_qmax_dev, float *out_dmax_dev);
+
+/* Accounting of the last acoss_serra09_pairs* call (synchronises the stream). */
+int acoss_get_pair_stats(acoss_ctx *ctx, acoss_pair_stats *out);
+
+/* Test hook: the binary cross-recurrence plot of ONE pair, (M, N) uint8 0/1,
+ * rows = query frames (ChromaCrossSimilarity output, rqa_serra09.py:66).
+ * Optional (may be NULL): thresholds thr_q[M], thr_r[N], oti. */
+int acoss_crp_pair(acoss_ctx *ctx, int32_t query, int32_t reference,
+                   const acoss_crp_params *params, uint8_t *out_crp_host,
+                   int32_t *out_M, int32_t *out_N,
+                   float *out_thr_q_host, float *out_thr_r_host, int32_t *out_oti);
+
+/* Test hook / first kernel: CoverSongSimilarity on caller-supplied binary
+ * matrices.  crps_host = concatenation of n (M_k, N_k) uint8 0/1 row-major
+ * matrices; alignment 0 = 'serra09' (Qmax), 1 = 'chen17' (Dmax).
+ * Replaces alignment_algo(csm)[1] (rqa_serra09.py:67). */
+int acoss_cover_similarity_from_crp(acoss_ctx *ctx, const uint8_t *crps_host,
+                                    const int32_t *Ms_host, const int32_t *Ns_host,
+                                    int32_t n, int32_t alignment,
+                                    float dis_onset, float dis_extension,
+                                    float *out_scores_host);
+
+/* ---- N x N score matrix: scatter, mirror, length normalisation, evaluation -- */
+
+/* D (n x n float32, device) := 0, then D[i,j] = score for each pair, then
+ * D += D.T when symmetric != 0  (CoverAlgorithm.all_pairwise,
+ * algorithm_template.py:168-190). */
+int acoss_scores_to_matrix_dev(acoss_ctx *ctx, const int32_t *pairs_dev,
+                               const float *scores_dev, int64_t n_pairs,
+                               int32_t n, int32_t symmetric, float *D_dev);
+
+/* mode 0: D[i,j] /= sqrt(len_j)        (Serra09.normalize_by_length, rqa_serra09.py:71-83)
+ * mode 1: D[i,j] = sqrt(len_j)/D[i,j]  (ChenFusion.normalize_by_length, latefusion_chen.py:75-85)
+ * lengths = frames per track after downsampling (int32, device). float64
+ * arithmetic, float32 store, like the reference's memmap update. */
+int acoss_normalize_by_length_dev(acoss_ctx *ctx, float *D_dev, int32_t n,
+                                  const int32_t *lengths_dev, int32_t mode);
+
+/* CoverAlgorithm.getEvalStatistics (algorithm_template.py:206-291) on the device.
+ * D_dev: (n x n) float32, higher = more similar.  order_host[n]: the track
+ * indices in clique-contiguous order (cliques sorted by size, descending);
+ * clique_size_host[n]: for position p in that order the size of its clique;
+ * clique_start_host[n]: position where its clique starts.
+ * out_host[4 + n_tops] = MR, MRR, MDR, MAP, Top-k counts (float64).
+ * out_ranks_host (may be NULL): first-hit rank per position (NaN where the
+ * reference leaves NaN).  Ties are ranked by position (stable), SURVEY H5. */
+int acoss_eval_statistics(acoss_ctx *ctx, const float *D_dev, int32_t n,
+                          const int32_t *order_host, const int32_t *clique_size_host,
+                          const int32_t *clique_start_host,
+                          const int32_t *tops_host, int32_t n_tops,
+                          double *out_host, double *out_ranks_host);
+
+/* numpy's pairwise float64 summation, used by acoss_eval_statistics so that MR/MRR/MAP
+ * round exactly like np.mean/np.nanmean (algorithm_template.py:262-267).  Pure host
+ * arithmetic, exported so a CPU-only test can pin it against numpy. */
+double acoss_np_pairwise_sum(const double *a, int64_t n);
+
+/* ---- constrained Smith-Waterman (EarlyFusionTralie) ----------------------- */
+
+/* smith_waterman_constrained(B) for n binary matrices
+ * (acoss/algorithms/utils/alignment_tools.py:25-46).  Same packing as
+ * acoss_cover_similarity_from_crp.  Scores float64. */
+int acoss_sw_constrained_from_binary(acoss_ctx *ctx, const uint8_t *mats_host,
+                                     const int32_t *Ms_host, const int32_t *Ns_host,
+                                     int32_t n, double *out_scores_host);
+
+/* ---- plain device memory helpers for host languages without a CUDA binding -- */
+int acoss_dev_alloc(acoss_ctx *ctx, int64_t bytes, void **out_dev);
+int acoss_dev_free(acoss_ctx *ctx, void *dev);
+int acoss_memcpy_h2d(acoss_ctx *ctx, void *dst_dev, const void *src_host, int64_t bytes);
+int acoss_memcpy_d2h(acoss_ctx *ctx, void *dst_host, const void *src_dev, int64_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACOSS_B200_H */

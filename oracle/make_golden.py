@@ -1,0 +1,213 @@
+# -*- coding: utf-8 -*-
+"""
+CPU ORACLE (golden generator) -- TEST INFRASTRUCTURE ONLY, THIS CONTAINER ONLY.
+
+Freezes outputs of the reference's own Python code (imported verbatim from
+/root/reference through oracle/refload.py) and of the oracle under tests/golden/,
+so that the GPU box -- where /root/reference does not exist -- can check against
+them.  Run:  python -m oracle.make_golden        (from the repository root)
+
+Files written (all small .npz):
+  sw_reference.npz       smith_waterman_constrained (numba, verbatim) on random binary matrices
+  eval_reference.npz     CoverAlgorithm.getEvalStatistics (verbatim) on random + tied matrices
+  snf_reference.npz      doSimilarityFusion (verbatim) at (n_mats, N, K, niters) of SURVEY App. B-8
+  serra09_small.npz      16-track synthetic set: reference Serra09 / ChenFusion classes run
+                         verbatim on top of the C restatement of essentia (parity UNPINNED for
+                         that part) -> Ds before/after normalisation, eval tuples, a few CRPs
+  percentile_kat.npz     oracle percentile vs np.percentile(method='linear') in float32
+"""
+import contextlib
+import io
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def quiet(fn, *a, **k):
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        return fn(*a, **k)
+
+
+def gen_sw(ns):
+    rng = np.random.default_rng(1234)
+    shapes = [(3, 9), (4, 4), (5, 7), (12, 12), (40, 37), (64, 64), (100, 130), (257, 190), (300, 512)]
+    mats, scores = [], []
+    for (M, N) in shapes:
+        for dens in (0.05, 0.15, 0.5):
+            B = (rng.random((M, N)) < dens).astype(np.uint8)
+            # add a few diagonal runs so that scores are non-trivial
+            for _ in range(3):
+                L = int(rng.integers(2, max(3, min(M, N))))
+                i0, j0 = int(rng.integers(0, M - 1)), int(rng.integers(0, N - 1))
+                for k in range(L):
+                    if i0 + k < M and j0 + k < N:
+                        B[i0 + k, j0 + k] = 1
+            mats.append(B)
+            scores.append(float(ns.align.smith_waterman_constrained(B)))
+    d = {"n": len(mats), "scores": np.array(scores, np.float64)}
+    for k, B in enumerate(mats):
+        d["B%d" % k] = B
+    np.savez_compressed(os.path.join(GOLD, "sw_reference.npz"), **d)
+    print("sw_reference:", len(mats), "matrices")
+
+
+def _eval_verbatim(ns, D, labels, tmp):
+    """Run the reference's getEvalStatistics on matrix D with clique labels."""
+    csv = os.path.join(tmp, "e.csv")
+    with open(csv, "w") as f:
+        f.write("work_id,track_id\n")
+        for i, l in enumerate(labels):
+            f.write("%s,t%d\n" % (l, i))
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    try:
+        obj = quiet(ns.template.CoverAlgorithm, csv, name="E", datapath=tmp + "/", shortname="g", cachedir=os.path.join(tmp, "cache"))
+        for i, l in enumerate(labels):
+            obj.cliques.setdefault(l, set([])).add(i)
+        obj.Ds["main"][:, :] = D
+        res = quiet(obj.getEvalStatistics, "main")
+    finally:
+        os.chdir(cwd)
+    return res
+
+
+def gen_eval(ns):
+    rng = np.random.default_rng(99)
+    out = {}
+    cases = []
+    # (n_works, per_work, singletons)
+    for ci, (nw, pw, nsng, quant) in enumerate([(8, 2, 0, False), (5, 4, 7, False), (6, 13, 12, False), (10, 3, 5, True)]):
+        labels = []
+        for w in range(nw):
+            labels += ["W%d" % w] * pw
+        labels += ["S%d" % s for s in range(nsng)]
+        perm = rng.permutation(len(labels))
+        labels = [labels[p] for p in perm]
+        n = len(labels)
+        same = np.array([[labels[i] == labels[j] for j in range(n)] for i in range(n)])
+        D = rng.random((n, n)).astype(np.float32) + 0.35 * same
+        if quant:   # heavy quantisation -> ties exist; only tie-free-robust fields are compared
+            D = np.round(D * 4) / 4
+        D = D.astype(np.float32)
+        with tempfile.TemporaryDirectory() as tmp:
+            MR, MRR, MDR, MAP, tops = _eval_verbatim(ns, D, labels, tmp)
+        out["D%d" % ci] = D
+        out["labels%d" % ci] = np.array(labels)
+        out["res%d" % ci] = np.array([MR, MRR, MDR, MAP] + list(tops), np.float64)
+        out["ties%d" % ci] = np.array(int(quant))
+        cases.append(ci)
+    out["n"] = np.array(len(cases))
+    np.savez_compressed(os.path.join(GOLD, "eval_reference.npz"), **out)
+    print("eval_reference:", len(cases), "cases")
+
+
+def gen_snf(ns):
+    rng = np.random.default_rng(7)
+    out = {}
+    cfgs = [(2, 64, 5, 3), (3, 200, 20, 20), (4, 120, 20, 20)]
+    for ci, (nm, N, K, nit) in enumerate(cfgs):
+        mats = []
+        for _ in range(nm):
+            X = rng.random((N, 6))
+            Dm = np.sqrt(((X[:, None, :] - X[None, :, :]) ** 2).sum(-1)) + 0.05 * rng.random((N, N))
+            mats.append(Dm.astype(np.float32))
+        Ws, fused = ns.snf.doSimilarityFusion([np.array(m) for m in mats], K=K, niters=nit, reg_diag=1)
+        out["cfg%d" % ci] = np.array([nm, N, K, nit])
+        for k, m in enumerate(mats):
+            out["D%d_%d" % (ci, k)] = m
+        out["fused%d" % ci] = fused
+    out["n"] = np.array(len(cfgs))
+    np.savez_compressed(os.path.join(GOLD, "snf_reference.npz"), **out)
+    print("snf_reference:", len(cfgs), "configs")
+
+
+def gen_serra(ns):
+    import acoss_b200
+    from acoss_b200 import synth
+    from oracle import oracle as O
+    ds = synth.make_named("covers80", "S", seed=4242, scale=0.15)    # 12 works x 2 = 24 tracks, T ~ 1600-2400
+    out = {"n_tracks": np.array(len(ds["hpcp"])), "labels": np.array(ds["labels"]), "fac": np.array(ds["fac"])}
+    for i, h in enumerate(ds["hpcp"]):
+        out["hpcp%d" % i] = h
+    with tempfile.TemporaryDirectory() as tmp:
+        fdir = synth.write_dataset(os.path.join(tmp, "feat"), ds, os.path.join(tmp, "ds.csv"))
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            # --- reference Serra09 verbatim (orchestration) on the essentia restatement
+            s = quiet(ns.serra09.Serra09, os.path.join(tmp, "ds.csv"), fdir, shortname="g")
+            quiet(s.all_pairwise, 0, 1, True)
+            out["serra_raw"] = np.array(s.Ds["main"])
+            quiet(s.normalize_by_length)
+            out["serra_norm"] = np.array(s.Ds["main"])
+            out["serra_eval"] = np.array([x for x in quiet(s.getEvalStatistics, "main")[:4]], np.float64)
+            out["lengths"] = np.array([s.all_feats[i].shape[0] for i in range(s.N)], np.int32)
+            for i in range(s.N):
+                out["ds%d" % i] = np.asarray(s.all_feats[i], np.float32)
+            # --- reference ChenFusion verbatim
+            c = quiet(ns.chen.ChenFusion, os.path.join(tmp, "ds.csv"), fdir, shortname="g")
+            quiet(c.all_pairwise, 0, 1, True)
+            out["chen_q_raw"] = np.array(c.Ds["qmax"])
+            out["chen_d_raw"] = np.array(c.Ds["dmax"])
+            with np.errstate(divide="ignore"):
+                quiet(c.normalize_by_length)
+            out["chen_q_norm"] = np.array(c.Ds["qmax"])
+            out["chen_d_norm"] = np.array(c.Ds["dmax"])
+            with np.errstate(all="ignore"):
+                quiet(c.do_late_fusion)
+            out["chen_late"] = np.array(c.Ds["Late"])
+            ev = {}
+            for k in ("qmax", "dmax", "Late"):
+                ev[k] = quiet(c.getEvalStatistics, k)
+                out["chen_eval_" + k] = np.array(list(ev[k][:4]), np.float64)
+        finally:
+            os.chdir(cwd)
+    # a few full CRPs + thresholds from the oracle
+    pairs = [(0, 1), (2, 7), (5, 4), (10, 3), (23, 22)]
+    out["crp_pairs"] = np.array(pairs, np.int32)
+    for k, (a, b) in enumerate(pairs):
+        R, info = O.chroma_cross_similarity(out["ds%d" % a], out["ds%d" % b], full=True)
+        out["crp%d" % k] = R
+        out["thrq%d" % k] = info["thr_q"]
+        out["thrr%d" % k] = info["thr_r"]
+        out["oti%d" % k] = np.array(info["oti"])
+    np.savez_compressed(os.path.join(GOLD, "serra09_small.npz"), **out)
+    print("serra09_small: MAP", out["serra_eval"][3], "chen late MAP", out["chen_eval_Late"][3])
+
+
+def gen_percentile():
+    from oracle import oracle as O
+    rng = np.random.default_rng(5)
+    vs, ps = [], []
+    for n in (1, 2, 3, 11, 12, 41, 200, 1999, 2000):
+        v = rng.random(n).astype(np.float32) * 3
+        vs.append(v)
+        ps.append(O.percentile(v, 0.095))
+    d = {"n": np.array(len(vs)), "p": np.array(ps, np.float32)}
+    for k, v in enumerate(vs):
+        d["v%d" % k] = v
+    np.savez_compressed(os.path.join(GOLD, "percentile_kat.npz"), **d)
+    print("percentile_kat ok")
+
+
+def main():
+    from oracle import refload
+    os.makedirs(GOLD, exist_ok=True)
+    ns = refload.load()
+    gen_percentile()
+    gen_sw(ns)
+    gen_eval(ns)
+    gen_snf(ns)
+    gen_serra(ns)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,272 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C-ABI, against the oracle on the
+same seeded inputs, against the committed golden fixtures, and -- at large sizes -- through
+size-independent properties.  Bar: bit-exact for the CRP / thresholds / integer scores and ranks;
+normalised float32 matrices bit-equal (same float64 arithmetic); eval tuples identical."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _tracks(rng, lens, noise=0.15):
+    out = []
+    base = rng.random((max(lens) + 50, 12)).astype(np.float32)
+    for k, n in enumerate(lens):
+        x = np.roll(base[k % 7: k % 7 + n], k % 12, axis=1) + noise * rng.random((n, 12)).astype(np.float32)
+        x = x / x.max(axis=1, keepdims=True)
+        out.append(np.ascontiguousarray(x, np.float32))
+    return out
+
+
+# ---- first kernel: Qmax / Dmax on given binary matrices -------------------------------------
+def test_dp_known_answers(ctx):
+    L = 12
+    I = np.eye(L, dtype=np.uint8)
+    G = I.copy(); G[6, 6] = 0
+    Z = np.zeros((L, L), np.uint8)
+    O1 = np.ones((L, L), np.uint8)
+    q = ctx.cover_similarity_from_crp([I, G, Z, O1], "serra09")
+    d = ctx.cover_similarity_from_crp([I, G, Z, O1], "chen17")
+    assert q.tolist() == [10.0, 8.5, 0.0, 10.0]
+    assert d.tolist()[1:] == [8.5, 0.0, 14.0]
+
+
+@pytest.mark.parametrize("shape", [(3, 3), (2, 50), (50, 2), (41, 37), (64, 128), (130, 129), (300, 511), (257, 513),
+                                   (600, 1279), (500, 1281), (400, 1536), (300, 2391), (200, 2560), (90, 2700)])
+def test_dp_random_vs_oracle(ctx, oracle, shape):
+    rng = np.random.default_rng(shape[0] * 7919 + shape[1])
+    mats = []
+    for dens in (0.03, 0.1, 0.4):
+        B = (rng.random(shape) < dens).astype(np.uint8)
+        for _ in range(4):   # diagonal runs
+            i0, j0 = int(rng.integers(0, shape[0])), int(rng.integers(0, shape[1]))
+            L = int(rng.integers(1, 1 + min(shape)))
+            for k in range(L):
+                if i0 + k < shape[0] and j0 + k < shape[1]:
+                    B[i0 + k, j0 + k] = 1
+        mats.append(B)
+    for a in ("serra09", "chen17"):
+        got = ctx.cover_similarity_from_crp(mats, a)
+        exp = [oracle.cover_song_similarity(B, a)[1] for B in mats]
+        assert got.tolist() == exp, (a, shape)
+
+
+def test_dp_ragged_batch_and_general_gammas(ctx, oracle):
+    rng = np.random.default_rng(5)
+    mats = [(rng.random((int(rng.integers(1, 200)), int(rng.integers(1, 400)))) < 0.2).astype(np.uint8) for _ in range(40)]
+    for a in ("serra09", "chen17"):
+        assert ctx.cover_similarity_from_crp(mats, a).tolist() == [oracle.cover_song_similarity(B, a)[1] for B in mats]
+        for (go, ge) in [(0.5, 0.7), (0.25, 1.0)]:   # generic fp32 kernel
+            got = ctx.cover_similarity_from_crp(mats, a, go, ge)
+            exp = np.array([oracle.cover_song_similarity(B, a, go, ge)[1] for B in mats], np.float32)
+            assert np.array_equal(got, exp)
+
+
+def test_dp_rejects_non_binary(ctx):
+    import acoss_b200
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.cover_similarity_from_crp([np.full((5, 5), 2, np.uint8)])
+
+
+def test_dp_transpose_invariance_large(ctx):
+    """size-independent property at full size: the recurrences are symmetric in (i, j)."""
+    rng = np.random.default_rng(8)
+    B = (rng.random((2300, 2391)) < 0.08).astype(np.uint8)
+    for a in ("serra09", "chen17"):
+        s = ctx.cover_similarity_from_crp([B, np.ascontiguousarray(B.T[:, :2300])], a)
+        assert s[0] == s[1] and s[0] > 0
+
+
+# ---- constrained Smith-Waterman ----------------------------------------------------------------
+def test_sw_vs_reference_golden(ctx, golden):
+    g = golden("sw_reference.npz")
+    mats = [g["B%d" % k] for k in range(int(g["n"]))]
+    got = ctx.sw_constrained(mats)
+    assert np.array_equal(got.astype(np.float32), g["scores"].astype(np.float32))
+
+
+def test_sw_vs_oracle_random(ctx, oracle):
+    rng = np.random.default_rng(21)
+    mats = [(rng.random((int(rng.integers(1, 300)), int(rng.integers(1, 300)))) < 0.15).astype(np.uint8) for _ in range(30)]
+    got = ctx.sw_constrained(mats)
+    exp = np.array([oracle.sw_constrained(B) for B in mats])
+    assert np.array_equal(got.astype(np.float32), exp.astype(np.float32))
+
+
+# ---- CRP: OTI, thresholds, binary plot bit-exact -------------------------------------------------
+@pytest.mark.parametrize("m,tau", [(9, 1), (5, 2), (1, 1), (3, 3)])
+def test_crp_bit_exact_small(ctx, oracle, m, tau):
+    rng = np.random.default_rng(100 + m * 10 + tau)
+    lens = [40, 37, 64, 129, 300, 31, 55, 270]
+    tracks = _tracks(rng, lens)
+    ctx.upload_tracks(tracks, m=m, tau=tau)
+    prm = ctx.params(m=m, tau=tau)
+    for (a, b) in [(0, 1), (1, 0), (2, 3), (4, 3), (5, 6), (7, 4), (3, 3)]:
+        R, tq, tr, o = ctx.crp_pair(a, b, prm)
+        Ro, info = oracle.chroma_cross_similarity(tracks[a], tracks[b], m=m, tau=tau, full=True)
+        assert o == info["oti"]
+        assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"])
+        assert np.array_equal(R, Ro)
+
+
+def test_crp_kappa_and_no_oti(ctx, oracle):
+    rng = np.random.default_rng(77)
+    tracks = _tracks(rng, [90, 120, 200])
+    ctx.upload_tracks(tracks)
+    for kappa in (0.0, 0.05, 0.1, 0.5, 1.0):
+        for oti in (True, False):
+            prm = ctx.params(kappa=kappa, oti=oti)
+            R, tq, tr, o = ctx.crp_pair(0, 2, prm)
+            Ro, info = oracle.chroma_cross_similarity(tracks[0], tracks[2], kappa=kappa, oti=oti, full=True)
+            assert o == info["oti"] and np.array_equal(R, Ro)
+
+
+def test_crp_exact_ties_duplicate_frames(ctx, oracle):
+    """duplicated frames produce exactly equal distances: order statistics with ties"""
+    rng = np.random.default_rng(9)
+    a = rng.random((30, 12)).astype(np.float32)
+    q = np.concatenate([a, a, a[:15]], 0)
+    r = np.concatenate([a[5:], a[5:], np.zeros((12, 12), np.float32)], 0)
+    ctx.upload_tracks([q, r])
+    R, tq, tr, o = ctx.crp_pair(0, 1)
+    Ro, info = oracle.chroma_cross_similarity(q, r, full=True)
+    assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]) and np.array_equal(R, Ro)
+
+
+def test_crp_golden(ctx, golden):
+    g = golden("serra09_small.npz")
+    n = int(g["n_tracks"])
+    ctx.upload_tracks([g["ds%d" % i] for i in range(n)])
+    for k, (a, b) in enumerate(g["crp_pairs"]):
+        R, tq, tr, o = ctx.crp_pair(int(a), int(b))
+        assert o == int(g["oti%d" % k])
+        assert np.array_equal(tq, g["thrq%d" % k]) and np.array_equal(tr, g["thrr%d" % k])
+        assert np.array_equal(R, g["crp%d" % k])
+
+
+def test_too_short_track_errors(ctx):
+    import acoss_b200
+    ctx.upload_tracks([np.ones((9, 12), np.float32), np.ones((30, 12), np.float32)])
+    with pytest.raises(acoss_b200.AcossError) as e:
+        ctx.serra09_pairs(np.array([[0, 1]]))
+    assert e.value.code == -3
+
+
+# ---- pairs: scores ----------------------------------------------------------------------------
+def test_pairs_scores_vs_oracle(ctx, oracle):
+    rng = np.random.default_rng(31)
+    lens = [int(x) for x in rng.integers(30, 420, size=14)]
+    tracks = _tracks(rng, lens)
+    ctx.upload_tracks(tracks)
+    pairs = np.array([(i, j) for i in range(14) for j in range(14) if i != j], np.int32)
+    q, d = ctx.serra09_pairs(pairs, want_dmax=True)
+    oq, od, cells = oracle.serra09_pairs(tracks, pairs, want_dmax=True, n_threads=8)
+    assert np.array_equal(q, oq) and np.array_equal(d, od)
+    st = ctx.pair_stats()
+    assert st["dp_cells"] == 2 * cells and st["n_launches"] >= 5
+
+
+def test_pairs_scores_long_tracks_sample(ctx, oracle):
+    """BASELINE config sizes (n ~ 2000 at the DP stage): a few pairs against the oracle."""
+    rng = np.random.default_rng(32)
+    tracks = _tracks(rng, [2400, 1600, 2011, 1893])
+    ctx.upload_tracks(tracks)
+    pairs = np.array([(0, 1), (1, 0), (2, 3), (0, 3)], np.int32)
+    q, d = ctx.serra09_pairs(pairs, want_dmax=True)
+    oq, od, _ = oracle.serra09_pairs(tracks, pairs, want_dmax=True, n_threads=4)
+    assert np.array_equal(q, oq) and np.array_equal(d, od)
+
+
+def test_median_downsample_vs_oracle(ctx, oracle):
+    rng = np.random.default_rng(41)
+    raws = [rng.random((n, 12)).astype(np.float32) for n in (1, 39, 40, 41, 1600, 2399, 80)]
+    for fac in (40, 7, 2):
+        got = ctx.median_downsample(raws, fac)
+        for x, y in zip(got, raws):
+            assert np.array_equal(x, oracle.sync_median(y, fac))
+
+
+# ---- N x N stage + the reference-facing classes ------------------------------------------------
+def _write_golden_dataset(g, workdir):
+    from acoss_b200 import synth
+    n = int(g["n_tracks"])
+    labels = [str(x) for x in g["labels"]]
+    ds = dict(labels=labels, work_ids=labels, track_ids=["P_%d" % i for i in range(n)],
+              hpcp=[g["hpcp%d" % i] for i in range(n)], fac=int(g["fac"]))
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"))
+    return str(workdir / "ds.csv"), fdir
+
+
+def test_serra09_class_matches_reference_golden(golden, workdir):
+    """The reference's own Serra09 class (run verbatim on the essentia restatement, frozen in
+    tests/golden) vs the drop-in class: Ds before / after normalisation bit-equal, eval identical."""
+    import acoss_b200
+    g = golden("serra09_small.npz")
+    csv, fdir = _write_golden_dataset(g, workdir)
+    s = acoss_b200.Serra09(csv, fdir, shortname="g")
+    for i in range(s.N):
+        assert np.array_equal(s.load_features(i), g["ds%d" % i])
+    s.all_pairwise(1, n_cores=4, symmetric=True)
+    assert np.array_equal(np.array(s.Ds["main"]), g["serra_raw"])
+    s.normalize_by_length()
+    assert np.array_equal(np.array(s.Ds["main"]), g["serra_norm"])
+    MR, MRR, MDR, MAP, tops = s.getEvalStatistics("main")
+    assert [MR, MRR, MDR, MAP] == g["serra_eval"].tolist()
+    s.cleanup_memmap()
+
+
+def test_eval_vs_reference_golden(ctx, golden):
+    import torch
+    g = golden("eval_reference.npz")
+    for c in range(int(g["n"])):
+        if int(g["ties%d" % c]):
+            continue
+        D, labels, res = g["D%d" % c], [str(x) for x in g["labels%d" % c]], g["res%d" % c]
+        cl = {}
+        for i, l in enumerate(labels):
+            cl.setdefault(l, []).append(i)
+        cliques = list(cl.values())
+        Ks = np.array([len(x) for x in cliques])
+        idx = np.argsort(-Ks)
+        cliques = [cliques[i] for i in idx]
+        Ks = Ks[idx]
+        order = np.concatenate(cliques).astype(np.int32)
+        csize = np.repeat(Ks, Ks).astype(np.int32)
+        cstart = np.repeat(np.concatenate([[0], np.cumsum(Ks)[:-1]]), Ks).astype(np.int32)
+        Dd = torch.from_numpy(D).cuda()
+        torch.cuda.synchronize()
+        out, ranks = ctx.eval_statistics(Dd.data_ptr(), D.shape[0], order, csize, cstart, [1, 10, 100, 1000])
+        assert out.tolist() == res.tolist()
+
+
+def test_eval_vs_oracle_with_ties_stable(ctx, oracle):
+    import torch
+    rng = np.random.default_rng(3)
+    n = 90
+    labels = ["W%d" % (i // 3) for i in range(60)] + ["S%d" % i for i in range(30)]
+    D = (np.round(rng.random((n, n)) * 6) / 6).astype(np.float32)
+    cl = {}
+    for i, l in enumerate(labels):
+        cl.setdefault(l, []).append(i)
+    exp = oracle.eval_statistics(D, cl, stable=True)
+    cliques = list(cl.values())
+    Ks = np.array([len(x) for x in cliques])
+    idx = np.argsort(-Ks, kind="stable")
+    cliques = [cliques[i] for i in idx]
+    Ks = Ks[idx]
+    order = np.concatenate(cliques).astype(np.int32)
+    csize = np.repeat(Ks, Ks).astype(np.int32)
+    cstart = np.repeat(np.concatenate([[0], np.cumsum(Ks)[:-1]]), Ks).astype(np.int32)
+    Dd = torch.from_numpy(D).cuda()
+    torch.cuda.synchronize()
+    out, _ = ctx.eval_statistics(Dd.data_ptr(), n, order, csize, cstart, [1, 10, 100, 1000])
+    assert out[:4].tolist() == list(exp[:4]) and out[4:].tolist() == exp[4].tolist()
+
+
+def test_benchmark_entry_point(golden, workdir):
+    import acoss_b200
+    g = golden("serra09_small.npz")
+    csv, fdir = _write_golden_dataset(g, workdir)
+    res = acoss_b200.benchmark(csv, fdir, algorithm="Serra09", shortname="bm")
+    assert list(res["main"][:4]) == g["serra_eval"].tolist()
+    assert (workdir / "results_bm_Serra09.csv").exists()
