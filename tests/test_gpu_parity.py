@@ -224,8 +224,10 @@ def test_eval_vs_reference_golden(ctx, golden):
         D, labels, res = g["D%d" % c], [str(x) for x in g["labels%d" % c]], g["res%d" % c]
         cl = {}
         for i, l in enumerate(labels):
-            cl.setdefault(l, []).append(i)
-        cliques = list(cl.values())
+            cl.setdefault(l, set([])).add(i)
+        # list(set) like the reference (algorithm_template.py:220): the within-clique order fixes the
+        # order in which nanmean sums AllMap, hence the last ulp of MAP
+        cliques = [list(c) for c in cl.values()]
         Ks = np.array([len(x) for x in cliques])
         idx = np.argsort(-Ks)
         cliques = [cliques[i] for i in idx]
