@@ -32,7 +32,7 @@ class PairStats(ctypes.Structure):
     _fields_ = [("ms_total", ctypes.c_double), ("ms_prep", ctypes.c_double), ("ms_crp", ctypes.c_double),
                 ("ms_dp", ctypes.c_double), ("dp_cells", ctypes.c_int64), ("crp_cells", ctypes.c_int64),
                 ("crp_bytes", ctypes.c_int64), ("n_launches", ctypes.c_int64), ("n_dp_launches", ctypes.c_int64),
-                ("n_batches", ctypes.c_int64), ("n_exact_cells", ctypes.c_int64)]
+                ("n_batches", ctypes.c_int64), ("n_exact_cells", ctypes.c_int64), ("n_fallback_rows", ctypes.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -51,6 +51,7 @@ SYMBOLS = {
     "acoss_serra09_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_f32p, c_f32p]),
     "acoss_serra09_pairs_dev": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_vp, c_vp]),
     "acoss_get_pair_stats": (ctypes.c_int, [c_vp, ctypes.POINTER(PairStats)]),
+    "acoss_debug_counters": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64)]),
     "acoss_crp_pair": (ctypes.c_int, [c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(CrpParams), c_u8p,
                                       c_i32p, c_i32p, c_f32p, c_f32p, c_i32p]),
     "acoss_cover_similarity_from_crp": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, ctypes.c_int32,
@@ -190,6 +191,11 @@ class Context(object):
         s = PairStats()
         self._ck(self.lib.acoss_get_pair_stats(self.h, ctypes.byref(s)))
         return s.as_dict()
+
+    def debug_counters(self):
+        out = (ctypes.c_uint64 * 16)()
+        self._ck(self.lib.acoss_debug_counters(self.h, out))
+        return [int(x) for x in out]
 
     def crp_pair(self, q, r, params=None):
         """(crp uint8 (M,N), thr_q, thr_r, oti) of one uploaded pair (test hook)."""

@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "kernels_prep.cuh"
 #include "kernels_crp.cuh"
+#include "kernels_crp_band.cuh"
 #include "kernels_dp.cuh"
 #include "kernels_eval.cuh"
 
@@ -49,9 +50,10 @@ struct acoss_ctx {
     std::vector<int64_t> h_sd_off;    // self-dot table offsets
     DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma;
     // per-call scratch
-    DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2;
+    DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2, d_counters;
     cudaEvent_t ev[8] = {};
     acoss_pair_stats stats = {};
+    unsigned long long h_counters[16] = {};
     size_t crp_budget = (size_t)8 << 30;
     int max_smem = 0;
     int num_sms = ACOSS_NUM_SMS;
@@ -104,7 +106,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
                       &ctx->d_gchroma, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
-                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2};
+                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);

@@ -1,0 +1,578 @@
+// kernels_crp_band.cuh -- fast bit-exact CRP: approximate cross-similarity + rigorous
+// error band + exact re-check (sm_100a).  Same contract as kernels_crp.cuh (which stays
+// as the always-exact reference path and as the fallback for m != 9 or tau != 1).
+//
+// Why it is exact.  Let rho_o be the oracle's radicand (fp32, sequential 108-term sums,
+// no FMA) and rho~ the value computed here.  Forward error
+// analysis (u = 2^-24; all terms relative to xx + yy, the squared norms of the two
+// embedded rows; |x.y| <= (xx+yy)/2):
+//     oracle:  |rho_o - rho*| <= 220 u (xx + yy)   (three 108-term chains + 2 roundings)
+//     here:    |rho~  - rho*| <=  42 u (xx + yy)   (12-term FMA chains, 9-term tree)
+//     =>  |rho~ - rho_o| <= 262 u (xx + yy)  <  EPS_REL (xx + yy),   EPS_REL = 2^-15.
+// D = sqrt_rn(max(rho_o, 0)) is monotone in rho_o, so
+//   * order statistics: the exact k-th smallest lies within E of the approximate k-th
+//     smallest; every element whose rho~ is within 2E of it is recomputed exactly (the
+//     oracle's op order) and the order statistic is selected among those exact values;
+//   * binarisation: D <= eps is decided by rho~ against T = eps*eps when
+//     |rho~ - T| > E + 8uT, otherwise the cell is recomputed exactly.
+// Everything that is written out (thresholds, CRP bits) therefore equals the oracle's.
+//
+// How the approximation is computed ("sliding Gram").  With m = 9, tau = 1 the squared
+// embedded distance is a diagonal sum of squared 12-d frame distances,
+//     rho*(i, j) = sum_{k<9} G2[i+k][j+k],   G2[a][b] = |f_a|^2 + |f_b|^2 - 2 <f_a, f_b>,
+// i.e. 12 FMA per G2 entry shared by 9 cells instead of 108 MACs per cell.
+//   phase 1: a thread owns one G2 column b (B frame in registers) and streams the strip's
+//            24 A frames from shared memory (broadcast LDS.128, pre-scaled by -2); G2 goes to
+//            shared memory in a skewed layout Gs[a][(b - a) mod TW] so that
+//   phase 2: a thread owns a diagonal delta = b - a, reads its 24 G2 values conflict-free,
+//            forms the 16 window sums with a 4-level tree in registers and writes rho~ into
+//            the strip buffer V (fp32, shared memory).
+#pragma once
+#include "common.cuh"
+#include "kernels_crp.cuh"
+
+#define BAND_RS 16                    // strip rows
+#define BAND_GR (BAND_RS + 8)         // G rows per strip
+#define BAND_TW 512                   // G columns per tile
+#define BAND_ND (BAND_TW - BAND_GR + 1)   // complete diagonals per tile (489)
+#define BAND_THREADS 512
+#define BAND_WARPS (BAND_THREADS / 32)
+#define BAND_LMAX 256                 // per-warp candidate list capacity
+#define BAND_LPL (BAND_LMAX / 32)     // list entries per lane
+#define BAND_EPS_REL 3.0517578125e-05f    // 2^-15
+#define BAND_SAMPLE 512
+#define BAND_SPL (BAND_SAMPLE / 32)
+#define BAND_MIN_NB 128               // below this every row takes the exact-row path
+#define BAND_AFS 16                   // floats per staged A frame: 12 bins (x -2), |f|^2, pad
+#define BAND_WSCR 768                 // per-warp scratch words inside Gs: lidx[256] lval[256] stage[256]
+#define BAND_SMEM_FIXED (BAND_GR * BAND_AFS + 3 * BAND_RS + 32 + BAND_GR * BAND_TW)   // + 17 * NBpad floats
+
+// exact distance of (query embedded row u, reference embedded row v): the oracle's op order
+__device__ __noinline__ float exact_dist(const float* __restrict__ frames, const PairDesc& pd, int rot,
+                                         const float* __restrict__ selfdot, int u, int v)
+{
+    const float* qf = frames + (pd.q_frame_off + u) * ACOSS_NBINS;
+    const float* rf = frames + (pd.r_frame_off + v) * ACOSS_NBINS;
+    float acc = 0.0f;
+    for (int s = 0; s < 9; ++s) {
+#pragma unroll
+        for (int c = 0; c < ACOSS_NBINS; ++c)
+            acc = xadd(acc, xmul(qf[s * ACOSS_NBINS + c], rf[s * ACOSS_NBINS + rot_src(c, rot)]));
+    }
+    const float xx = selfdot[pd.q_sd_off + u];
+    const float yy = selfdot[pd.r_sd_off + (int64_t)rot * pd.N + v];
+    float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
+    if (item < 0.0f) item = 0.0f;
+    return __fsqrt_rn(item);
+}
+
+// order-preserving map float -> uint32 for values of either sign (rho~ can be slightly negative)
+__device__ __forceinline__ uint32_t fkey(float f)
+{
+    uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float fkey_inv(uint32_t k)
+{
+    uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+    return __uint_as_float(b);
+}
+
+// counters: [0] exact cells  [1] fallback rows  [2..5] cycles (thread 0): stage, tiles, select, binarise
+//           [7] tasks  [8..12] cycles (warp 0): pivots, count+list, list select, exact, rank  [13] rows profiled
+//
+// Shared-memory carve-up (floats):
+//   Afr [24*16]  A frames of the strip: -2 * bins (pre-rotated), |f|^2, pad
+//   xxA [16] thA [16] flag[16] red[32]
+//   yyB [NBpad]  exact self dots of all side-B rows; later: lower band edges of the column thresholds
+//   Gs  [24*512] skewed G2 tile; later: per-warp scratch; later: upper band edges + ambiguity list
+//   V   [16*NBpad]
+__global__ void __launch_bounds__(BAND_THREADS, 1)
+crp_strip_band_kernel(const PairDesc* __restrict__ descs,
+                      const StripTask* __restrict__ tasks, int n_tasks,
+                      const float* __restrict__ frames,
+                      const float* __restrict__ selfdot,
+                      float* __restrict__ thr, uint8_t* __restrict__ crp,
+                      int side_a_is_query, float qf, int NBpad,
+                      unsigned long long* __restrict__ counters)
+{
+    extern __shared__ __align__(16) float smem[];
+    float* Afr = smem;
+    float* xxA = Afr + BAND_GR * BAND_AFS;
+    float* thA = xxA + BAND_RS;
+    int* flag = reinterpret_cast<int*>(thA + BAND_RS);
+    float* red = reinterpret_cast<float*>(flag + BAND_RS);          // 32 words
+    float* yyB = red + 32;
+    float* Gs = yyB + NBpad;
+    float* V = Gs + BAND_GR * BAND_TW;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long n_exact = 0;
+
+    for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
+        const StripTask tk = tasks[task];
+        const PairDesc pd = descs[tk.pair];
+        const int rot = pd.oti % ACOSS_NBINS;
+        const int NB = side_a_is_query ? pd.N : pd.M;
+        const int na_frames = side_a_is_query ? pd.nq : pd.nr;
+        const int nb_frames = side_a_is_query ? pd.nr : pd.nq;
+        const int64_t a_f0 = side_a_is_query ? pd.q_frame_off : pd.r_frame_off;
+        const int64_t b_f0 = side_a_is_query ? pd.r_frame_off : pd.q_frame_off;
+        // <roll(ref, rot), query>: the B frames stay unrotated in registers; the A frames are staged
+        // pre-rotated: by +rot when A is the reference, by -rot when A is the query.
+        const int rot_a = side_a_is_query ? (ACOSS_NBINS - rot) % ACOSS_NBINS : rot;
+        const float* sdA = selfdot + (side_a_is_query ? pd.q_sd_off : pd.r_sd_off + (int64_t)rot * pd.N);
+        const float* sdB = selfdot + (side_a_is_query ? pd.r_sd_off + (int64_t)rot * pd.N : pd.q_sd_off);
+
+        __syncthreads();
+        long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0;
+        if (tid == 0) ph0 = clock64();
+        // ---- stage A frames (x -2, with |f|^2), self dots, flags
+        if (tid < BAND_GR * BAND_AFS) {
+            const int a = tid / BAND_AFS, c = tid - a * BAND_AFS;
+            const int f = tk.row0 + a;
+            float v = 0.0f;
+            if (f < na_frames) {
+                const float* fp = frames + (a_f0 + f) * ACOSS_NBINS;
+                if (c < ACOSS_NBINS) v = -2.0f * fp[rot_src(c, rot_a)];
+                else if (c == ACOSS_NBINS) {
+#pragma unroll
+                    for (int q = 0; q < ACOSS_NBINS; ++q) v = fmaf(fp[q], fp[q], v);
+                }
+            }
+            Afr[tid] = v;
+        }
+        if (tid < BAND_RS) { xxA[tid] = (tid < tk.nrows) ? sdA[tk.row0 + tid] : 0.0f; flag[tid] = 0; }
+        float ymax = 0.0f;
+        for (int j = tid; j < NB; j += BAND_THREADS) { float y = sdB[j]; yyB[j] = y; ymax = fmaxf(ymax, y); }
+        for (int o = 16; o > 0; o >>= 1) ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+        if (lane == 0) red[warp] = ymax;
+        __syncthreads();
+        ymax = red[0];
+#pragma unroll
+        for (int w = 1; w < BAND_WARPS; ++w) ymax = fmaxf(ymax, red[w]);
+        float xmax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < BAND_RS; ++i) xmax = fmaxf(xmax, xxA[i]);
+        const float E = BAND_EPS_REL * (xmax + ymax);     // one bound for the whole strip (conservative)
+
+        const bool tiny = NB < BAND_MIN_NB;
+        if (tid == 0) ph1 = clock64();
+        if (!tiny) {
+            // ---- approximate radicands of the strip: sliding Gram over column tiles
+            const bool full_rows = (tk.nrows == BAND_RS);
+            for (int b0 = -(BAND_RS - 1); b0 < NB; b0 += BAND_ND) {
+                // phase 1: thread (h, t) = (tid >> 8, tid & 255) owns G2 columns b0 + t and b0 + t + 256 for the
+                // A rows [12 h, 12 h + 12): every broadcast A load feeds two columns
+                {
+                    const int t = tid & 255, a_base = (tid >> 8) * (BAND_GR / 2);
+                    float B0[ACOSS_NBINS], B1[ACOSS_NBINS];
+                    const int c0 = b0 + t, c1 = c0 + 256;
+                    const bool v0 = (c0 >= 0 && c0 < nb_frames), v1 = (c1 >= 0 && c1 < nb_frames);
+                    const float4* p0 = reinterpret_cast<const float4*>(frames + (b_f0 + (v0 ? c0 : 0)) * ACOSS_NBINS);
+                    const float4* p1 = reinterpret_cast<const float4*>(frames + (b_f0 + (v1 ? c1 : 0)) * ACOSS_NBINS);
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) {
+                        const float4 x = v0 ? __ldg(p0 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        const float4 y = v1 ? __ldg(p1 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        B0[4 * q] = x.x; B0[4 * q + 1] = x.y; B0[4 * q + 2] = x.z; B0[4 * q + 3] = x.w;
+                        B1[4 * q] = y.x; B1[4 * q + 1] = y.y; B1[4 * q + 2] = y.z; B1[4 * q + 3] = y.w;
+                    }
+                    float ff0 = 0.f, ff1 = 0.f;
+#pragma unroll
+                    for (int q = 0; q < ACOSS_NBINS; ++q) { ff0 = fmaf(B0[q], B0[q], ff0); ff1 = fmaf(B1[q], B1[q], ff1); }
+#pragma unroll
+                    for (int aa = 0; aa < BAND_GR / 2; ++aa) {
+                        const int a = a_base + aa;
+                        const float4* ap = reinterpret_cast<const float4*>(Afr + a * BAND_AFS);
+                        const float4 x0 = ap[0], x1 = ap[1], x2 = ap[2], x3 = ap[3];
+                        float g0 = x3.x + ff0, g1 = x3.x + ff1;       // |f_a|^2 + |f_b|^2
+                        g0 = fmaf(x0.x, B0[0], g0); g1 = fmaf(x0.x, B1[0], g1);
+                        g0 = fmaf(x0.y, B0[1], g0); g1 = fmaf(x0.y, B1[1], g1);
+                        g0 = fmaf(x0.z, B0[2], g0); g1 = fmaf(x0.z, B1[2], g1);
+                        g0 = fmaf(x0.w, B0[3], g0); g1 = fmaf(x0.w, B1[3], g1);
+                        g0 = fmaf(x1.x, B0[4], g0); g1 = fmaf(x1.x, B1[4], g1);
+                        g0 = fmaf(x1.y, B0[5], g0); g1 = fmaf(x1.y, B1[5], g1);
+                        g0 = fmaf(x1.z, B0[6], g0); g1 = fmaf(x1.z, B1[6], g1);
+                        g0 = fmaf(x1.w, B0[7], g0); g1 = fmaf(x1.w, B1[7], g1);
+                        g0 = fmaf(x2.x, B0[8], g0); g1 = fmaf(x2.x, B1[8], g1);
+                        g0 = fmaf(x2.y, B0[9], g0); g1 = fmaf(x2.y, B1[9], g1);
+                        g0 = fmaf(x2.z, B0[10], g0); g1 = fmaf(x2.z, B1[10], g1);
+                        g0 = fmaf(x2.w, B0[11], g0); g1 = fmaf(x2.w, B1[11], g1);
+                        // Gs[a][(col - a) mod 512], col = t and t + 256
+                        Gs[a * BAND_TW + ((t - a) & (BAND_TW - 1))] = g0;
+                        Gs[a * BAND_TW + ((t + 256 - a) & (BAND_TW - 1))] = g1;
+                    }
+                }
+                __syncthreads();
+                // phase 2: diagonal delta = tid
+                if (tid < BAND_ND) {
+                    float g[BAND_GR];
+#pragma unroll
+                    for (int a = 0; a < BAND_GR; ++a) g[a] = Gs[a * BAND_TW + tid];
+                    float t2[BAND_GR - 1], t4[BAND_GR - 3], t8[BAND_GR - 7];
+#pragma unroll
+                    for (int a = 0; a < BAND_GR - 1; ++a) t2[a] = g[a] + g[a + 1];
+#pragma unroll
+                    for (int a = 0; a < BAND_GR - 3; ++a) t4[a] = t2[a] + t2[a + 2];
+#pragma unroll
+                    for (int a = 0; a < BAND_GR - 7; ++a) t8[a] = t4[a] + t4[a + 4];
+                    const int jb = b0 + tid;                       // column of row 0 on this diagonal
+                    float* vp = V + jb;
+                    if (full_rows && jb >= 0 && jb + BAND_RS <= NB) {
+#pragma unroll
+                        for (int i = 0; i < BAND_RS; ++i) vp[i * (NBpad + 1)] = t8[i] + g[i + 8];
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < BAND_RS; ++i) {
+                            const int j = jb + i;
+                            if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[i] + g[i + 8];
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        if (tid == 0) ph2 = clock64();
+
+        // ---- per-row percentile thresholds: one warp per row.  Per-warp scratch inside Gs.
+        const PercentileRank pr = percentile_rank(NB, qf);
+        float* thr_out = thr + (side_a_is_query ? pd.thr_q_off : pd.thr_r_off);
+        if (warp < tk.nrows) {
+            const int r = warp;
+            int* lidx = reinterpret_cast<int*>(Gs) + warp * BAND_WSCR;
+            float* lval = reinterpret_cast<float*>(lidx + BAND_LMAX);
+            float* stage = lval + BAND_LMAX;
+            float* vr = V + r * NBpad;
+            const int u_or_v = tk.row0 + r;     // the strip row's index on side A
+            bool exact_row = tiny;
+            float v_lo = 0.f, v_hi = 0.f;
+            const bool prof = (warp == 0 && lane == 0);
+            long long tc0 = 0, tc1 = 0, tc2 = 0, tc3 = 0, tc4 = 0;
+            if (!exact_row) {
+                if (prof) tc0 = clock64();
+                // (a) sample (registers) -> two pivots bracketing the wanted order statistics
+                float sm[BAND_SPL];
+                float smin = INFINITY, smax = -INFINITY;
+#pragma unroll
+                for (int q = 0; q < BAND_SPL; ++q) {
+                    const int pos = (int)(((long long)(q * 32 + lane) * NB) >> 9);     // / BAND_SAMPLE
+                    sm[q] = vr[pos];
+                    smin = fminf(smin, sm[q]); smax = fmaxf(smax, sm[q]);
+                }
+                for (int o = 16; o > 0; o >>= 1) {
+                    smin = fminf(smin, __shfl_xor_sync(0xffffffffu, smin, o));
+                    smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, o));
+                }
+                const float frac = ((float)pr.lo + 0.5f) / (float)NB;
+                const float rs = frac * (float)BAND_SAMPLE;
+                const float sg = sqrtf(fmaxf(rs * (1.0f - frac), 1.0f));
+                bool ok = false;
+                int c_a = 0, c_ab = 0;
+                float pa = -INFINITY, pb = INFINITY;
+                uint32_t key[BAND_LPL];
+                for (int attempt = 0; attempt < 2 && !ok; ++attempt) {
+                    const float ns = attempt == 0 ? 2.0f : 4.0f;
+                    const int r_lo = (int)floorf(rs - ns * sg) - 1;       // sample ranks of the two pivots
+                    const int r_hi = (int)ceilf(rs + ns * sg) + 1;
+                    pa = -INFINITY; pb = INFINITY;
+                    if (r_lo >= 0 || r_hi < BAND_SAMPLE) {
+                        // value bisection on the sample, both pivots at once, counts packed in one REDUX
+                        float la = smin, ha = smax, lb = smin, hb = smax;
+                        for (int it = 0; it < 8; ++it) {
+                            const float ma = 0.5f * (la + ha), mb = 0.5f * (lb + hb);
+                            int cc = 0;
+#pragma unroll
+                            for (int q = 0; q < BAND_SPL; ++q) cc += (sm[q] < ma ? 1 : 0) + (sm[q] < mb ? 65536 : 0);
+                            cc = __reduce_add_sync(0xffffffffu, cc);
+                            if ((cc & 0xffff) <= r_lo) la = ma; else ha = ma;      // want #(< pa) <= r_lo
+                            if ((cc >> 16) <= r_hi) lb = mb; else hb = mb;          // want #(< pb) >  r_hi
+                        }
+                        if (r_lo >= 0) pa = la;
+                        if (r_hi < BAND_SAMPLE) pb = hb;
+                    }
+                    if (prof && attempt == 0) tc1 = clock64();
+                    // (b) pass A: per-lane counts, 8 loads in flight
+                    int ca_l = 0, cb_l = 0;
+                    int j = lane;
+                    for (; j + 7 * 32 < NB; j += 8 * 32) {
+                        float x[8];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) x[q] = vr[j + q * 32];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) { ca_l += (x[q] < pa); cb_l += (x[q] < pb); }
+                    }
+                    for (; j < NB; j += 32) { const float x = vr[j]; ca_l += (x < pa); cb_l += (x < pb); }
+                    const int cab_l = cb_l - ca_l;
+                    const int pk = __reduce_add_sync(0xffffffffu, ca_l | (cab_l << 16));
+                    c_a = pk & 0xffff; c_ab = pk >> 16;
+                    ok = (c_a <= pr.lo) && (c_a + c_ab >= pr.hi + 1) && (c_ab <= BAND_LMAX);
+                    if (!ok) continue;
+                    int incl = cab_l;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                    // pass B: every lane writes its in-band elements at its private offset
+                    int off = incl - cab_l;
+                    j = lane;
+                    for (; j + 7 * 32 < NB; j += 8 * 32) {
+                        float x[8];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) x[q] = vr[j + q * 32];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            if (x[q] >= pa && x[q] < pb) { lidx[off] = j + q * 32; lval[off] = x[q]; ++off; }
+                    }
+                    for (; j < NB; j += 32) { const float x = vr[j]; if (x >= pa && x < pb) { lidx[off] = j; lval[off] = x; ++off; } }
+                    __syncwarp();
+                }
+                if (prof) tc2 = clock64();
+                float t_lo = 0.f, t_hi = 0.f;
+                if (ok) {
+                    // (c) approximate order statistics inside the list: keys in registers, bitwise bisection
+                    //     restricted to the bits in which the list's keys can differ
+                    uint32_t kmin = 0xffffffffu, kmax = 0u;
+#pragma unroll
+                    for (int q = 0; q < BAND_LPL; ++q) {
+                        const int e = q * 32 + lane;
+                        key[q] = (e < c_ab) ? fkey(lval[e]) : 0xffffffffu;
+                        if (e < c_ab) { kmin = min(kmin, key[q]); kmax = max(kmax, key[q]); }
+                    }
+                    kmin = __reduce_min_sync(0xffffffffu, kmin);
+                    kmax = __reduce_max_sync(0xffffffffu, kmax);
+                    const uint32_t dif = kmin ^ kmax;
+                    const int top = dif ? (31 - __clz(dif)) : -1;
+                    const int kk = pr.lo - c_a;
+                    uint32_t ans = (top >= 31) ? 0u : (kmin & ~(((top >= 0) ? (2u << top) : 1u) - 1u));
+                    for (int bit = top; bit >= 0; --bit) {
+                        const uint32_t cand = ans | (1u << bit);
+                        int cnt = 0;
+#pragma unroll
+                        for (int q = 0; q < BAND_LPL; ++q) cnt += (key[q] < cand);
+                        cnt = __reduce_add_sync(0xffffffffu, cnt);
+                        if (cnt <= kk) ans = cand;
+                    }
+                    int cle = 0;
+                    uint32_t mgt = 0xffffffffu;
+#pragma unroll
+                    for (int q = 0; q < BAND_LPL; ++q) {
+                        cle += (key[q] <= ans);
+                        if (key[q] > ans && key[q] < mgt) mgt = key[q];
+                    }
+                    cle = __reduce_add_sync(0xffffffffu, cle);
+                    mgt = __reduce_min_sync(0xffffffffu, mgt);
+                    t_lo = fkey_inv(ans);
+                    t_hi = (pr.hi == pr.lo || cle >= kk + 2) ? t_lo : (mgt == 0xffffffffu ? INFINITY : fkey_inv(mgt));
+                    // the candidate window must lie strictly inside the list's value range
+                    ok = (t_lo - 2.0f * E > pa || pa == -INFINITY) && (t_hi + 2.0f * E < pb || pb == INFINITY) && (t_hi < INFINITY);
+                }
+                if (prof) tc3 = clock64();
+                if (ok) {
+                    // (d) gather every list element within 2E of the approximate order statistics
+                    const uint32_t kw_lo = fkey(t_lo - 2.0f * E), kw_hi = fkey(t_hi + 2.0f * E);
+                    int n_below = c_a, n_c = 0;
+#pragma unroll
+                    for (int q = 0; q < BAND_LPL; ++q) {
+                        const int e = q * 32 + lane;
+                        const bool valid = e < c_ab;
+                        const bool below = valid && key[q] < kw_lo;
+                        const bool cand = valid && !below && key[q] <= kw_hi;
+                        const int jj = valid ? lidx[e] : 0;
+                        n_below += __popc(__ballot_sync(0xffffffffu, below));
+                        const unsigned mc = __ballot_sync(0xffffffffu, cand);
+                        __syncwarp();
+                        // compact candidate columns to the front of lidx (slot <= e: nothing unread is overwritten)
+                        if (cand) lidx[n_c + __popc(mc & ((1u << lane) - 1u))] = jj;
+                        n_c += __popc(mc);
+                        __syncwarp();
+                    }
+                    const int kx = pr.lo - n_below;
+                    if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) ok = false;
+                    else {
+                        // exact values, two candidates per round.  Both operands are staged in the ORACLE's
+                        // element order (bin c of the oracle = staged bin (st + c) mod 12, see the staging rotation
+                        // above): the A row (108 floats, un-scaled) into lval (its keys live in registers by now),
+                        // the candidates' 9 B frames into `stage`; lane c then runs the 108-term chain.
+                        const int st = side_a_is_query ? rot_a : 0;
+                        for (int e = lane; e < 108; e += 32) {
+                            const int s_ = e / ACOSS_NBINS, c = e - s_ * ACOSS_NBINS;
+                            int cb = st + c; if (cb >= ACOSS_NBINS) cb -= ACOSS_NBINS;
+                            lval[e] = -0.5f * Afr[(r + s_) * BAND_AFS + cb];       // exact: staged as -2 * a
+                        }
+                        float dex = INFINITY;
+                        for (int c0 = 0; c0 < n_c; c0 += 2) {
+                            const int nc2 = min(2, n_c - c0);
+                            for (int e = lane; e < nc2 * 108; e += 32) {
+                                const int ci = e / 108, w = e - ci * 108;
+                                const int s_ = w / ACOSS_NBINS, c = w - s_ * ACOSS_NBINS;
+                                int cb = st + c; if (cb >= ACOSS_NBINS) cb -= ACOSS_NBINS;
+                                stage[e] = __ldg(frames + (b_f0 + lidx[c0 + ci] + s_) * ACOSS_NBINS + cb);
+                            }
+                            __syncwarp();
+                            if (lane >= c0 && lane < c0 + nc2) {
+                                const float4* bs = reinterpret_cast<const float4*>(stage + (lane - c0) * 108);
+                                const float4* as = reinterpret_cast<const float4*>(lval);
+                                float acc = 0.0f;
+#pragma unroll 9
+                                for (int q = 0; q < 27; ++q) {
+                                    const float4 av = as[q], bv = bs[q];
+                                    acc = xadd(acc, xmul(av.x, bv.x));
+                                    acc = xadd(acc, xmul(av.y, bv.y));
+                                    acc = xadd(acc, xmul(av.z, bv.z));
+                                    acc = xadd(acc, xmul(av.w, bv.w));
+                                }
+                                const int jj = lidx[lane];
+                                const float sa = xxA[r], sb = yyB[jj];
+                                const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
+                                float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
+                                if (item < 0.0f) item = 0.0f;
+                                dex = __fsqrt_rn(item);
+                                ++n_exact;
+                            }
+                            __syncwarp();
+                        }
+                        if (prof) tc4 = clock64();
+                        // rank by comparison through shuffles (ties by lane), pick ranks kx and kx+1
+                        int rank = 0;
+                        for (int b = 0; b < n_c; ++b) {
+                            const float db = __shfl_sync(0xffffffffu, dex, b);
+                            rank += (db < dex) || (db == dex && b < lane);
+                        }
+                        const unsigned m0 = __ballot_sync(0xffffffffu, lane < n_c && rank == kx);
+                        const unsigned m1 = __ballot_sync(0xffffffffu, lane < n_c && rank == kx + 1);
+                        v_lo = __shfl_sync(0xffffffffu, dex, __ffs(m0) - 1);
+                        v_hi = m1 ? __shfl_sync(0xffffffffu, dex, __ffs(m1) - 1) : v_lo;
+                        if (prof) {
+                            const long long tc5 = clock64();
+                            atomicAdd(&counters[8], (unsigned long long)(tc1 - tc0));
+                            atomicAdd(&counters[9], (unsigned long long)(tc2 - tc1));
+                            atomicAdd(&counters[10], (unsigned long long)(tc3 - tc2));
+                            atomicAdd(&counters[11], (unsigned long long)(tc4 - tc3));
+                            atomicAdd(&counters[12], (unsigned long long)(tc5 - tc4));
+                            atomicAdd(&counters[13], 1ull);
+                        }
+                    }
+                }
+                if (!ok) exact_row = true;
+            }
+            if (exact_row) {
+                // fallback (tiny rows, heavy ties, list overflow): the whole row exactly, as in kernels_crp.cuh
+                for (int j = lane; j < NB; j += 32) {
+                    vr[j] = side_a_is_query ? exact_dist(frames, pd, rot, selfdot, u_or_v, j)
+                                            : exact_dist(frames, pd, rot, selfdot, j, u_or_v);
+                }
+                n_exact += (NB + 31 - lane) / 32;
+                __syncwarp();
+                v_lo = warp_select_pair(vr, NB, pr.lo, lane, v_hi);
+                if (lane == 0) { flag[r] = 1; if (!tiny) atomicAdd(&counters[1], 1ull); }
+            }
+            const float t = percentile_combine(pr, v_lo, v_hi);
+            if (lane == 0) { thA[r] = t; thr_out[tk.row0 + r] = t; }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            ph3 = clock64();
+            atomicAdd(&counters[2], (unsigned long long)(ph1 - ph0));
+            atomicAdd(&counters[3], (unsigned long long)(ph2 - ph1));
+            atomicAdd(&counters[4], (unsigned long long)(ph3 - ph2));
+            atomicAdd(&counters[7], 1ull);
+        }
+        if (!side_a_is_query) continue;
+
+        // ---- pass 2: binarise.  Per column the band edges of T_r = thr_r^2 go to shared memory once
+        //      (lo in yyB, hi in Gs); per cell: sure-in  <=> rho~ < min(lo_q, lo_r[j]),
+        //      sure-out <=> rho~ > min(hi_q, hi_r[j]); anything else is decided exactly afterwards.
+        const float* thB = thr + pd.thr_r_off;
+        float* lo_r = yyB;
+        float* hi_r = Gs;
+        int* amb = reinterpret_cast<int*>(Gs + NBpad);
+        int* amb_cnt = reinterpret_cast<int*>(red + 24);
+        const int amb_cap = BAND_GR * BAND_TW - NBpad;
+        if (tid == 0) *amb_cnt = 0;
+        for (int j = tid; j < NBpad; j += BAND_THREADS) {
+            float lo = -INFINITY, hi = -INFINITY;          // padding columns: never "in", always "out"
+            if (j < NB) {
+                const float tb = __ldg(thB + j);
+                const float Tr = xmul(tb, tb);
+                const float mr = E + Tr * 4.76837158203125e-07f;        // E + 8uT
+                lo = Tr - mr; hi = Tr + mr;
+            }
+            lo_r[j] = lo; hi_r[j] = hi;
+        }
+        __syncthreads();
+        const int words = pd.pitch >> 2;
+        // per-row band edges of T_q = thr_q^2 (lo in red[0..15], hi in thA-adjacent scratch: reuse xxA, no longer needed)
+        if (tid < BAND_RS) {
+            const float ta = thA[tid];
+            const float Tq = xmul(ta, ta);
+            const float mq = E + Tq * 4.76837158203125e-07f;
+            red[tid] = Tq - mq;
+            xxA[tid] = Tq + mq;
+        }
+        __syncthreads();
+        const int items = tk.nrows * words;
+        for (int it = tid; it < items; it += BAND_THREADS) {
+            const int r = it / words, w = it - r * words;
+            uint32_t* out = reinterpret_cast<uint32_t*>(crp + pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch);
+            const float* vr = V + r * NBpad;
+            uint32_t word = (CRP_DELTA_ZERO) | (CRP_DELTA_ZERO << 8) | (CRP_DELTA_ZERO << 16) | (CRP_DELTA_ZERO << 24);
+            const int j0 = w * 4;
+            if (j0 < NBpad) {
+                const float4 x4 = *reinterpret_cast<const float4*>(vr + j0);
+                const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+                if (flag[r] != 0) {
+                    const float ta = thA[r];
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        const int j = j0 + b;
+                        if (j < NB && xs[b] <= ta && xs[b] <= __ldg(thB + j))
+                            word ^= (CRP_DELTA_ZERO ^ CRP_DELTA_ONE) << (8 * b);
+                    }
+                } else {
+                    const float lo_q = red[r], hi_q = xxA[r];
+                    const float4 l4 = *reinterpret_cast<const float4*>(lo_r + j0);
+                    const float4 h4 = *reinterpret_cast<const float4*>(hi_r + j0);
+                    const float ls[4] = {l4.x, l4.y, l4.z, l4.w};
+                    const float hs[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        const float lo = fminf(lo_q, ls[b]), hi = fminf(hi_q, hs[b]);
+                        if (xs[b] < lo) word ^= (CRP_DELTA_ZERO ^ CRP_DELTA_ONE) << (8 * b);
+                        else if (!(xs[b] > hi) && j0 + b < NB) {
+                            const int slot = atomicAdd(amb_cnt, 1);
+                            if (slot < amb_cap) amb[slot] = (r << 24) | (j0 + b);
+                        }
+                    }
+                }
+            }
+            out[w] = word;
+        }
+        __syncthreads();
+        {
+            const int na = *amb_cnt;
+            if (na > amb_cap) {
+                // pathological (massive exact ties): decide every non-exact row of the strip exactly
+                for (int r = 0; r < tk.nrows; ++r) {
+                    if (flag[r]) continue;
+                    uint8_t* out = crp + pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch;
+                    for (int j = tid; j < NB; j += BAND_THREADS) {
+                        const float dv = exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j);
+                        ++n_exact;
+                        out[j] = (dv <= thA[r] && dv <= thB[j]) ? (uint8_t)CRP_DELTA_ONE : (uint8_t)CRP_DELTA_ZERO;
+                    }
+                }
+            } else {
+                for (int e = tid; e < na; e += BAND_THREADS) {
+                    const int code = amb[e];
+                    const int r = code >> 24, j = code & 0xFFFFFF;
+                    const float dv = exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j);
+                    ++n_exact;
+                    if (dv <= thA[r] && dv <= thB[j])
+                        crp[pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch + j] = (uint8_t)CRP_DELTA_ONE;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) atomicAdd(&counters[5], (unsigned long long)(clock64() - ph3));
+    }
+    for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o);
+    if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
+}

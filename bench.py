@@ -332,7 +332,9 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roofline, "roofline_kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(n_launch), "clocks": clocks,
             "eval": {"MR": ev[0], "MRR": ev[1], "MDR": ev[2], "MAP": ev[3], "Top-1": ev[4]},
-            "batches_per_step": int(st["n_batches"])}
+            "batches_per_step": int(st["n_batches"]), "crp_mode": args.crp_mode,
+            "debug_counters": ctx.debug_counters(),
+            "exact_cell_fraction": st["n_exact_cells"] / max(1, 2 * st["crp_cells"]), "fallback_rows": int(st["n_fallback_rows"])}
     print(json.dumps(line))
 
 

@@ -67,7 +67,8 @@ typedef struct acoss_pair_stats {
     int64_t n_launches;      /* kernels launched by this call                  */
     int64_t n_dp_launches;
     int64_t n_batches;
-    int64_t n_exact_cells;   /* cells recomputed exactly (band mode)           */
+    int64_t n_exact_cells;   /* cells computed with the oracle's exact op order */
+    int64_t n_fallback_rows; /* band mode: rows that fell back to the exact-row path */
 } acoss_pair_stats;
 
 /* ---- context ------------------------------------------------------------- */
@@ -126,6 +127,10 @@ int acoss_serra09_pairs_dev(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n
 
 /* Accounting of the last acoss_serra09_pairs* call (synchronises the stream). */
 int acoss_get_pair_stats(acoss_ctx *ctx, acoss_pair_stats *out);
+
+/* Profiling aid: raw device counters of the last pair call (clock64 cycles per phase of the
+ * CRP strip kernel summed over CTAs; layout documented in kernels_crp_band.cuh). */
+int acoss_debug_counters(acoss_ctx *ctx, uint64_t *out16);
 
 /* Test hook: the binary cross-recurrence plot of ONE pair, (M, N) uint8 0/1,
  * rows = query frames (ChromaCrossSimilarity output, rqa_serra09.py:66).

@@ -133,6 +133,60 @@ def test_crp_exact_ties_duplicate_frames(ctx, oracle):
     assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]) and np.array_equal(R, Ro)
 
 
+@pytest.mark.parametrize("mode", [1, 2])
+def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
+    """exact-everywhere strips (mode 1) and approximate + band + exact re-check (mode 2) give the
+    same bits as the oracle; sizes large enough for the band path (NB >= 128), ragged tiles."""
+    rng = np.random.default_rng(500 + mode)
+    lens = [137, 200, 333, 498, 512, 523, 700, 1009, 150]
+    tracks = _tracks(rng, lens, noise=0.1)
+    ctx.upload_tracks(tracks)
+    for kappa in (0.095, 0.3):
+        prm = ctx.params(kappa=kappa, crp_mode=mode)
+        for (a, b) in [(0, 1), (2, 3), (4, 5), (6, 7), (7, 2), (8, 6), (3, 3)]:
+            R, tq, tr, o = ctx.crp_pair(a, b, prm)
+            Ro, info = oracle.chroma_cross_similarity(tracks[a], tracks[b], kappa=kappa, full=True)
+            assert o == info["oti"]
+            assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]), (mode, a, b)
+            assert np.array_equal(R, Ro), (mode, a, b)
+
+
+def test_crp_band_degenerate_inputs(ctx, oracle):
+    """constant / silent / duplicated frames: massive exact ties force the band kernel's fallbacks"""
+    rng = np.random.default_rng(12)
+    a = rng.random((40, 12)).astype(np.float32)
+    const = np.tile(rng.random((1, 12)).astype(np.float32), (300, 1))
+    silent = np.zeros((260, 12), np.float32)
+    dup = np.concatenate([a] * 8, 0)
+    half = np.concatenate([const[:150], rng.random((200, 12)).astype(np.float32)], 0)
+    tracks = [const, silent, dup, half, _tracks(rng, [400])[0]]
+    ctx.upload_tracks(tracks)
+    prm = ctx.params(crp_mode=2)
+    for (x, y) in [(0, 0), (0, 1), (1, 1), (2, 2), (2, 4), (3, 0), (3, 2), (4, 3), (1, 4)]:
+        R, tq, tr, o = ctx.crp_pair(x, y, prm)
+        Ro, info = oracle.chroma_cross_similarity(tracks[x], tracks[y], full=True)
+        assert o == info["oti"], (x, y)
+        assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]), (x, y)
+        assert np.array_equal(R, Ro), (x, y)
+
+
+def test_band_vs_exact_mode_scores_large(ctx):
+    """BASELINE-size tracks: mode 2 against mode 1 (itself checked against the oracle) on more pairs
+    than the CPU oracle could do in seconds"""
+    rng = np.random.default_rng(33)
+    tracks = _tracks(rng, [int(x) for x in rng.integers(1600, 2400, size=10)], noise=0.08)
+    ctx.upload_tracks(tracks)
+    pairs = np.array([(i, j) for i in range(10) for j in range(10) if i < j], np.int32)
+    q1, d1 = ctx.serra09_pairs(pairs, ctx.params(crp_mode=1), want_dmax=True)
+    q2, d2 = ctx.serra09_pairs(pairs, ctx.params(crp_mode=2), want_dmax=True)
+    st = ctx.pair_stats()
+    assert np.array_equal(q1, q2) and np.array_equal(d1, d2)
+    assert st["n_exact_cells"] < 0.02 * st["crp_cells"], st
+    R1 = ctx.crp_pair(0, 1, ctx.params(crp_mode=1))
+    R2 = ctx.crp_pair(0, 1, ctx.params(crp_mode=2))
+    assert all(np.array_equal(x, y) for x, y in zip(R1[:3], R2[:3]))
+
+
 def test_crp_golden(ctx, golden):
     g = golden("serra09_small.npz")
     n = int(g["n_tracks"])
