@@ -62,6 +62,8 @@ SYMBOLS = {
                                              ctypes.c_int32, c_f64p, c_f64p]),
     "acoss_np_pairwise_sum": (ctypes.c_double, [c_f64p, ctypes.c_int64]),
     "acoss_sw_constrained_from_binary": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, c_f64p]),
+    "acoss_snf": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                 ctypes.c_double, c_f64p, c_vp]),
     "acoss_dev_alloc": (ctypes.c_int, [c_vp, ctypes.c_int64, ctypes.POINTER(c_vp)]),
     "acoss_dev_free": (ctypes.c_int, [c_vp, c_vp]),
     "acoss_memcpy_h2d": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64]),
@@ -250,3 +252,16 @@ class Context(object):
                                                 _ptr(cstart, ctypes.c_int32), _ptr(tops, ctypes.c_int32), len(tops),
                                                 _ptr(out, ctypes.c_double), _ptr(ranks, ctypes.c_double)))
         return out, ranks
+
+    # ---- similarity network fusion -------------------------------------------------
+    def snf(self, mats, K=5, niters=5, reg_diag=1, want_Ws=True):
+        """doSimilarityFusion on a list of (n, n) distance matrices (float32 or float64, all the same
+        dtype).  Returns (Ws list | None, fused float64 (n, n))."""
+        dt = np.float64 if any(np.asarray(m).dtype == np.float64 for m in mats) else np.float32
+        stack = np.ascontiguousarray(np.stack([np.asarray(m, dtype=dt) for m in mats]))
+        nm, n = stack.shape[0], stack.shape[1]
+        fused = np.zeros((n, n), np.float64)
+        Ws = np.zeros_like(stack) if want_Ws else None
+        self._ck(self.lib.acoss_snf(self.h, stack.ctypes.data_as(c_vp), 0 if dt == np.float32 else 1, nm, n, int(K), int(niters),
+                                    float(reg_diag), _ptr(fused, ctypes.c_double), Ws.ctypes.data_as(c_vp) if want_Ws else None))
+        return ([Ws[k] for k in range(nm)] if want_Ws else None), fused

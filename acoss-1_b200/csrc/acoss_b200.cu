@@ -17,6 +17,7 @@
 #include "kernels_crp_band.cuh"
 #include "kernels_dp.cuh"
 #include "kernels_eval.cuh"
+#include "kernels_snf.cuh"
 
 static std::string g_create_error;
 
@@ -249,3 +250,4 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 
 #include "api_pairs.inc"
 #include "api_matrix.inc"
+#include "api_snf.inc"

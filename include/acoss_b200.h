@@ -194,6 +194,18 @@ int acoss_sw_constrained_from_binary(acoss_ctx *ctx, const uint8_t *mats_host,
                                      const int32_t *Ms_host, const int32_t *Ns_host,
                                      int32_t n, double *out_scores_host);
 
+/* ---- similarity network fusion (LateFusionChen, EarlyFusionTralie) -------------- */
+
+/* doSimilarityFusion(Scores, K, niters, reg_diag) (acoss/algorithms/utils/similarity_fusion.py:188-196;
+ * getW :15-36, getP :101-122, getS :124-144, doSimilarityFusionWs :146-186) on n_mats
+ * (n x n) distance matrices, concatenated in mats_host.  dtype 0 = float32, 1 = float64: the
+ * affinity stage runs in that type, the diffusion in float64, as numpy promotes in the reference.
+ * out_fused_host: (n x n) float64.  out_Ws_host (may be NULL): the n_mats affinity matrices in the
+ * input dtype (first element of the tuple the reference returns).  The reference's list aliasing
+ * (iteration 0 Jacobi, then Gauss-Seidel) is reproduced. */
+int acoss_snf(acoss_ctx *ctx, const void *mats_host, int32_t dtype, int32_t n_mats, int32_t n,
+              int32_t K, int32_t niters, double reg_diag, double *out_fused_host, void *out_Ws_host);
+
 /* ---- plain device memory helpers for host languages without a CUDA binding -- */
 int acoss_dev_alloc(acoss_ctx *ctx, int64_t bytes, void **out_dev);
 int acoss_dev_free(acoss_ctx *ctx, void *dev);

@@ -326,3 +326,101 @@ def test_benchmark_entry_point(golden, workdir):
     res = acoss_b200.benchmark(csv, fdir, algorithm="Serra09", shortname="bm")
     assert list(res["main"][:4]) == g["serra_eval"].tolist()
     assert (workdir / "results_bm_Serra09.csv").exists()
+
+
+# ---- similarity network fusion + LateFusionChen ------------------------------------------------
+@pytest.mark.gpu
+def test_snf_vs_reference_golden(ctx, golden):
+    """doSimilarityFusion run verbatim from the reference (float32 inputs, incl. the Q8 aliasing)."""
+    g = golden("snf_reference.npz")
+    for c in range(int(g["n"])):
+        nm, N, K, nit = (int(x) for x in g["cfg%d" % c])
+        mats = [g["D%d_%d" % (c, k)] for k in range(nm)]
+        Ws, fused = ctx.snf(mats, K=K, niters=nit, reg_diag=1)
+        assert fused.dtype == np.float64 and fused.shape == (N, N)
+        # tolerance: the affinity stage is float32 (expf vs numpy's exp differ in the last ulp)
+        np.testing.assert_allclose(fused, g["fused%d" % c], rtol=2e-5, atol=1e-9)
+
+
+@pytest.mark.gpu
+def test_snf_float64_vs_numpy_restatement(ctx):
+    """float64 inputs: compare with a plain numpy restatement of the same equations written here
+    (Jacobi first sweep, Gauss-Seidel afterwards)."""
+    rng = np.random.default_rng(11)
+    N, K, nit, nm = 150, 10, 6, 3
+    mats = []
+    for _ in range(nm):
+        X = rng.random((N, 5))
+        mats.append(np.sqrt(((X[:, None] - X[None]) ** 2).sum(-1)) + 0.05 * rng.random((N, N)))
+    Ws_dev, fused = ctx.snf(mats, K=K, niters=nit, reg_diag=1)
+
+    def getW(D):
+        S = 0.5 * (D + D.T)
+        np.fill_diagonal(S, 0)
+        md = np.sort(S, 1)[:, :K + 1].mean(1) * (K + 1) / K
+        eps = (md[:, None] + md[None, :] + S) / 3
+        den = 2 * (0.5 * eps) ** 2
+        den[den == 0] = 1
+        return np.exp(-S ** 2 / den)
+    Ws = [getW(D) for D in mats]
+    for a, b in zip(Ws, Ws_dev):
+        np.testing.assert_allclose(b, a, rtol=1e-12)
+    Ps = [W / W.sum(1, keepdims=True) for W in Ws]
+    Ss = []
+    for W in Ws:
+        S = np.zeros_like(W)
+        J = np.argsort(-W, 1, kind="stable")[:, :K]
+        for i in range(N):
+            S[i, J[i]] = W[i, J[i]] / W[i, J[i]].sum()
+        Ss.append(S)
+    Pts = [P.copy() for P in Ps]
+    for it in range(nit):
+        src = [P.copy() for P in Pts] if it == 0 else Pts
+        for i in range(nm):
+            X = sum(src[k] for k in range(nm) if k != i) / (nm - 1)
+            Pts[i] = Ss[i] @ X @ Ss[i].T + np.eye(N)
+            if it > 0:
+                src = Pts
+    np.testing.assert_allclose(fused, sum(Pts) / nm, rtol=1e-10)
+
+
+@pytest.mark.gpu
+def test_snf_argument_errors(ctx):
+    import acoss_b200
+    D = np.random.default_rng(0).random((10, 10)).astype(np.float32)
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.snf([D], K=3)                      # one matrix: the reference divides by N-1 = 0
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.snf([D, D], K=9)                   # kth = K+1 out of bounds (np.partition raises)
+
+
+@pytest.mark.gpu
+def test_chen_class_matches_reference_golden(golden, workdir):
+    """The reference's ChenFusion run verbatim (on the essentia restatement) vs the drop-in class."""
+    import acoss_b200
+    g = golden("serra09_small.npz")
+    csv, fdir = _write_golden_dataset(g, workdir)
+    c = acoss_b200.ChenFusion(csv, fdir, shortname="g")
+    c.all_pairwise(1, n_cores=4, symmetric=True)
+    assert np.array_equal(np.array(c.Ds["qmax"]), g["chen_q_raw"])
+    assert np.array_equal(np.array(c.Ds["dmax"]), g["chen_d_raw"])
+    c.normalize_by_length()
+    assert np.array_equal(np.array(c.Ds["qmax"]), g["chen_q_norm"])
+    assert np.array_equal(np.array(c.Ds["dmax"]), g["chen_d_norm"])
+    c.do_late_fusion()
+    np.testing.assert_allclose(np.array(c.Ds["Late"]), g["chen_late"], rtol=2e-5, atol=1e-9)
+    assert np.array_equal(np.array(c.Ds["qmax"]), -g["chen_q_norm"])
+    for k in ("qmax", "dmax", "Late"):
+        res = c.getEvalStatistics(k)
+        assert list(res[:4]) == g["chen_eval_" + k].tolist()
+    c.cleanup_memmap()
+
+
+@pytest.mark.gpu
+def test_benchmark_entry_point_chen(golden, workdir):
+    import acoss_b200
+    g = golden("serra09_small.npz")
+    csv, fdir = _write_golden_dataset(g, workdir)
+    res = acoss_b200.benchmark(csv, fdir, algorithm="LateFusionChen", shortname="bm")
+    for k in ("qmax", "dmax", "Late"):
+        assert list(res[k][:4]) == g["chen_eval_" + k].tolist()
