@@ -10,5 +10,7 @@ from .algorithm_template import CoverAlgorithm
 from .coverid import algorithm_names, benchmark
 from .latefusion_chen import ChenFusion
 from .rqa_serra09 import Serra09
+from .simple_silva import Simple
+from .ftm2d import FTM2D
 
 __version__ = "0.1.0"

@@ -64,6 +64,9 @@ SYMBOLS = {
     "acoss_sw_constrained_from_binary": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, c_f64p]),
     "acoss_snf": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                  ctypes.c_double, c_f64p, c_vp]),
+    "acoss_simple_upload": (ctypes.c_int, [c_vp, c_f64p, c_i64p, ctypes.c_int32]),
+    "acoss_simple_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_int32, c_f64p]),
+    "acoss_ftm2d_allpairs": (ctypes.c_int, [c_vp, c_f64p, ctypes.c_int32, ctypes.c_int32, c_f64p]),
     "acoss_dev_alloc": (ctypes.c_int, [c_vp, ctypes.c_int64, ctypes.POINTER(c_vp)]),
     "acoss_dev_free": (ctypes.c_int, [c_vp, c_vp]),
     "acoss_memcpy_h2d": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64]),
@@ -265,3 +268,26 @@ class Context(object):
         self._ck(self.lib.acoss_snf(self.h, stack.ctypes.data_as(c_vp), 0 if dt == np.float32 else 1, nm, n, int(K), int(niters),
                                     float(reg_diag), _ptr(fused, ctypes.c_double), Ws.ctypes.data_as(c_vp) if want_Ws else None))
         return ([Ws[k] for k in range(nm)] if want_Ws else None), fused
+
+    # ---- SiMPle / FTM2D ---------------------------------------------------------------
+    def simple_upload(self, feats):
+        """feats: list of (12, L_t) float64 arrays (Simple.load_features output)."""
+        feats = [_np(f, np.float64) for f in feats]
+        offs = np.zeros(len(feats) + 1, np.int64)
+        offs[1:] = np.cumsum([f.shape[1] for f in feats])
+        flat = np.concatenate([f.ravel() for f in feats]) if feats else np.zeros(0)
+        flat = _np(flat, np.float64)
+        self._ck(self.lib.acoss_simple_upload(self.h, _ptr(flat, ctypes.c_double), _ptr(offs, ctypes.c_int64), len(feats)))
+
+    def simple_pairs(self, pairs, sslen=10):
+        pairs = _np(pairs, np.int32).reshape(-1, 2)
+        out = np.zeros(pairs.shape[0], np.float64)
+        self._ck(self.lib.acoss_simple_pairs(self.h, _ptr(pairs, ctypes.c_int32), pairs.shape[0], int(sslen), _ptr(out, ctypes.c_double)))
+        return out
+
+    def ftm2d_allpairs(self, shingles):
+        S = _np(shingles, np.float64)
+        n, d = S.shape
+        D = np.zeros((n, n), np.float64)
+        self._ck(self.lib.acoss_ftm2d_allpairs(self.h, _ptr(S, ctypes.c_double), n, d, _ptr(D, ctypes.c_double)))
+        return D

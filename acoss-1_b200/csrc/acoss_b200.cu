@@ -18,6 +18,7 @@
 #include "kernels_dp.cuh"
 #include "kernels_eval.cuh"
 #include "kernels_snf.cuh"
+#include "kernels_simple.cuh"
 
 static std::string g_create_error;
 
@@ -50,6 +51,10 @@ struct acoss_ctx {
     std::vector<int32_t> h_emb;       // embedded rows per track
     std::vector<int64_t> h_sd_off;    // self-dot table offsets
     DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma;
+    // SiMPle feature store (frame-major float64) + per-track chroma profiles
+    int sp_tracks = 0;
+    std::vector<int64_t> sp_offs;
+    DevBuf d_sp_feats, d_sp_offs, d_sp_prof;
     // per-call scratch
     DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2, d_counters;
     cudaEvent_t ev[8] = {};
@@ -107,7 +112,8 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
                       &ctx->d_gchroma, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
-                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters};
+                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters,
+                      &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
@@ -251,3 +257,4 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 #include "api_pairs.inc"
 #include "api_matrix.inc"
 #include "api_snf.inc"
+#include "api_simple.inc"

@@ -1,0 +1,209 @@
+// kernels_simple.cuh -- SiMPle matrix-profile similarity and FTM2D shingle distance (sm_100a).
+//
+// SiMPle (acoss/algorithms/simple_silva.py): Simple.oti (:45-54), Simple.simple_sim (:68-118),
+// Simple.similarity (:120-126).  For the ordered pair (i, j):
+//     B' = roll(B_j, oti, axis=0),  oti = argsort(<sum_t A_i, roll(sum_t B_j, k)>)[-1]
+//     MP[p] = min_q  sum_{k < SSLEN} sum_{c < 12} (A[c][p+k] - B'[c][q+k])^2,   p <= La - SSLEN, q <= Lb - SSLEN
+//     score = -median(MP)                                   (float64 throughout, like the reference)
+// The reference evaluates the same quantity through FFT-seeded sliding dot products (STOMP); here
+// each diagonal of the (La x Lb) frame-distance matrix is walked once with a running SSLEN-window sum,
+// i.e. 12 subtract + 12 FMA per cell and no dependence on the reference's rounding path.
+// One CTA per ordered pair; both sequences and the profile live in shared memory.  Compute-bound on
+// the FP64 pipe (~26 flop per cell, 8*12*(La+Lb) bytes in, 8 bytes out).
+//
+// FTM2D (acoss/algorithms/ftm2d.py:85-97): sim(i, j) = exp(-sum((s_i - s_j)^2)) on 900-d float64
+// shingles: one tiled all-pairs kernel (4*N_t^2 output bytes; 2*900 flop per pair).
+#pragma once
+#include "common.cuh"
+
+#define SIMPLE_THREADS 256
+#define SIMPLE_SEG 48            // profile rows per work item (plus SSLEN-1 warm-up cells)
+
+// feats: frame-major (L_t, 12) float64 per track; prof: (n_tracks, 12) sums over time
+__global__ void simple_prepare_kernel(const double* __restrict__ rowmajor /* (12, L) per track */,
+                                      const int64_t* __restrict__ offs, int n_tracks,
+                                      double* __restrict__ framemajor, double* __restrict__ prof)
+{
+    const int t = blockIdx.x;
+    if (t >= n_tracks) return;
+    const int64_t o = offs[t];
+    const int L = (int)(offs[t + 1] - o);
+    const double* src = rowmajor + o * ACOSS_NBINS;
+    double* dst = framemajor + o * ACOSS_NBINS;
+    for (int e = threadIdx.x; e < L * ACOSS_NBINS; e += blockDim.x) {
+        const int p = e / ACOSS_NBINS, c = e - p * ACOSS_NBINS;
+        dst[e] = src[(int64_t)c * L + p];
+    }
+    if (threadIdx.x < ACOSS_NBINS) {
+        double s = 0.0;
+        for (int p = 0; p < L; ++p) s += src[(int64_t)threadIdx.x * L + p];
+        prof[t * ACOSS_NBINS + threadIdx.x] = s;
+    }
+}
+
+template <int SSLEN>
+__device__ __forceinline__ void simple_walk(const double* __restrict__ As, const double* __restrict__ Bs,
+                                            int p0, int q0, int n_out, unsigned long long* mp)
+{
+    // cells (p0 + t, q0 + t), t = 0 .. n_out + SSLEN - 2; output row p0 + t - (SSLEN - 1) for t >= SSLEN - 1
+    double ring[SSLEN];
+#pragma unroll
+    for (int k = 0; k < SSLEN; ++k) ring[k] = 0.0;
+    double s = 0.0;
+    const int total = n_out + SSLEN - 1;
+    for (int base = 0; base < total; base += SSLEN) {
+#pragma unroll
+        for (int k = 0; k < SSLEN; ++k) {
+            const int t = base + k;
+            if (t < total) {
+                const double* a = As + (p0 + t) * ACOSS_NBINS;
+                const double* b = Bs + (q0 + t) * ACOSS_NBINS;
+                double g = 0.0;
+#pragma unroll
+                for (int c = 0; c < ACOSS_NBINS; ++c) { const double d = a[c] - b[c]; g = fma(d, d, g); }
+                s += g - ring[k];
+                ring[k] = g;
+                if (t >= SSLEN - 1) {
+                    // re-sum the window exactly every SSLEN steps is unnecessary in fp64 (drift ~1e-16 per step)
+                    const double v = s < 0.0 ? 0.0 : s;
+                    const int row = p0 + t - (SSLEN - 1);
+                    const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+                    if (bits < mp[row]) atomicMin(&mp[row], bits);
+                }
+            }
+        }
+    }
+}
+
+// generic window length: the outgoing cell is recomputed instead of kept in a register ring
+__device__ __forceinline__ double simple_cell(const double* a, const double* b)
+{
+    double g = 0.0;
+#pragma unroll
+    for (int c = 0; c < ACOSS_NBINS; ++c) { const double d = a[c] - b[c]; g = fma(d, d, g); }
+    return g;
+}
+
+template <int SSLEN_T>
+__global__ void __launch_bounds__(SIMPLE_THREADS)
+simple_pair_kernel(const int32_t* __restrict__ pairs, int64_t n_pairs, const double* __restrict__ feats,
+                   const int64_t* __restrict__ offs, const double* __restrict__ prof, int sslen, int maxL,
+                   double* __restrict__ out)
+{
+    extern __shared__ __align__(16) unsigned char simple_smem[];
+    double* As = reinterpret_cast<double*>(simple_smem);
+    double* Bs = As + (size_t)maxL * ACOSS_NBINS;
+    unsigned long long* mp = reinterpret_cast<unsigned long long*>(Bs + (size_t)maxL * ACOSS_NBINS);
+    __shared__ double otiv[ACOSS_NBINS];
+    __shared__ int s_oti;
+    __shared__ double s_med[2];
+    const int tid = threadIdx.x;
+    for (int64_t pi = blockIdx.x; pi < n_pairs; pi += gridDim.x) {
+        const int ta = pairs[2 * pi], tb = pairs[2 * pi + 1];
+        const int64_t oa = offs[ta], ob = offs[tb];
+        const int La = (int)(offs[ta + 1] - oa), Lb = (int)(offs[tb + 1] - ob);
+        __syncthreads();
+        if (tid < ACOSS_NBINS) {
+            double v = 0.0;                    // np.dot(profile_a, np.roll(profile_b, tid))
+            for (int c = 0; c < ACOSS_NBINS; ++c) v += prof[ta * ACOSS_NBINS + c] * prof[tb * ACOSS_NBINS + rot_src(c, tid)];
+            otiv[tid] = v;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int best = 0;                      // argsort(...)[-1]: the last (largest index) among equal maxima
+            for (int k = 1; k < ACOSS_NBINS; ++k) if (otiv[k] >= otiv[best]) best = k;
+            s_oti = best;
+        }
+        __syncthreads();
+        const int rot = s_oti;
+        for (int e = tid; e < La * ACOSS_NBINS; e += SIMPLE_THREADS) As[e] = feats[oa * ACOSS_NBINS + e];
+        for (int e = tid; e < Lb * ACOSS_NBINS; e += SIMPLE_THREADS) {
+            const int q = e / ACOSS_NBINS, c = e - q * ACOSS_NBINS;
+            Bs[e] = feats[(ob + q) * ACOSS_NBINS + rot_src(c, rot)];
+        }
+        const int n_mp = La - sslen + 1, n_q = Lb - sslen + 1;
+        for (int e = tid; e < n_mp; e += SIMPLE_THREADS) mp[e] = 0x7FF0000000000000ull;     // +inf
+        __syncthreads();
+        // work items: (diagonal delta = q - p, segment of SIMPLE_SEG profile rows), dealt round-robin
+        int item = 0;
+        for (int delta = -(n_mp - 1); delta <= n_q - 1; ++delta) {
+            const int p_lo = delta < 0 ? -delta : 0;                  // first profile row on this diagonal
+            const int p_hi = min(n_mp - 1, n_q - 1 - delta);          // last
+            const int n_rows = p_hi - p_lo + 1;
+            for (int r0 = 0; r0 < n_rows; r0 += SIMPLE_SEG, ++item) {
+                if ((item & (SIMPLE_THREADS - 1)) != tid) continue;
+                const int n_out = min(SIMPLE_SEG, n_rows - r0);
+                const int p0 = p_lo + r0, q0 = p0 + delta;
+                if (SSLEN_T > 0) simple_walk<(SSLEN_T > 0 ? SSLEN_T : 1)>(As, Bs, p0, q0, n_out, mp);
+                else {
+                    double s = 0.0;
+                    for (int t = 0; t < n_out + sslen - 1; ++t) {
+                        s += simple_cell(As + (p0 + t) * ACOSS_NBINS, Bs + (q0 + t) * ACOSS_NBINS);
+                        if (t >= sslen) s -= simple_cell(As + (p0 + t - sslen) * ACOSS_NBINS, Bs + (q0 + t - sslen) * ACOSS_NBINS);
+                        if (t >= sslen - 1) {
+                            const double v = s < 0.0 ? 0.0 : s;
+                            const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+                            const int row = p0 + t - (sslen - 1);
+                            if (bits < mp[row]) atomicMin(&mp[row], bits);
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        // np.median(matrix_profile): rank by counting (non-negative doubles order like their bit patterns)
+        const int k_lo = (n_mp - 1) / 2, k_hi = n_mp / 2;
+        for (int e = tid; e < n_mp; e += SIMPLE_THREADS) {
+            const unsigned long long v = mp[e];
+            int rank = 0;
+            for (int j = 0; j < n_mp; ++j) { const unsigned long long w = mp[j]; rank += (w < v) || (w == v && j < e); }
+            if (rank == k_lo) s_med[0] = __longlong_as_double((long long)v);
+            if (rank == k_hi) s_med[1] = __longlong_as_double((long long)v);
+        }
+        __syncthreads();
+        if (tid == 0) out[pi] = -((k_lo == k_hi) ? s_med[0] : (s_med[0] + s_med[1]) / 2.0);
+    }
+}
+
+// FTM2D: D[i][j] = exp(-sum_k (S[i][k] - S[j][k])^2); 64 x 64 tile per CTA, 4 x 4 per thread
+#define FTM_TILE 64
+#define FTM_KC 16
+__global__ void __launch_bounds__(256)
+ftm2d_allpairs_kernel(const double* __restrict__ S, int n, int d, double* __restrict__ D)
+{
+    __shared__ double sa[FTM_KC][FTM_TILE + 1];
+    __shared__ double sb[FTM_KC][FTM_TILE + 1];
+    const int i0 = blockIdx.y * FTM_TILE, j0 = blockIdx.x * FTM_TILE;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    double acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+    for (int k0 = 0; k0 < d; k0 += FTM_KC) {
+        for (int e = threadIdx.x; e < FTM_TILE * FTM_KC; e += 256) {
+            const int r = e / FTM_KC, k = e - r * FTM_KC;
+            sa[k][r] = (i0 + r < n && k0 + k < d) ? S[(int64_t)(i0 + r) * d + k0 + k] : 0.0;
+            sb[k][r] = (j0 + r < n && k0 + k < d) ? S[(int64_t)(j0 + r) * d + k0 + k] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < FTM_KC; ++k) {
+            double av[4], bv[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) { av[a] = sa[k][ty * 4 + a]; bv[a] = sb[k][tx * 4 + a]; }
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) { const double df = av[a] - bv[b]; acc[a][b] = fma(df, df, acc[a][b]); }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int i = i0 + ty * 4 + a, j = j0 + tx * 4 + b;
+            if (i < n && j < n) D[(int64_t)i * n + j] = exp(-acc[a][b]);
+        }
+}

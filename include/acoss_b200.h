@@ -206,6 +206,24 @@ int acoss_sw_constrained_from_binary(acoss_ctx *ctx, const uint8_t *mats_host,
 int acoss_snf(acoss_ctx *ctx, const void *mats_host, int32_t dtype, int32_t n_mats, int32_t n,
               int32_t K, int32_t niters, double reg_diag, double *out_fused_host, void *out_Ws_host);
 
+/* ---- SiMPle (matrix profile) and FTM2D ------------------------------------------- */
+
+/* Uploads the SiMPle features of all tracks: feats_host = concatenation of (12, L_t) row-major
+ * float64 arrays (what Simple.load_features returns, acoss/algorithms/simple_silva.py:34-43),
+ * col_offsets_host[n_tracks+1] = column offsets.  Also computes np.sum(seq, 1) per track (:46-47). */
+int acoss_simple_upload(acoss_ctx *ctx, const double *feats_host, const int64_t *col_offsets_host,
+                        int32_t n_tracks);
+
+/* For every ORDERED pair (i, j): Sj = Simple.oti(Si, Sj)[0]; out = -Simple.simple_sim(Si, Sj)
+ * (simple_silva.py:45-54, 68-118, 120-126); sslen = SSLEN (default 10).  float64 scores. */
+int acoss_simple_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pairs, int32_t sslen,
+                       double *out_scores_host);
+
+/* FTM2D.similarity for all pairs at once (acoss/algorithms/ftm2d.py:85-97):
+ * out_D_host[i*n + j] = exp(-sum((s_i - s_j)**2)), shingles_host = (n, d) float64 (d = 900). */
+int acoss_ftm2d_allpairs(acoss_ctx *ctx, const double *shingles_host, int32_t n, int32_t d,
+                         double *out_D_host);
+
 /* ---- plain device memory helpers for host languages without a CUDA binding -- */
 int acoss_dev_alloc(acoss_ctx *ctx, int64_t bytes, void **out_dev);
 int acoss_dev_free(acoss_ctx *ctx, void *dev);

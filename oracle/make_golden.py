@@ -183,6 +183,54 @@ def gen_serra(ns):
     print("serra09_small: MAP", out["serra_eval"][3], "chen late MAP", out["chen_eval_Late"][3])
 
 
+
+def simple_ftm_dataset():
+    """Deterministic small dataset for the SiMPle / FTM2D goldens: 5 works x 2 covers, raw T ~ 2400-3600
+    (SiMPle: 24-36 columns; FTM2D: beats every ~18 frames -> 130-200 beats >= WIN = 75)."""
+    from acoss_b200 import synth
+    labels, works, tids, hp = synth.make_tracks(5, 2, 0, 777, 2400, 3600)
+    rng = np.random.default_rng(778)
+    onsets = []
+    for h in hp:
+        gaps = rng.integers(14, 23, size=h.shape[0] // 14 + 2)
+        o = np.cumsum(gaps)
+        onsets.append(o[o < h.shape[0]].astype(np.int64))
+    ds = dict(labels=labels, work_ids=works, track_ids=tids, hpcp=hp, fac=1)
+    extra = {"madmom_features": [{"onsets": o} for o in onsets]}
+    return ds, extra
+
+
+def gen_simple_ftm(ns):
+    from acoss_b200 import synth
+    ds, extra = simple_ftm_dataset()
+    out = {"hpcp_sum": np.array([float(np.sum(h, dtype=np.float64)) for h in ds["hpcp"]])}
+    with tempfile.TemporaryDirectory() as tmp:
+        fdir = synth.write_dataset(os.path.join(tmp, "feat"), ds, os.path.join(tmp, "ds.csv"), extra=extra)
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            s = quiet(ns.simple.Simple, os.path.join(tmp, "ds.csv"), fdir, shortname="g")
+            for i in range(s.N):
+                out["simple_feat%d" % i] = np.asarray(quiet(s.load_features, i), np.float64)
+            quiet(s.all_pairwise, 0, 1, False)
+            out["simple_D"] = np.array(s.Ds["main"])
+            # float64 scores of a few ordered pairs straight from simple_sim (Ds is float32)
+            prs = [(0, 1), (1, 0), (2, 7), (9, 4), (3, 3)]
+            out["simple_pairs"] = np.array(prs, np.int32)
+            out["simple_scores"] = np.array([-s.simple_sim(out["simple_feat%d" % a], s.oti(out["simple_feat%d" % a], out["simple_feat%d" % b])[0])
+                                             for a, b in prs], np.float64)
+            out["simple_eval"] = np.array(list(quiet(s.getEvalStatistics, "main")[:4]), np.float64)
+            f = quiet(ns.ftm2d.FTM2D, os.path.join(tmp, "ds.csv"), fdir, shortname="g")
+            for i in range(f.N):
+                out["ftm_shingle%d" % i] = np.asarray(quiet(f.load_features, i), np.float64)
+            quiet(f.all_pairwise, 0, 1, True)
+            out["ftm_D"] = np.array(f.Ds["main"])
+            out["ftm_eval"] = np.array(list(quiet(f.getEvalStatistics, "main")[:4]), np.float64)
+        finally:
+            os.chdir(cwd)
+    np.savez_compressed(os.path.join(GOLD, "simple_ftm2d_reference.npz"), **out)
+    print("simple_ftm2d_reference: simple MAP", out["simple_eval"][3], "ftm MAP", out["ftm_eval"][3])
+
 def gen_percentile():
     from oracle import oracle as O
     rng = np.random.default_rng(5)
@@ -207,6 +255,7 @@ def main():
     gen_eval(ns)
     gen_snf(ns)
     gen_serra(ns)
+    gen_simple_ftm(ns)
 
 
 if __name__ == "__main__":

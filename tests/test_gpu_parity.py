@@ -424,3 +424,82 @@ def test_benchmark_entry_point_chen(golden, workdir):
     res = acoss_b200.benchmark(csv, fdir, algorithm="LateFusionChen", shortname="bm")
     for k in ("qmax", "dmax", "Late"):
         assert list(res[k][:4]) == g["chen_eval_" + k].tolist()
+
+
+# ---- SiMPle and FTM2D ------------------------------------------------------------------------
+def _simple_ftm_dataset(workdir):
+    from acoss_b200 import synth
+    from oracle.make_golden import simple_ftm_dataset
+    ds, extra = simple_ftm_dataset()
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"), extra=extra)
+    return str(workdir / "ds.csv"), fdir
+
+
+def test_simple_pairs_vs_reference_golden(ctx, golden):
+    """-simple_sim(Si, oti(Si, Sj)) of the reference (float64) vs the matrix-profile kernel.
+    Tolerance: the reference accumulates FFT-seeded sliding dot products (~1e-13 absolute noise)."""
+    g = golden("simple_ftm2d_reference.npz")
+    feats = [g["simple_feat%d" % i] for i in range(10)]
+    ctx.simple_upload(feats)
+    got = ctx.simple_pairs(g["simple_pairs"])
+    np.testing.assert_allclose(got, g["simple_scores"], rtol=1e-9, atol=1e-11)
+    n = len(feats)
+    allp = np.array([(i, j) for i in range(n) for j in range(n) if i != j], np.int32)
+    sc = ctx.simple_pairs(allp)
+    D = np.zeros((n, n), np.float32)
+    D[allp[:, 0], allp[:, 1]] = sc
+    np.testing.assert_allclose(D, g["simple_D"], rtol=1e-6, atol=1e-9)
+
+
+def test_simple_generic_sslen_and_errors(ctx):
+    import acoss_b200
+    rng = np.random.default_rng(5)
+    feats = []
+    for L in (31, 24, 40):
+        x = rng.random((12, L)) + 0.05
+        feats.append(x / np.sqrt((x ** 2).sum(0, keepdims=True)))
+    ctx.simple_upload(feats)
+    pairs = np.array([(0, 1), (1, 2), (2, 0)], np.int32)
+
+    def brute(a, b, ss):
+        prof_a, prof_b = a.sum(1), b.sum(1)
+        v = [np.dot(prof_a, np.roll(prof_b, k)) for k in range(12)]
+        b = np.roll(b, int(np.argsort(v)[-1]), axis=0)
+        na, nb = a.shape[1] - ss + 1, b.shape[1] - ss + 1
+        mp = [min(((a[:, p:p + ss] - b[:, q:q + ss]) ** 2).sum() for q in range(nb)) for p in range(na)]
+        return -np.median(mp)
+    for ss in (10, 7):
+        got = ctx.simple_pairs(pairs, sslen=ss)
+        exp = [brute(feats[a], feats[b], ss) for a, b in pairs]
+        np.testing.assert_allclose(got, exp, rtol=1e-12, atol=1e-14)
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.simple_pairs(pairs, sslen=30)          # track 1 has 24 columns < SSLEN
+
+
+def test_ftm2d_allpairs_vs_reference_golden(ctx, golden):
+    g = golden("simple_ftm2d_reference.npz")
+    S = np.stack([g["ftm_shingle%d" % i] for i in range(10)])
+    D = ctx.ftm2d_allpairs(S)
+    exp = np.exp(-((S[:, None, :] - S[None, :, :]) ** 2).sum(-1))
+    np.testing.assert_allclose(D, exp, rtol=1e-13)
+    ref = g["ftm_D"]                                # float32 memmap of the reference, diagonal 0
+    Dz = D.astype(np.float32)
+    np.fill_diagonal(Dz, 0)
+    assert np.array_equal(Dz, ref)
+    S2 = np.random.default_rng(2).random((131, 900))
+    D2 = ctx.ftm2d_allpairs(S2)
+    np.testing.assert_allclose(D2, np.exp(-((S2 ** 2).sum(1)[:, None] + (S2 ** 2).sum(1)[None] - 2 * S2 @ S2.T)), rtol=1e-9)
+
+
+def test_simple_and_ftm2d_classes_and_benchmark(golden, workdir):
+    import acoss_b200
+    g = golden("simple_ftm2d_reference.npz")
+    csv, fdir = _simple_ftm_dataset(workdir)
+    res = acoss_b200.benchmark(csv, fdir, algorithm="SiMPle", shortname="g")
+    assert list(res["main"][:4]) == g["simple_eval"].tolist()
+    res = acoss_b200.benchmark(csv, fdir, algorithm="FTM2D", shortname="g")
+    assert list(res["main"][:4]) == g["ftm_eval"].tolist()
+    f = acoss_b200.FTM2D(csv, fdir, shortname="g2")
+    f.all_pairwise(1, symmetric=True)
+    assert np.array_equal(np.array(f.Ds["main"]), g["ftm_D"])
+    f.cleanup_memmap()

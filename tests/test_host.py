@@ -137,3 +137,29 @@ def test_gloo_world2_shard_and_allgather(tmp_path):
                        capture_output=True, text=True, timeout=240, env=env)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.count("ok") == 2
+
+
+def _simple_ftm_dataset(workdir):
+    from acoss_b200 import synth
+    from oracle.make_golden import simple_ftm_dataset
+    ds, extra = simple_ftm_dataset()
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"), extra=extra)
+    return str(workdir / "ds.csv"), fdir, ds
+
+
+def test_simple_and_ftm2d_load_features_match_reference(golden, workdir):
+    """Per-track preprocessing of SiMPle / FTM2D (host side) against the reference run verbatim."""
+    import acoss_b200
+    from acoss_b200.simple_silva import Simple
+    from acoss_b200.ftm2d import FTM2D
+    g = golden("simple_ftm2d_reference.npz")
+    csv, fdir, ds = _simple_ftm_dataset(workdir)
+    assert np.allclose([float(np.sum(h, dtype=np.float64)) for h in ds["hpcp"]], g["hpcp_sum"], rtol=0, atol=0)
+    s = Simple(csv, fdir, shortname="g")
+    f = FTM2D(csv, fdir, shortname="g")
+    for i in range(s.N):
+        np.testing.assert_allclose(s.load_features(i), g["simple_feat%d" % i], rtol=1e-12, atol=1e-15)
+        np.testing.assert_allclose(f.load_features(i), g["ftm_shingle%d" % i], rtol=1e-10, atol=1e-14)
+    a, b = g["simple_feat0"], g["simple_feat1"]
+    rolled, idx = s.oti(a, b)
+    assert rolled.shape == b.shape and len(idx) == 12
