@@ -12,5 +12,6 @@ from .latefusion_chen import ChenFusion
 from .rqa_serra09 import Serra09
 from .simple_silva import Simple
 from .ftm2d import FTM2D
+from .earlyfusion_traile import EarlyFusion
 
 __version__ = "0.1.0"

@@ -67,6 +67,12 @@ SYMBOLS = {
     "acoss_simple_upload": (ctypes.c_int, [c_vp, c_f64p, c_i64p, ctypes.c_int32]),
     "acoss_simple_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_int32, c_f64p]),
     "acoss_ftm2d_allpairs": (ctypes.c_int, [c_vp, c_f64p, ctypes.c_int32, ctypes.c_int32, c_f64p]),
+    "acoss_earlyfusion_upload": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32,
+                                                c_f32p, c_i64p, ctypes.c_int32]),
+    "acoss_earlyfusion_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_double, ctypes.c_int32, c_f64p]),
+    "acoss_earlyfusion_pair_matrices": (ctypes.c_int, [c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
+                                                       c_f32p, c_u8p, c_f64p]),
+    "acoss_earlyfusion_stats": (ctypes.c_int, [c_vp, c_f64p, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]),
     "acoss_dev_alloc": (ctypes.c_int, [c_vp, ctypes.c_int64, ctypes.POINTER(c_vp)]),
     "acoss_dev_free": (ctypes.c_int, [c_vp, c_vp]),
     "acoss_memcpy_h2d": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64]),
@@ -291,3 +297,41 @@ class Context(object):
         D = np.zeros((n, n), np.float64)
         self._ck(self.lib.acoss_ftm2d_allpairs(self.h, _ptr(S, ctypes.c_double), n, d, _ptr(D, ctypes.c_double)))
         return D
+
+    # ---- EarlyFusionTralie ---------------------------------------------------------------
+    def earlyfusion_upload(self, block_feats):
+        """block_feats: list of dicts with 'mfccs', 'ssms', 'chromas' (n_blocks, d) and 'chroma_med' (12)."""
+        nb = [int(f['mfccs'].shape[0]) for f in block_feats]
+        offs = np.zeros(len(nb) + 1, np.int64)
+        offs[1:] = np.cumsum(nb)
+        cat = {k: _np(np.concatenate([np.asarray(f[k], np.float32) for f in block_feats]), np.float32) for k in ('mfccs', 'ssms', 'chromas')}
+        cmed = _np(np.stack([np.asarray(f['chroma_med'], np.float32) for f in block_feats]), np.float32)
+        self.ef_blocks = np.array(nb, np.int64)
+        self._ck(self.lib.acoss_earlyfusion_upload(self.h, _ptr(cat['mfccs'], ctypes.c_float), cat['mfccs'].shape[1],
+                                                   _ptr(cat['ssms'], ctypes.c_float), cat['ssms'].shape[1],
+                                                   _ptr(cat['chromas'], ctypes.c_float), cat['chromas'].shape[1],
+                                                   _ptr(cmed, ctypes.c_float), _ptr(offs, ctypes.c_int64), len(nb)))
+
+    def earlyfusion_pairs(self, pairs, kappa=0.1, K=10):
+        """(P, 4) float64 scores: mfccs, ssms, chromas, early."""
+        pairs = _np(pairs, np.int32).reshape(-1, 2)
+        out = np.zeros((pairs.shape[0], 4), np.float64)
+        self._ck(self.lib.acoss_earlyfusion_pairs(self.h, _ptr(pairs, ctypes.c_int32), pairs.shape[0], float(kappa), int(K),
+                                                  _ptr(out, ctypes.c_double)))
+        return out
+
+    def earlyfusion_pair_matrices(self, i, j, kappa=0.1, K=10):
+        M, N = int(self.ef_blocks[i]), int(self.ef_blocks[j])
+        csm = np.zeros((4, M, N), np.float32)
+        bn = np.zeros((4, M, N), np.uint8)
+        sc = np.zeros(4, np.float64)
+        self._ck(self.lib.acoss_earlyfusion_pair_matrices(self.h, int(i), int(j), float(kappa), int(K), _ptr(csm, ctypes.c_float),
+                                                          _ptr(bn, ctypes.c_uint8), _ptr(sc, ctypes.c_double)))
+        return csm, bn, sc
+
+    def earlyfusion_stats(self):
+        ms = np.zeros(3, np.float64)
+        fl = ctypes.c_double(0)
+        cells = ctypes.c_int64(0)
+        self._ck(self.lib.acoss_earlyfusion_stats(self.h, _ptr(ms, ctypes.c_double), ctypes.byref(fl), ctypes.byref(cells)))
+        return {"ms_csm": ms[0], "ms_select": ms[1], "ms_sw": ms[2], "gemm_flop": fl.value, "cells": cells.value}

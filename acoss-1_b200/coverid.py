@@ -56,6 +56,15 @@ def benchmark(dataset_csv, feature_dir, feature_type="hpcp", algorithm="Serra09"
         algo.all_pairwise(parallel, n_cores=n_workers, symmetric=True)
         algo.normalize_by_length()
         algo.do_late_fusion()
+    elif algorithm in ("EarlyFusion", "EarlyFusionTraile"):
+        from .earlyfusion_traile import EarlyFusion
+        algo = EarlyFusion(dataset_csv=dataset_csv, datapath=feature_dir, chroma_type=feature_type,
+                           shortname=shortname, **algo_kwargs)
+        for i in range(len(algo.filepaths)):
+            algo.load_features(i)
+        _logger().info('Feature loading done...')
+        algo.all_pairwise(parallel, n_cores=n_workers, symmetric=True)
+        algo.do_late_fusion()
     elif algorithm == "FTM2D":
         from .ftm2d import FTM2D
         algo = FTM2D(dataset_csv=dataset_csv, datapath=feature_dir, chroma_type=feature_type,

@@ -19,6 +19,7 @@
 #include "kernels_eval.cuh"
 #include "kernels_snf.cuh"
 #include "kernels_simple.cuh"
+#include "kernels_early.cuh"
 
 static std::string g_create_error;
 
@@ -55,6 +56,12 @@ struct acoss_ctx {
     int sp_tracks = 0;
     std::vector<int64_t> sp_offs;
     DevBuf d_sp_feats, d_sp_offs, d_sp_prof;
+    // EarlyFusion block-feature store (mfccs, ssms, chromas), squared row norms, chroma medians; pair scratch
+    int ef_tracks = 0, ef_d[3] = {0, 0, 0};
+    std::vector<int64_t> ef_offs;
+    DevBuf d_ef_x[3], d_ef_sq[3], d_ef_cmed, d_ef_csm, d_ef_bin;
+    double ef_ms[3] = {0, 0, 0}, ef_flop = 0;
+    int64_t ef_cells = 0;
     // per-call scratch
     DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2, d_counters;
     cudaEvent_t ev[8] = {};
@@ -113,7 +120,9 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
                       &ctx->d_gchroma, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
                       &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters,
-                      &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof};
+                      &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
+                      &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
+                      &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
@@ -258,3 +267,4 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 #include "api_matrix.inc"
 #include "api_snf.inc"
 #include "api_simple.inc"
+#include "api_early.inc"

@@ -120,3 +120,48 @@ def write_dataset(feature_dir, ds, csv_path, extra=None):
             featio.save(os.path.join(feature_dir, w, t + ".h5"), d)
             f.write("%s,%s\n" % (w, t))
     return feature_dir
+
+
+def make_block_features(n_works, per_work, n_singletons, seed, nb_lo, nb_hi, n_mfcc=20, noise=0.35):
+    """Synthetic EarlyFusion block features (what EarlyFusion.load_features returns,
+    acoss/algorithms/earlyfusion_traile.py:67-154): per track a dict with
+    'mfccs' (n_blocks, 50*n_mfcc), 'ssms' (n_blocks, 1225), 'chromas' (n_blocks, 480) float32 and
+    'chroma_med' (12,) float32.  Covers of a work share a latent block sequence (random start offset,
+    additive noise, random key shift of the chroma blocks)."""
+    rng = np.random.default_rng(seed)
+    d_m, d_s, d_c = 50 * n_mfcc, 1225, 480
+    labels, works, tids, feats = [], [], [], []
+
+    def render(lat, nb, start, key):
+        m = lat["m"][start:start + nb] + noise * rng.standard_normal((nb, d_m))
+        m = m - m.mean(1, keepdims=True)
+        m = m / np.sqrt((m ** 2).sum(1, keepdims=True))
+        s = np.abs(lat["s"][start:start + nb] + noise * rng.standard_normal((nb, d_s)))
+        c = np.abs(lat["c"][start:start + nb] + 0.5 * noise * rng.standard_normal((nb, d_c)))
+        c = np.roll(c.reshape(nb, d_c // 12, 12), key, axis=2).reshape(nb, d_c)
+        med = np.roll(lat["med"] + 0.02 * rng.random(12), key)
+        return {"mfccs": m.astype(np.float32), "ssms": s.astype(np.float32), "chromas": c.astype(np.float32),
+                "chroma_med": med.astype(np.float32)}
+
+    def latent(length):
+        # slowly varying paths: neighbouring blocks overlap by 19 of 20 beats in the real features
+        def path(d, scale):
+            x = np.cumsum(rng.standard_normal((length, d)), 0) * scale
+            return x - x.mean(0, keepdims=True)
+        return {"m": path(d_m, 0.25), "s": path(d_s, 0.25) + 1.0, "c": np.abs(path(d_c, 0.2)) + 0.1,
+                "med": rng.random(12) + 0.2}
+
+    t = 0
+    for w in range(n_works + n_singletons):
+        n_cov = per_work if w < n_works else 1
+        lat = latent(nb_hi + 16)
+        for c in range(n_cov):
+            nb = int(rng.integers(nb_lo, nb_hi + 1))
+            start = int(rng.integers(0, 16))
+            key = int(rng.integers(0, 12))
+            feats.append(render(lat, nb, start, key))
+            labels.append("W_%d" % w)
+            works.append("W_%d" % w)
+            tids.append("P_%d" % t)
+            t += 1
+    return dict(labels=labels, work_ids=works, track_ids=tids, block_feats=feats)

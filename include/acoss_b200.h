@@ -224,6 +224,35 @@ int acoss_simple_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pair
 int acoss_ftm2d_allpairs(acoss_ctx *ctx, const double *shingles_host, int32_t n, int32_t d,
                          double *out_D_host);
 
+/* ---- EarlyFusionTralie ------------------------------------------------------------ */
+
+/* Uploads the blocked features of all tracks (what EarlyFusion.load_features returns,
+ * acoss/algorithms/earlyfusion_traile.py:67-154): 'mfccs' (n_blocks, d_mfcc), 'ssms' (n_blocks, d_ssm),
+ * 'chromas' (n_blocks, d_chroma = 12 * chromas_per_block), all float32 and concatenated over tracks;
+ * 'chroma_med' (n_tracks, 12) float32; block_offsets_host[n_tracks+1]. */
+int acoss_earlyfusion_upload(acoss_ctx *ctx, const float *mfccs_host, int32_t d_mfcc,
+                             const float *ssms_host, int32_t d_ssm,
+                             const float *chromas_host, int32_t d_chroma,
+                             const float *chroma_med_host, const int64_t *block_offsets_host,
+                             int32_t n_tracks);
+
+/* The body of EarlyFusion.similarity (earlyfusion_traile.py:157-198) for every pair (i, j):
+ * get_csm x2, get_csm_blocked_oti(get_csm_cosine), csm_to_binary(kappa), getWCSM(K, K), the early
+ * fusion exp(-sum W) and four smith_waterman_constrained scores.
+ * out_scores_host: (n_pairs, 4) float64 in the order mfccs, ssms, chromas, early. */
+int acoss_earlyfusion_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pairs,
+                            double kappa, int32_t K, double *out_scores_host);
+
+/* Test hook: the 3 CSMs + the early matrix (4, M, N) float32 and the 4 binary matrices (4, M, N)
+ * uint8 of one pair, plus its 4 scores. */
+int acoss_earlyfusion_pair_matrices(acoss_ctx *ctx, int32_t i, int32_t j, double kappa, int32_t K,
+                                    float *out_csm_host, uint8_t *out_bin_host,
+                                    double *out_scores_host);
+
+/* Device time (CUDA events) of the last acoss_earlyfusion_pairs call: out_ms3 = {CSM GEMMs,
+ * selection + W + early, Smith-Waterman}; GEMM flop; sum of M*N. */
+int acoss_earlyfusion_stats(acoss_ctx *ctx, double *out_ms3, double *out_flop, int64_t *out_cells);
+
 /* ---- plain device memory helpers for host languages without a CUDA binding -- */
 int acoss_dev_alloc(acoss_ctx *ctx, int64_t bytes, void **out_dev);
 int acoss_dev_free(acoss_ctx *ctx, void *dev);

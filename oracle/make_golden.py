@@ -231,6 +231,61 @@ def gen_simple_ftm(ns):
     np.savez_compressed(os.path.join(GOLD, "simple_ftm2d_reference.npz"), **out)
     print("simple_ftm2d_reference: simple MAP", out["simple_eval"][3], "ftm MAP", out["ftm_eval"][3])
 
+
+def early_dataset():
+    """Deterministic block features for the EarlyFusion goldens: 11 works x 2 + 2 singletons = 24 tracks
+    (K + 1 = 21 < N_t for the N x N fusion), 36-60 blocks each."""
+    from acoss_b200 import synth
+    ds = synth.make_block_features(11, 2, 2, 991, 36, 60)
+    ds["hpcp"] = [np.zeros((4, 12), np.float32) for _ in ds["labels"]]
+    ds["fac"] = 1
+    return ds
+
+
+def gen_early(ns):
+    from acoss_b200 import synth
+    ds = early_dataset()
+    out = {"checksum": np.array([float(np.sum(f["mfccs"], dtype=np.float64) + np.sum(f["chromas"], dtype=np.float64))
+                                 for f in ds["block_feats"]])}
+    with tempfile.TemporaryDirectory() as tmp:
+        fdir = synth.write_dataset(os.path.join(tmp, "feat"), ds, os.path.join(tmp, "ds.csv"))
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            e = quiet(ns.early.EarlyFusion, os.path.join(tmp, "ds.csv"), fdir, shortname="g")
+            for i, f in enumerate(ds["block_feats"]):
+                e.all_block_feats[i] = f
+            quiet(e.all_pairwise, 0, 1, True)
+            quiet(e.get_all_clique_ids)       # the injected block features bypass load_features' side effect
+            for s_ in ("mfccs", "ssms", "chromas", "early"):
+                out["D_" + s_] = np.array(e.Ds[s_])
+            # matrices of two pairs, straight from the reference's free functions
+            prs = [(0, 1), (5, 12)]
+            out["mat_pairs"] = np.array(prs, np.int32)
+            for k, (a, b) in enumerate(prs):
+                f1, f2 = ds["block_feats"][a], ds["block_feats"][b]
+                C = [ns.xrec.get_csm(f1["mfccs"], f2["mfccs"]), ns.xrec.get_csm(f1["ssms"], f2["ssms"]),
+                     ns.xrec.get_csm_blocked_oti(f1["chromas"], f2["chromas"], f1["chroma_med"], f2["chroma_med"], ns.xrec.get_csm_cosine)]
+                Ws = [ns.snf.getWCSM(c, e.K, e.K) for c in C]
+                Wsum = np.zeros_like(C[0])
+                for w in Ws:
+                    Wsum += w
+                C.append(np.exp(-Wsum))
+                out["csm%d" % k] = np.stack(C).astype(np.float32)
+                out["bin%d" % k] = np.stack([np.asarray(ns.xrec.csm_to_binary(c, e.kappa).toarray() if hasattr(ns.xrec.csm_to_binary(c, e.kappa), "toarray")
+                                                        else ns.xrec.csm_to_binary(c, e.kappa)) for c in C]).astype(np.uint8)
+                out["oti%d" % k] = np.array(ns.xrec.get_oti(f1["chroma_med"], f2["chroma_med"]))
+            with np.errstate(all="ignore"):
+                quiet(e.do_late_fusion)
+            out["D_late"] = np.array(e.Ds["late"])
+            out["D_early+late"] = np.array(e.Ds["early+late"])
+            for s_ in ("mfccs", "ssms", "chromas", "early", "late", "early+late"):
+                out["eval_" + s_] = np.array(list(quiet(e.getEvalStatistics, s_)[:4]), np.float64)
+        finally:
+            os.chdir(cwd)
+    np.savez_compressed(os.path.join(GOLD, "earlyfusion_reference.npz"), **out)
+    print("earlyfusion_reference: MAP", {s_: float(out["eval_" + s_][3]) for s_ in ("mfccs", "ssms", "chromas", "early", "late", "early+late")})
+
 def gen_percentile():
     from oracle import oracle as O
     rng = np.random.default_rng(5)
@@ -256,6 +311,7 @@ def main():
     gen_snf(ns)
     gen_serra(ns)
     gen_simple_ftm(ns)
+    gen_early(ns)
 
 
 if __name__ == "__main__":

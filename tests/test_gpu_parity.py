@@ -503,3 +503,68 @@ def test_simple_and_ftm2d_classes_and_benchmark(golden, workdir):
     f.all_pairwise(1, symmetric=True)
     assert np.array_equal(np.array(f.Ds["main"]), g["ftm_D"])
     f.cleanup_memmap()
+
+
+# ---- EarlyFusionTralie -----------------------------------------------------------------------
+def _early_dataset(workdir):
+    from acoss_b200 import synth
+    from oracle.make_golden import early_dataset
+    ds = early_dataset()
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"))
+    return str(workdir / "ds.csv"), fdir, ds
+
+
+def test_earlyfusion_pair_matrices_vs_reference_golden(ctx, golden):
+    """CSMs / early matrix (float32) and the four binary matrices of two pairs against the reference's
+    free functions run verbatim.  The GEMM summation order differs from numpy's BLAS, so the float
+    matrices agree to float32 rounding; the binary matrices must then be identical (seeded data has no
+    near-ties at the k-th neighbour)."""
+    from oracle.make_golden import early_dataset
+    g = golden("earlyfusion_reference.npz")
+    ds = early_dataset()
+    assert np.array_equal([float(np.sum(f["mfccs"], dtype=np.float64) + np.sum(f["chromas"], dtype=np.float64))
+                           for f in ds["block_feats"]], g["checksum"])
+    ctx.earlyfusion_upload(ds["block_feats"])
+    for k, (a, b) in enumerate(g["mat_pairs"]):
+        csm, bn, sc = ctx.earlyfusion_pair_matrices(int(a), int(b), kappa=0.1, K=10)
+        np.testing.assert_allclose(csm[:3], g["csm%d" % k][:3], rtol=2e-5, atol=2e-6)
+        np.testing.assert_allclose(csm[3], g["csm%d" % k][3], rtol=1e-4, atol=1e-6)
+        assert np.array_equal(bn.sum(2), g["bin%d" % k].sum(2))          # exactly k ones per row
+        mism = int((bn != g["bin%d" % k]).sum())
+        assert mism == 0, "binary matrices differ in %d cells" % mism
+        assert sc.astype(np.float32).tolist() == [g["D_" + s][a, b] for s in ("mfccs", "ssms", "chromas", "early")]
+
+
+def test_earlyfusion_class_matches_reference_golden(golden, workdir):
+    import acoss_b200
+    g = golden("earlyfusion_reference.npz")
+    csv, fdir, ds = _early_dataset(workdir)
+    e = acoss_b200.EarlyFusion(csv, fdir, shortname="g")
+    for i, f in enumerate(ds["block_feats"]):
+        e.set_block_features(i, f)
+    e.all_pairwise(1, symmetric=True)
+    for s in ("mfccs", "ssms", "chromas", "early"):
+        assert np.array_equal(np.array(e.Ds[s]), g["D_" + s]), s
+    e.do_late_fusion()
+    for s in ("late", "early+late"):
+        np.testing.assert_allclose(np.array(e.Ds[s]), g["D_" + s], rtol=2e-5, atol=1e-9)
+    for s in ("mfccs", "ssms", "chromas", "early", "late", "early+late"):
+        assert list(e.getEvalStatistics(s)[:4]) == g["eval_" + s].tolist()
+    e.cleanup_memmap()
+    # the reference's cache files now exist: the benchmark entry point runs from them (both names, SURVEY Q1)
+    res = acoss_b200.benchmark(csv, fdir, algorithm="EarlyFusionTraile", shortname="g")
+    assert list(res["early+late"][:4]) == g["eval_early+late"].tolist()
+
+
+def test_earlyfusion_errors(ctx):
+    import acoss_b200
+    from acoss_b200 import synth
+    ds = synth.make_block_features(1, 2, 0, 3, 12, 14)
+    ctx.earlyfusion_upload(ds["block_feats"])
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.earlyfusion_pairs(np.array([[0, 5]], np.int32))
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.earlyfusion_pairs(np.array([[0, 1]], np.int32), kappa=100)       # kth out of bounds
+    sc = ctx.earlyfusion_pairs(np.array([[0, 1]], np.int32), kappa=0)         # kappa = 0: all ones
+    M, N = ds["block_feats"][0]["mfccs"].shape[0], ds["block_feats"][1]["mfccs"].shape[0]
+    assert sc[0].tolist() == [float(min(M, N) - 3)] * 4
