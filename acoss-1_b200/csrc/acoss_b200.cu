@@ -51,7 +51,7 @@ struct acoss_ctx {
     std::vector<int64_t> h_offs;      // frame offsets
     std::vector<int32_t> h_emb;       // embedded rows per track
     std::vector<int64_t> h_sd_off;    // self-dot table offsets
-    DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma;
+    DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma, d_fnorm;
     // SiMPle feature store (frame-major float64) + per-track chroma profiles
     int sp_tracks = 0;
     std::vector<int64_t> sp_offs;
@@ -118,7 +118,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
-                      &ctx->d_gchroma, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
+                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
                       &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
@@ -194,6 +194,7 @@ extern "C" int acoss_upload_tracks(acoss_ctx* ctx, const float* frames_host, con
     RESERVE(ctx->d_sd_off, sizeof(int64_t) * (n_tracks + 1));
     RESERVE(ctx->d_selfdot, sizeof(float) * (size_t)std::max<int64_t>(sd, 1));
     RESERVE(ctx->d_gchroma, sizeof(float) * ACOSS_NBINS * n_tracks);
+    RESERVE(ctx->d_fnorm, sizeof(float2) * (size_t)std::max<int64_t>(total, 1));
     cudaStream_t st = ctx->stream;
     CK(cudaMemcpyAsync(ctx->d_frames.p, frames_host, sizeof(float) * ACOSS_NBINS * (size_t)total, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(ctx->d_offs.p, ctx->h_offs.data(), sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st));
@@ -204,6 +205,10 @@ extern "C" int acoss_upload_tracks(acoss_ctx* ctx, const float* frames_host, con
         int blocks = (n_tracks + warps_per_block - 1) / warps_per_block;
         global_chroma_kernel<<<blocks, threads, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(),
                                                          n_tracks, ctx->d_gchroma.as<float>());
+        CK_LAUNCH();
+    }
+    if (total > 0) {
+        tc_frame_norm_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(ctx->d_frames.as<float>(), total, ctx->d_fnorm.as<float2>());
         CK_LAUNCH();
     }
     if (max_emb > 0) {

@@ -30,6 +30,7 @@
 #pragma once
 #include "common.cuh"
 #include "kernels_crp.cuh"
+#include "kernels_crp_tc.cuh"
 
 #define BAND_RS 16                    // strip rows
 #define BAND_GR (BAND_RS + 8)         // G rows per strip
@@ -87,6 +88,12 @@ __device__ __forceinline__ float fkey_inv(uint32_t k)
 //   yyB [NBpad]  exact self dots of all side-B rows; later: lower band edges of the column thresholds
 //   Gs  [24*512] skewed G2 tile; later: per-warp scratch; later: upper band edges + ambiguity list
 //   V   [16*NBpad]
+//
+// TC = 1: the G2 tiles come from the tensor cores (kernels_crp_tc.cuh); shared memory additionally holds the
+// strip operand OpA, one mbarrier and the TMEM base address behind V; the Gs region doubles as the side-B
+// operand buffer OpB.  `fnorm` = per-frame |f|^2 split (tc_frame_norm_kernel).
+#define TC_ND (TC_TW - BAND_GR + 1)      // complete diagonals per tensor-core tile (233)
+template <int TC>
 __global__ void __launch_bounds__(BAND_THREADS, 1)
 crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                       const StripTask* __restrict__ tasks, int n_tasks,
@@ -94,7 +101,7 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                       const float* __restrict__ selfdot,
                       float* __restrict__ thr, uint8_t* __restrict__ crp,
                       int side_a_is_query, float qf, int NBpad,
-                      unsigned long long* __restrict__ counters)
+                      unsigned long long* __restrict__ counters, const float2* __restrict__ fnorm)
 {
     extern __shared__ __align__(16) float smem[];
     float* Afr = smem;
@@ -107,6 +114,20 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
     float* V = Gs + BAND_GR * BAND_TW;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_exact = 0;
+    // tensor-core state
+    unsigned char* OpB = reinterpret_cast<unsigned char*>(Gs);
+    unsigned char* OpA = reinterpret_cast<unsigned char*>(V + (size_t)BAND_RS * NBpad);
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(OpA + TC_OPA_BYTES);
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 1);
+    uint32_t tmem_base = 0, mma_phase = 0;
+    if (TC) {
+        if (warp == 0) tmem_alloc(tmem_holder);
+        if (tid == 0) { mbar_init(mbar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        tmem_base = *tmem_holder;
+    }
 
     for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
         const StripTask tk = tasks[task];
@@ -160,76 +181,173 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
         if (!tiny) {
             // ---- approximate radicands of the strip: sliding Gram over column tiles
             const bool full_rows = (tk.nrows == BAND_RS);
-            for (int b0 = -(BAND_RS - 1); b0 < NB; b0 += BAND_ND) {
-                // phase 1: thread (h, t) = (tid >> 8, tid & 255) owns G2 columns b0 + t and b0 + t + 256 for the
-                // A rows [12 h, 12 h + 12): every broadcast A load feeds two columns
-                {
-                    const int t = tid & 255, a_base = (tid >> 8) * (BAND_GR / 2);
-                    float B0[ACOSS_NBINS], B1[ACOSS_NBINS];
-                    const int c0 = b0 + t, c1 = c0 + 256;
-                    const bool v0 = (c0 >= 0 && c0 < nb_frames), v1 = (c1 >= 0 && c1 < nb_frames);
-                    const float4* p0 = reinterpret_cast<const float4*>(frames + (b_f0 + (v0 ? c0 : 0)) * ACOSS_NBINS);
-                    const float4* p1 = reinterpret_cast<const float4*>(frames + (b_f0 + (v1 ? c1 : 0)) * ACOSS_NBINS);
-#pragma unroll
-                    for (int q = 0; q < 3; ++q) {
-                        const float4 x = v0 ? __ldg(p0 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-                        const float4 y = v1 ? __ldg(p1 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-                        B0[4 * q] = x.x; B0[4 * q + 1] = x.y; B0[4 * q + 2] = x.z; B0[4 * q + 3] = x.w;
-                        B1[4 * q] = y.x; B1[4 * q + 1] = y.y; B1[4 * q + 2] = y.z; B1[4 * q + 3] = y.w;
-                    }
-                    float ff0 = 0.f, ff1 = 0.f;
-#pragma unroll
-                    for (int q = 0; q < ACOSS_NBINS; ++q) { ff0 = fmaf(B0[q], B0[q], ff0); ff1 = fmaf(B1[q], B1[q], ff1); }
-#pragma unroll
-                    for (int aa = 0; aa < BAND_GR / 2; ++aa) {
-                        const int a = a_base + aa;
-                        const float4* ap = reinterpret_cast<const float4*>(Afr + a * BAND_AFS);
-                        const float4 x0 = ap[0], x1 = ap[1], x2 = ap[2], x3 = ap[3];
-                        float g0 = x3.x + ff0, g1 = x3.x + ff1;       // |f_a|^2 + |f_b|^2
-                        g0 = fmaf(x0.x, B0[0], g0); g1 = fmaf(x0.x, B1[0], g1);
-                        g0 = fmaf(x0.y, B0[1], g0); g1 = fmaf(x0.y, B1[1], g1);
-                        g0 = fmaf(x0.z, B0[2], g0); g1 = fmaf(x0.z, B1[2], g1);
-                        g0 = fmaf(x0.w, B0[3], g0); g1 = fmaf(x0.w, B1[3], g1);
-                        g0 = fmaf(x1.x, B0[4], g0); g1 = fmaf(x1.x, B1[4], g1);
-                        g0 = fmaf(x1.y, B0[5], g0); g1 = fmaf(x1.y, B1[5], g1);
-                        g0 = fmaf(x1.z, B0[6], g0); g1 = fmaf(x1.z, B1[6], g1);
-                        g0 = fmaf(x1.w, B0[7], g0); g1 = fmaf(x1.w, B1[7], g1);
-                        g0 = fmaf(x2.x, B0[8], g0); g1 = fmaf(x2.x, B1[8], g1);
-                        g0 = fmaf(x2.y, B0[9], g0); g1 = fmaf(x2.y, B1[9], g1);
-                        g0 = fmaf(x2.z, B0[10], g0); g1 = fmaf(x2.z, B1[10], g1);
-                        g0 = fmaf(x2.w, B0[11], g0); g1 = fmaf(x2.w, B1[11], g1);
-                        // Gs[a][(col - a) mod 512], col = t and t + 256
-                        Gs[a * BAND_TW + ((t - a) & (BAND_TW - 1))] = g0;
-                        Gs[a * BAND_TW + ((t + 256 - a) & (BAND_TW - 1))] = g1;
-                    }
+            if (TC) {
+                // ---- strip operand OpA[slice][chunk][row][4]: built once per task
+                for (int e = tid; e < TC_SLICES * 2 * TC_NROWS; e += BAND_THREADS) {
+                    const int n = e & (TC_NROWS - 1), ch = (e >> 5) & 1, sl = e >> 6;
+                    const bool valid = n < BAND_GR && (tk.row0 + n) < na_frames;
+                    const float* ar = Afr + (n < BAND_GR ? n : 0) * BAND_AFS;
+                    float4 o;
+                    o.x = tc_opa_elem(ar, sl, 4 * ch + 0, valid);
+                    o.y = tc_opa_elem(ar, sl, 4 * ch + 1, valid);
+                    o.z = tc_opa_elem(ar, sl, 4 * ch + 2, valid);
+                    o.w = tc_opa_elem(ar, sl, 4 * ch + 3, valid);
+                    *reinterpret_cast<float4*>(OpA + (size_t)e * 16) = o;
                 }
-                __syncthreads();
-                // phase 2: diagonal delta = tid
-                if (tid < BAND_ND) {
-                    float g[BAND_GR];
+                const float* fr_b = frames + b_f0 * ACOSS_NBINS;
+                const float2* fn_b = fnorm + b_f0;
+                for (int b0 = -(BAND_RS - 1); b0 < NB; b0 += TC_ND) {
+                    // side-B operand rows of frames b0 .. b0 + 255: hi / lo split of the raw bins, norm chunk, zero chunk
+                    for (int e = tid; e < TC_TW * ACOSS_NBINS; e += BAND_THREADS) {
+                        const int fl = e / ACOSS_NBINS, c = e - fl * ACOSS_NBINS;
+                        const int col = b0 + fl;
+                        float x = 0.f;
+                        if (col >= 0 && col < nb_frames) x = __ldg(fr_b + (int64_t)col * ACOSS_NBINS + c);
+                        float hi, lo;
+                        tf32_split(x, hi, lo);
+                        const int q = fl >> 7, m = fl & (TC_BLK - 1);
+                        float* rowp = reinterpret_cast<float*>(OpB + (size_t)q * (TC_CHUNKS * TC_BLK * 16) + (size_t)m * 16) + (c & 3);
+                        rowp[(c >> 2) * (TC_BLK * 4)] = hi;
+                        rowp[(3 + (c >> 2)) * (TC_BLK * 4)] = lo;
+                    }
+                    if (tid < TC_TW) {
+                        const int col = b0 + tid;
+                        float2 nn = make_float2(0.f, 0.f);
+                        if (col >= 0 && col < nb_frames) nn = __ldg(fn_b + col);
+                        const int q = tid >> 7, m = tid & (TC_BLK - 1);
+                        float4* rowp = reinterpret_cast<float4*>(OpB + (size_t)q * (TC_CHUNKS * TC_BLK * 16) + (size_t)m * 16);
+                        rowp[6 * TC_BLK] = make_float4(1.f, 1.f, nn.x, nn.y);
+                        rowp[7 * TC_BLK] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    fence_proxy_async_smem();
+                    tc_fence_before();
+                    __syncthreads();
+                    if (tid == 0) {
+                        tc_fence_after();
+                        const uint32_t a_base = smem_u32(OpB), b_base = smem_u32(OpA);
 #pragma unroll
-                    for (int a = 0; a < BAND_GR; ++a) g[a] = Gs[a * BAND_TW + tid];
-                    float t2[BAND_GR - 1], t4[BAND_GR - 3], t8[BAND_GR - 7];
+                        for (int q = 0; q < 2; ++q)
 #pragma unroll
-                    for (int a = 0; a < BAND_GR - 1; ++a) t2[a] = g[a] + g[a + 1];
+                            for (int sl = 0; sl < TC_SLICES; ++sl) {
+                                const int c0 = (sl < 4) ? 2 * sl : 2 * (sl - 4);      // A-operand chunk pair of this slice
+                                const uint64_t ad = umma_desc(a_base + (uint32_t)((q * TC_CHUNKS + c0) * TC_BLK * 16), TC_BLK * 16, 128);
+                                const uint64_t bd = umma_desc(b_base + (uint32_t)(sl * 2 * TC_NROWS * 16), TC_NROWS * 16, 128);
+                                umma_tf32(tmem_base + (uint32_t)(q * TC_NROWS), ad, bd, sl > 0 ? 1u : 0u);
+                            }
+                        umma_commit(mbar);
+                    }
+                    mbar_wait(mbar, mma_phase);
+                    mma_phase ^= 1u;
+                    tc_fence_after();
+                    // TMEM -> skewed G2 tile: warp w reads lane quarter w & 3 of block (w >> 2) & 1, strip rows 12 (w >> 3) ..
+                    {
+                        const int quarter = warp & 3, q = (warp >> 2) & 1, half = warp >> 3;
+                        float v[16];
+                        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(q * TC_NROWS + half * 12), v);
+                        const int bl = q * TC_BLK + quarter * 32 + lane;          // column within the tile
 #pragma unroll
-                    for (int a = 0; a < BAND_GR - 3; ++a) t4[a] = t2[a] + t2[a + 2];
-#pragma unroll
-                    for (int a = 0; a < BAND_GR - 7; ++a) t8[a] = t4[a] + t4[a + 4];
-                    const int jb = b0 + tid;                       // column of row 0 on this diagonal
-                    float* vp = V + jb;
-                    if (full_rows && jb >= 0 && jb + BAND_RS <= NB) {
-#pragma unroll
-                        for (int i = 0; i < BAND_RS; ++i) vp[i * (NBpad + 1)] = t8[i] + g[i + 8];
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < BAND_RS; ++i) {
-                            const int j = jb + i;
-                            if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[i] + g[i + 8];
+                        for (int aa = 0; aa < 12; ++aa) {
+                            const int a = half * 12 + aa;
+                            Gs[a * TC_TW + ((bl - a) & (TC_TW - 1))] = v[aa];
                         }
                     }
+                    tc_fence_before();
+                    __syncthreads();
+                    // diagonal window sums: thread (delta, h) -> rows 8 h .. 8 h + 7 of diagonal delta
+                    if (tid < 2 * TC_ND) {
+                        const int h = tid >= TC_ND ? 1 : 0, dl = tid - h * TC_ND;
+                        float g[16];
+#pragma unroll
+                        for (int a = 0; a < 16; ++a) g[a] = Gs[(8 * h + a) * TC_TW + dl];
+                        float t2[15], t4[13], t8[9];
+#pragma unroll
+                        for (int a = 0; a < 15; ++a) t2[a] = g[a] + g[a + 1];
+#pragma unroll
+                        for (int a = 0; a < 13; ++a) t4[a] = t2[a] + t2[a + 2];
+#pragma unroll
+                        for (int a = 0; a < 9; ++a) t8[a] = t4[a] + t4[a + 4];
+                        const int jb = b0 + dl;
+                        float* vp = V + jb;
+#pragma unroll
+                        for (int ii = 0; ii < 8; ++ii) {
+                            const int i = 8 * h + ii, j = jb + i;
+                            if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[ii] + g[ii + 8];
+                        }
+                    }
+                    __syncthreads();
                 }
-                __syncthreads();
+            } else {
+                for (int b0 = -(BAND_RS - 1); b0 < NB; b0 += BAND_ND) {
+                    // phase 1: thread (h, t) = (tid >> 8, tid & 255) owns G2 columns b0 + t and b0 + t + 256 for the
+                    // A rows [12 h, 12 h + 12): every broadcast A load feeds two columns
+                    {
+                        const int t = tid & 255, a_base = (tid >> 8) * (BAND_GR / 2);
+                        float B0[ACOSS_NBINS], B1[ACOSS_NBINS];
+                        const int c0 = b0 + t, c1 = c0 + 256;
+                        const bool v0 = (c0 >= 0 && c0 < nb_frames), v1 = (c1 >= 0 && c1 < nb_frames);
+                        const float4* p0 = reinterpret_cast<const float4*>(frames + (b_f0 + (v0 ? c0 : 0)) * ACOSS_NBINS);
+                        const float4* p1 = reinterpret_cast<const float4*>(frames + (b_f0 + (v1 ? c1 : 0)) * ACOSS_NBINS);
+    #pragma unroll
+                        for (int q = 0; q < 3; ++q) {
+                            const float4 x = v0 ? __ldg(p0 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            const float4 y = v1 ? __ldg(p1 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            B0[4 * q] = x.x; B0[4 * q + 1] = x.y; B0[4 * q + 2] = x.z; B0[4 * q + 3] = x.w;
+                            B1[4 * q] = y.x; B1[4 * q + 1] = y.y; B1[4 * q + 2] = y.z; B1[4 * q + 3] = y.w;
+                        }
+                        float ff0 = 0.f, ff1 = 0.f;
+    #pragma unroll
+                        for (int q = 0; q < ACOSS_NBINS; ++q) { ff0 = fmaf(B0[q], B0[q], ff0); ff1 = fmaf(B1[q], B1[q], ff1); }
+    #pragma unroll
+                        for (int aa = 0; aa < BAND_GR / 2; ++aa) {
+                            const int a = a_base + aa;
+                            const float4* ap = reinterpret_cast<const float4*>(Afr + a * BAND_AFS);
+                            const float4 x0 = ap[0], x1 = ap[1], x2 = ap[2], x3 = ap[3];
+                            float g0 = x3.x + ff0, g1 = x3.x + ff1;       // |f_a|^2 + |f_b|^2
+                            g0 = fmaf(x0.x, B0[0], g0); g1 = fmaf(x0.x, B1[0], g1);
+                            g0 = fmaf(x0.y, B0[1], g0); g1 = fmaf(x0.y, B1[1], g1);
+                            g0 = fmaf(x0.z, B0[2], g0); g1 = fmaf(x0.z, B1[2], g1);
+                            g0 = fmaf(x0.w, B0[3], g0); g1 = fmaf(x0.w, B1[3], g1);
+                            g0 = fmaf(x1.x, B0[4], g0); g1 = fmaf(x1.x, B1[4], g1);
+                            g0 = fmaf(x1.y, B0[5], g0); g1 = fmaf(x1.y, B1[5], g1);
+                            g0 = fmaf(x1.z, B0[6], g0); g1 = fmaf(x1.z, B1[6], g1);
+                            g0 = fmaf(x1.w, B0[7], g0); g1 = fmaf(x1.w, B1[7], g1);
+                            g0 = fmaf(x2.x, B0[8], g0); g1 = fmaf(x2.x, B1[8], g1);
+                            g0 = fmaf(x2.y, B0[9], g0); g1 = fmaf(x2.y, B1[9], g1);
+                            g0 = fmaf(x2.z, B0[10], g0); g1 = fmaf(x2.z, B1[10], g1);
+                            g0 = fmaf(x2.w, B0[11], g0); g1 = fmaf(x2.w, B1[11], g1);
+                            // Gs[a][(col - a) mod 512], col = t and t + 256
+                            Gs[a * BAND_TW + ((t - a) & (BAND_TW - 1))] = g0;
+                            Gs[a * BAND_TW + ((t + 256 - a) & (BAND_TW - 1))] = g1;
+                        }
+                    }
+                    __syncthreads();
+                    // phase 2: diagonal delta = tid
+                    if (tid < BAND_ND) {
+                        float g[BAND_GR];
+    #pragma unroll
+                        for (int a = 0; a < BAND_GR; ++a) g[a] = Gs[a * BAND_TW + tid];
+                        float t2[BAND_GR - 1], t4[BAND_GR - 3], t8[BAND_GR - 7];
+    #pragma unroll
+                        for (int a = 0; a < BAND_GR - 1; ++a) t2[a] = g[a] + g[a + 1];
+    #pragma unroll
+                        for (int a = 0; a < BAND_GR - 3; ++a) t4[a] = t2[a] + t2[a + 2];
+    #pragma unroll
+                        for (int a = 0; a < BAND_GR - 7; ++a) t8[a] = t4[a] + t4[a + 4];
+                        const int jb = b0 + tid;                       // column of row 0 on this diagonal
+                        float* vp = V + jb;
+                        if (full_rows && jb >= 0 && jb + BAND_RS <= NB) {
+    #pragma unroll
+                            for (int i = 0; i < BAND_RS; ++i) vp[i * (NBpad + 1)] = t8[i] + g[i + 8];
+                        } else {
+    #pragma unroll
+                            for (int i = 0; i < BAND_RS; ++i) {
+                                const int j = jb + i;
+                                if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[i] + g[i + 8];
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
             }
         }
         if (tid == 0) ph2 = clock64();
@@ -575,4 +693,9 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
     }
     for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o);
     if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
+    if (TC) {
+        tc_fence_before();
+        __syncthreads();
+        if (warp == 0) tmem_free(tmem_base);
+    }
 }
