@@ -368,7 +368,7 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
             long long tc0 = 0, tc1 = 0, tc2 = 0, tc3 = 0, tc4 = 0;
             if (!exact_row) {
                 if (prof) tc0 = clock64();
-                // (a) sample (registers) -> two pivots bracketing the wanted order statistics
+                // (a) sample (registers): 16 values per lane, evenly spread over the row
                 float sm[BAND_SPL];
                 float smin = INFINITY, smax = -INFINITY;
 #pragma unroll
@@ -381,35 +381,61 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                     smin = fminf(smin, __shfl_xor_sync(0xffffffffu, smin, o));
                     smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, o));
                 }
+                // (b) 512-bin histogram of the sample (per-warp shared scratch, two 16-bit counters per word) ->
+                //     pivots at bin edges.  Pivots only need to be roughly right: pass A below verifies the bracket.
+                unsigned* hist = reinterpret_cast<unsigned*>(stage);
+                const float hscale = (smax > smin) ? 512.0f / (smax - smin) : 0.0f;
+                const float hwidth = (smax - smin) * (1.0f / 512.0f);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) hist[q * 32 + lane] = 0u;
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < BAND_SPL; ++q) {
+                    const int bin = min(511, (int)((sm[q] - smin) * hscale));
+                    atomicAdd(&hist[bin >> 1], 1u << (16 * (bin & 1)));
+                }
+                __syncwarp();
+                int hc[16], hpre;                        // lane owns bins 16 lane .. 16 lane + 15
+                {
+                    const uint4 h0 = *reinterpret_cast<const uint4*>(hist + 8 * lane);
+                    const uint4 h1 = *reinterpret_cast<const uint4*>(hist + 8 * lane + 4);
+                    const unsigned hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+                    int tot = 0;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) { hc[2 * q] = hw[q] & 0xffffu; hc[2 * q + 1] = hw[q] >> 16; tot += hc[2 * q] + hc[2 * q + 1]; }
+                    int incl = tot;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                    hpre = incl - tot;                   // samples in bins < 16 lane
+                }
                 const float frac = ((float)pr.lo + 0.5f) / (float)NB;
                 const float rs = frac * (float)BAND_SAMPLE;
                 const float sg = sqrtf(fmaxf(rs * (1.0f - frac), 1.0f));
                 bool ok = false;
                 int c_a = 0, c_ab = 0;
                 float pa = -INFINITY, pb = INFINITY;
-                uint32_t key[BAND_LPL];
                 for (int attempt = 0; attempt < 2 && !ok; ++attempt) {
                     const float ns = attempt == 0 ? 2.0f : 4.0f;
-                    const int r_lo = (int)floorf(rs - ns * sg) - 1;       // sample ranks of the two pivots
+                    const int r_lo = (int)floorf(rs - ns * sg) - 1;       // sample ranks the bracket must enclose
                     const int r_hi = (int)ceilf(rs + ns * sg) + 1;
-                    pa = -INFINITY; pb = INFINITY;
-                    if (r_lo >= 0 || r_hi < BAND_SAMPLE) {
-                        // value bisection on the sample, both pivots at once, counts packed in one REDUX
-                        float la = smin, ha = smax, lb = smin, hb = smax;
-                        for (int it = 0; it < 8; ++it) {
-                            const float ma = 0.5f * (la + ha), mb = 0.5f * (lb + hb);
-                            int cc = 0;
+                    // pa = lower edge of the last bin b with #(samples in bins < b) <= r_lo;
+                    // pb = upper edge of the first bin b with #(samples in bins <= b) > r_hi
+                    int ba = -1, bb = 512;
+                    {
+                        int run = hpre;
 #pragma unroll
-                            for (int q = 0; q < BAND_SPL; ++q) cc += (sm[q] < ma ? 1 : 0) + (sm[q] < mb ? 65536 : 0);
-                            cc = __reduce_add_sync(0xffffffffu, cc);
-                            if ((cc & 0xffff) <= r_lo) la = ma; else ha = ma;      // want #(< pa) <= r_lo
-                            if ((cc >> 16) <= r_hi) lb = mb; else hb = mb;          // want #(< pb) >  r_hi
+                        for (int q = 0; q < 16; ++q) {
+                            if (run <= r_lo) ba = 16 * lane + q;
+                            run += hc[q];
+                            if (run > r_hi && bb == 512) bb = 16 * lane + q;
                         }
-                        if (r_lo >= 0) pa = la;
-                        if (r_hi < BAND_SAMPLE) pb = hb;
+                        ba = __reduce_max_sync(0xffffffffu, ba);
+                        bb = __reduce_min_sync(0xffffffffu, bb);
                     }
+                    pa = (r_lo >= 0 && ba > 0) ? smin + (float)ba * hwidth : -INFINITY;
+                    pb = (r_hi < BAND_SAMPLE && bb < 511) ? smin + (float)(bb + 1) * hwidth : INFINITY;
                     if (prof && attempt == 0) tc1 = clock64();
-                    // (b) pass A: per-lane counts, 8 loads in flight
+                    // (c) pass A: per-lane counts, 8 loads in flight
                     int ca_l = 0, cb_l = 0;
                     int j = lane;
                     for (; j + 7 * 32 < NB; j += 8 * 32) {
@@ -443,110 +469,122 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                     __syncwarp();
                 }
                 if (prof) tc2 = clock64();
-                float t_lo = 0.f, t_hi = 0.f;
+                float w_lo = 0.f, w_hi = 0.f;
+                float lv[BAND_LPL];
                 if (ok) {
-                    // (c) approximate order statistics inside the list: keys in registers, bitwise bisection
-                    //     restricted to the bits in which the list's keys can differ
-                    uint32_t kmin = 0xffffffffu, kmax = 0u;
+                    // (d) shrink [w_lo, w_hi) by value bisection inside the list while it keeps both wanted order
+                    //     statistics (ranks kk and kk + need2 - 1 of the list), until it holds few elements
+                    float vmin = INFINITY, vmax = -INFINITY;
 #pragma unroll
                     for (int q = 0; q < BAND_LPL; ++q) {
                         const int e = q * 32 + lane;
-                        key[q] = (e < c_ab) ? fkey(lval[e]) : 0xffffffffu;
-                        if (e < c_ab) { kmin = min(kmin, key[q]); kmax = max(kmax, key[q]); }
+                        lv[q] = (e < c_ab) ? lval[e] : INFINITY;
+                        if (e < c_ab) { vmin = fminf(vmin, lv[q]); vmax = fmaxf(vmax, lv[q]); }
                     }
-                    kmin = __reduce_min_sync(0xffffffffu, kmin);
-                    kmax = __reduce_max_sync(0xffffffffu, kmax);
-                    const uint32_t dif = kmin ^ kmax;
-                    const int top = dif ? (31 - __clz(dif)) : -1;
-                    const int kk = pr.lo - c_a;
-                    uint32_t ans = (top >= 31) ? 0u : (kmin & ~(((top >= 0) ? (2u << top) : 1u) - 1u));
-                    for (int bit = top; bit >= 0; --bit) {
-                        const uint32_t cand = ans | (1u << bit);
-                        int cnt = 0;
+                    for (int o = 16; o > 0; o >>= 1) {
+                        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+                        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+                    }
+                    const int kk = pr.lo - c_a;                     // rank of the lower wanted order statistic inside the list
+                    w_lo = vmin; w_hi = INFINITY;                   // invariant: #(list < w_lo) <= kk < #(list < w_hi)
+                    int c_lo = 0, c_hi = c_ab;
+                    float b_hi = vmax;                              // finite upper end used for the midpoint
+                    for (int it = 0; it < 24 && c_hi - c_lo > 3; ++it) {
+                        const float mid = 0.5f * (w_lo + b_hi);
+                        if (!(mid > w_lo) || !(mid < b_hi)) break;
+                        int cm = 0;
 #pragma unroll
-                        for (int q = 0; q < BAND_LPL; ++q) cnt += (key[q] < cand);
-                        cnt = __reduce_add_sync(0xffffffffu, cnt);
-                        if (cnt <= kk) ans = cand;
+                        for (int q = 0; q < BAND_LPL; ++q) cm += (lv[q] < mid);
+                        cm = __reduce_add_sync(0xffffffffu, cm);
+                        if (cm <= kk) { w_lo = mid; c_lo = cm; }
+                        else { w_hi = mid; b_hi = mid; c_hi = cm; }
                     }
-                    int cle = 0;
-                    uint32_t mgt = 0xffffffffu;
+                    // the upper wanted order statistic (rank kk + 1) is inside the window or is the smallest element >= w_hi
+                    if (pr.hi != pr.lo && c_hi < kk + 2) {
+                        float nx = INFINITY;
 #pragma unroll
-                    for (int q = 0; q < BAND_LPL; ++q) {
-                        cle += (key[q] <= ans);
-                        if (key[q] > ans && key[q] < mgt) mgt = key[q];
+                        for (int q = 0; q < BAND_LPL; ++q) if (lv[q] >= w_hi) nx = fminf(nx, lv[q]);
+                        for (int o = 16; o > 0; o >>= 1) nx = fminf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
+                        w_hi = nx;                                  // candidates up to and including nx (+ 2E)
                     }
-                    cle = __reduce_add_sync(0xffffffffu, cle);
-                    mgt = __reduce_min_sync(0xffffffffu, mgt);
-                    t_lo = fkey_inv(ans);
-                    t_hi = (pr.hi == pr.lo || cle >= kk + 2) ? t_lo : (mgt == 0xffffffffu ? INFINITY : fkey_inv(mgt));
-                    // the candidate window must lie strictly inside the list's value range
-                    ok = (t_lo - 2.0f * E > pa || pa == -INFINITY) && (t_hi + 2.0f * E < pb || pb == INFINITY) && (t_hi < INFINITY);
+                    // the candidate window (+- 2E) must lie strictly inside the list's value range [pa, pb)
+                    const float hi_edge = (w_hi == INFINITY) ? vmax : w_hi;
+                    ok = (w_lo - 2.0f * E > pa || pa == -INFINITY) && (hi_edge + 2.0f * E < pb || pb == INFINITY);
                 }
                 if (prof) tc3 = clock64();
                 if (ok) {
-                    // (d) gather every list element within 2E of the approximate order statistics
-                    const uint32_t kw_lo = fkey(t_lo - 2.0f * E), kw_hi = fkey(t_hi + 2.0f * E);
+                    // (e) candidates = list elements in [w_lo - 2E, w_hi + 2E]; every exact order statistic is among them
+                    const float c_min = w_lo - 2.0f * E;
+                    const float c_max = (w_hi == INFINITY) ? INFINITY : w_hi + 2.0f * E;
                     int n_below = c_a, n_c = 0;
 #pragma unroll
                     for (int q = 0; q < BAND_LPL; ++q) {
                         const int e = q * 32 + lane;
                         const bool valid = e < c_ab;
-                        const bool below = valid && key[q] < kw_lo;
-                        const bool cand = valid && !below && key[q] <= kw_hi;
+                        const bool below = valid && lv[q] < c_min;
+                        const bool cand = valid && !below && lv[q] <= c_max;
                         const int jj = valid ? lidx[e] : 0;
                         n_below += __popc(__ballot_sync(0xffffffffu, below));
                         const unsigned mc = __ballot_sync(0xffffffffu, cand);
                         __syncwarp();
                         // compact candidate columns to the front of lidx (slot <= e: nothing unread is overwritten)
-                        if (cand) lidx[n_c + __popc(mc & ((1u << lane) - 1u))] = jj;
+                        if (cand) { const int slot = n_c + __popc(mc & ((1u << lane) - 1u)); if (slot < 32) lidx[slot] = jj; }
                         n_c += __popc(mc);
                         __syncwarp();
                     }
                     const int kx = pr.lo - n_below;
                     if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) ok = false;
                     else {
-                        // exact values, two candidates per round.  Both operands are staged in the ORACLE's
-                        // element order (bin c of the oracle = staged bin (st + c) mod 12, see the staging rotation
-                        // above): the A row (108 floats, un-scaled) into lval (its keys live in registers by now),
-                        // the candidates' 9 B frames into `stage`; lane c then runs the 108-term chain.
+                        if (lane < n_c) {           // pull the candidates' 9 frames (432 B) towards L1 while the A row is staged
+                            const float* bp = frames + (b_f0 + lidx[lane]) * ACOSS_NBINS;
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) asm volatile("prefetch.global.L1 [%0];" ::"l"(bp + q * 32));
+                        }
+                        // exact values of all candidates at once, one per lane, in the ORACLE's element order: the A row
+                        // goes to lval (108 floats, un-scaled, oracle order); bin c of the oracle is bin (st + c) mod 12 of
+                        // both staged operands (see the staging rotation above); lane l walks the 108-term chain of its
+                        // candidate straight from the frame store.
                         const int st = side_a_is_query ? rot_a : 0;
                         for (int e = lane; e < 108; e += 32) {
                             const int s_ = e / ACOSS_NBINS, c = e - s_ * ACOSS_NBINS;
                             int cb = st + c; if (cb >= ACOSS_NBINS) cb -= ACOSS_NBINS;
                             lval[e] = -0.5f * Afr[(r + s_) * BAND_AFS + cb];       // exact: staged as -2 * a
                         }
+                        __syncwarp();
+                        int cbs[ACOSS_NBINS];
+#pragma unroll
+                        for (int c = 0; c < ACOSS_NBINS; ++c) { int cb = st + c; if (cb >= ACOSS_NBINS) cb -= ACOSS_NBINS; cbs[c] = cb; }
                         float dex = INFINITY;
-                        for (int c0 = 0; c0 < n_c; c0 += 2) {
-                            const int nc2 = min(2, n_c - c0);
-                            for (int e = lane; e < nc2 * 108; e += 32) {
-                                const int ci = e / 108, w = e - ci * 108;
-                                const int s_ = w / ACOSS_NBINS, c = w - s_ * ACOSS_NBINS;
-                                int cb = st + c; if (cb >= ACOSS_NBINS) cb -= ACOSS_NBINS;
-                                stage[e] = __ldg(frames + (b_f0 + lidx[c0 + ci] + s_) * ACOSS_NBINS + cb);
+                        if (lane < n_c) {
+                            const int jj = lidx[lane];
+                            const float* bp = frames + (b_f0 + jj) * ACOSS_NBINS;
+                            const float4* as = reinterpret_cast<const float4*>(lval);
+                            float acc = 0.0f;
+#pragma unroll 3
+                            for (int s_ = 0; s_ < 9; ++s_) {
+                                const float4 a0 = as[3 * s_], a1 = as[3 * s_ + 1], a2 = as[3 * s_ + 2];
+                                const float* bs = bp + s_ * ACOSS_NBINS;
+                                acc = xadd(acc, xmul(a0.x, __ldg(bs + cbs[0])));
+                                acc = xadd(acc, xmul(a0.y, __ldg(bs + cbs[1])));
+                                acc = xadd(acc, xmul(a0.z, __ldg(bs + cbs[2])));
+                                acc = xadd(acc, xmul(a0.w, __ldg(bs + cbs[3])));
+                                acc = xadd(acc, xmul(a1.x, __ldg(bs + cbs[4])));
+                                acc = xadd(acc, xmul(a1.y, __ldg(bs + cbs[5])));
+                                acc = xadd(acc, xmul(a1.z, __ldg(bs + cbs[6])));
+                                acc = xadd(acc, xmul(a1.w, __ldg(bs + cbs[7])));
+                                acc = xadd(acc, xmul(a2.x, __ldg(bs + cbs[8])));
+                                acc = xadd(acc, xmul(a2.y, __ldg(bs + cbs[9])));
+                                acc = xadd(acc, xmul(a2.z, __ldg(bs + cbs[10])));
+                                acc = xadd(acc, xmul(a2.w, __ldg(bs + cbs[11])));
                             }
-                            __syncwarp();
-                            if (lane >= c0 && lane < c0 + nc2) {
-                                const float4* bs = reinterpret_cast<const float4*>(stage + (lane - c0) * 108);
-                                const float4* as = reinterpret_cast<const float4*>(lval);
-                                float acc = 0.0f;
-#pragma unroll 9
-                                for (int q = 0; q < 27; ++q) {
-                                    const float4 av = as[q], bv = bs[q];
-                                    acc = xadd(acc, xmul(av.x, bv.x));
-                                    acc = xadd(acc, xmul(av.y, bv.y));
-                                    acc = xadd(acc, xmul(av.z, bv.z));
-                                    acc = xadd(acc, xmul(av.w, bv.w));
-                                }
-                                const int jj = lidx[lane];
-                                const float sa = xxA[r], sb = yyB[jj];
-                                const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
-                                float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
-                                if (item < 0.0f) item = 0.0f;
-                                dex = __fsqrt_rn(item);
-                                ++n_exact;
-                            }
-                            __syncwarp();
+                            const float sa = xxA[r], sb = yyB[jj];
+                            const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
+                            float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
+                            if (item < 0.0f) item = 0.0f;
+                            dex = __fsqrt_rn(item);
+                            ++n_exact;
                         }
+                        __syncwarp();
                         if (prof) tc4 = clock64();
                         // rank by comparison through shuffles (ties by lane), pick ranks kx and kx+1
                         int rank = 0;
@@ -626,42 +664,55 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
             xxA[tid] = Tq + mq;
         }
         __syncthreads();
-        const int items = tk.nrows * words;
-        for (int it = tid; it < items; it += BAND_THREADS) {
-            const int r = it / words, w = it - r * words;
-            uint32_t* out = reinterpret_cast<uint32_t*>(crp + pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch);
-            const float* vr = V + r * NBpad;
-            uint32_t word = (CRP_DELTA_ZERO) | (CRP_DELTA_ZERO << 8) | (CRP_DELTA_ZERO << 16) | (CRP_DELTA_ZERO << 24);
+        // thread = one 4-column group (one output word per row); the column band edges stay in registers while
+        // the thread walks down the strip's rows; consecutive threads write consecutive words of a CRP row
+        int any_flag = 0;
+#pragma unroll
+        for (int r = 0; r < BAND_RS; ++r) any_flag |= flag[r];
+        const uint32_t zero_word = (CRP_DELTA_ZERO) | (CRP_DELTA_ZERO << 8) | (CRP_DELTA_ZERO << 16) | (CRP_DELTA_ZERO << 24);
+        const uint32_t flip = CRP_DELTA_ZERO ^ CRP_DELTA_ONE;
+        for (int w = tid; w < words; w += BAND_THREADS) {
             const int j0 = w * 4;
-            if (j0 < NBpad) {
-                const float4 x4 = *reinterpret_cast<const float4*>(vr + j0);
-                const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
-                if (flag[r] != 0) {
+            uint32_t* out = reinterpret_cast<uint32_t*>(crp + pd.crp_off + (int64_t)tk.row0 * pd.pitch) + w;
+            const int wstride = pd.pitch >> 2;
+            if (j0 >= NBpad) {
+                for (int r = 0; r < tk.nrows; ++r) out[(int64_t)r * wstride] = zero_word;
+                continue;
+            }
+            const float4 l4 = *reinterpret_cast<const float4*>(lo_r + j0);
+            const float4 h4 = *reinterpret_cast<const float4*>(hi_r + j0);
+            const bool tail = (j0 + 3 >= NB);
+            for (int r = 0; r < tk.nrows; ++r) {
+                const float4 x4 = *reinterpret_cast<const float4*>(V + r * NBpad + j0);
+                uint32_t word = zero_word;
+                if (any_flag && flag[r] != 0) {
                     const float ta = thA[r];
+                    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
 #pragma unroll
                     for (int b = 0; b < 4; ++b) {
                         const int j = j0 + b;
-                        if (j < NB && xs[b] <= ta && xs[b] <= __ldg(thB + j))
-                            word ^= (CRP_DELTA_ZERO ^ CRP_DELTA_ONE) << (8 * b);
+                        if (j < NB && xs[b] <= ta && xs[b] <= __ldg(thB + j)) word ^= flip << (8 * b);
                     }
                 } else {
                     const float lo_q = red[r], hi_q = xxA[r];
-                    const float4 l4 = *reinterpret_cast<const float4*>(lo_r + j0);
-                    const float4 h4 = *reinterpret_cast<const float4*>(hi_r + j0);
-                    const float ls[4] = {l4.x, l4.y, l4.z, l4.w};
-                    const float hs[4] = {h4.x, h4.y, h4.z, h4.w};
+                    const bool i0 = x4.x < fminf(lo_q, l4.x), i1 = x4.y < fminf(lo_q, l4.y);
+                    const bool i2 = x4.z < fminf(lo_q, l4.z), i3 = x4.w < fminf(lo_q, l4.w);
+                    const bool o0 = x4.x > fminf(hi_q, h4.x), o1 = x4.y > fminf(hi_q, h4.y);
+                    const bool o2 = x4.z > fminf(hi_q, h4.z), o3 = x4.w > fminf(hi_q, h4.w);
+                    word ^= (i0 ? flip : 0u) | (i1 ? flip << 8 : 0u) | (i2 ? flip << 16 : 0u) | (i3 ? flip << 24 : 0u);
+                    if (!((i0 | o0) & (i1 | o1) & (i2 | o2) & (i3 | o3))) {
+                        // at least one cell is neither surely in nor surely out (padding columns are always "out")
+                        const bool am[4] = {!(i0 | o0), !(i1 | o1), !(i2 | o2), !(i3 | o3)};
 #pragma unroll
-                    for (int b = 0; b < 4; ++b) {
-                        const float lo = fminf(lo_q, ls[b]), hi = fminf(hi_q, hs[b]);
-                        if (xs[b] < lo) word ^= (CRP_DELTA_ZERO ^ CRP_DELTA_ONE) << (8 * b);
-                        else if (!(xs[b] > hi) && j0 + b < NB) {
-                            const int slot = atomicAdd(amb_cnt, 1);
-                            if (slot < amb_cap) amb[slot] = (r << 24) | (j0 + b);
-                        }
+                        for (int b = 0; b < 4; ++b)
+                            if (am[b] && (!tail || j0 + b < NB)) {
+                                const int slot = atomicAdd(amb_cnt, 1);
+                                if (slot < amb_cap) amb[slot] = (r << 24) | (j0 + b);
+                            }
                     }
                 }
+                out[(int64_t)r * wstride] = word;
             }
-            out[w] = word;
         }
         __syncthreads();
         {
