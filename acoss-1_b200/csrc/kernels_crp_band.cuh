@@ -47,6 +47,7 @@
 #define BAND_AFS 16                   // floats per staged A frame: 12 bins (x -2), |f|^2, pad
 #define BAND_WSCR 768                 // per-warp scratch words inside Gs: lidx[256] lval[256] stage[256]
 #define BAND_SMEM_FIXED (BAND_GR * BAND_AFS + 3 * BAND_RS + 32 + BAND_GR * BAND_TW)   // + 17 * NBpad floats
+#define BAND_RGN_TC (TC_OPB_BYTES / 4 + BAND_GR * TC_TW)   // tensor-core mode: OpB (32 KB) + skewed tile (24 KB) in place of Gs
 
 // exact distance of (query embedded row u, reference embedded row v): the oracle's op order
 __device__ __noinline__ float exact_dist(const float* __restrict__ frames, const PairDesc& pd, int rot,
@@ -111,7 +112,7 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
     float* red = reinterpret_cast<float*>(flag + BAND_RS);          // 32 words
     float* yyB = red + 32;
     float* Gs = yyB + NBpad;
-    float* V = Gs + BAND_GR * BAND_TW;
+    float* V = Gs + (TC ? BAND_RGN_TC : BAND_GR * BAND_TW);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_exact = 0;
     // tensor-core state
@@ -196,46 +197,67 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                 }
                 const float* fr_b = frames + b_f0 * ACOSS_NBINS;
                 const float2* fn_b = fnorm + b_f0;
-                for (int b0 = -(BAND_RS - 1); b0 < NB; b0 += TC_ND) {
-                    // side-B operand rows of frames b0 .. b0 + 255: hi / lo split of the raw bins, norm chunk, zero chunk
-                    for (int e = tid; e < TC_TW * ACOSS_NBINS; e += BAND_THREADS) {
-                        const int fl = e / ACOSS_NBINS, c = e - fl * ACOSS_NBINS;
-                        const int col = b0 + fl;
-                        float x = 0.f;
-                        if (col >= 0 && col < nb_frames) x = __ldg(fr_b + (int64_t)col * ACOSS_NBINS + c);
-                        float hi, lo;
-                        tf32_split(x, hi, lo);
-                        const int q = fl >> 7, m = fl & (TC_BLK - 1);
-                        float* rowp = reinterpret_cast<float*>(OpB + (size_t)q * (TC_CHUNKS * TC_BLK * 16) + (size_t)m * 16) + (c & 3);
-                        rowp[(c >> 2) * (TC_BLK * 4)] = hi;
-                        rowp[(3 + (c >> 2)) * (TC_BLK * 4)] = lo;
+                float* GsT = Gs + TC_OPB_BYTES / 4;          // skewed G2 tile, behind the side-B operand buffer
+                // thread -> (frame fl = tid >> 1, bins 6 (tid & 1) .. + 5) of a tile; threads 0..255 also own the norm chunks
+                const int ld_fl = tid >> 1, ld_h = tid & 1;
+                float* ob_row = reinterpret_cast<float*>(OpB) + (size_t)(ld_fl >> 7) * (TC_CHUNKS * TC_BLK * 4) + (size_t)(ld_fl & (TC_BLK - 1)) * 4;
+                float4* on_row = reinterpret_cast<float4*>(OpB) + (size_t)(tid >> 7) * (TC_CHUNKS * TC_BLK) + (tid & (TC_BLK - 1));
+                float2 px0, px1, px2, pn;
+                auto tc_fetch = [&](int b0_) {      // raw bins + norm split of tile b0_ -> registers
+                    const int col = b0_ + ld_fl;
+                    px0 = px1 = px2 = make_float2(0.f, 0.f);
+                    if (col >= 0 && col < nb_frames) {
+                        const float2* p = reinterpret_cast<const float2*>(fr_b + (int64_t)col * ACOSS_NBINS + 6 * ld_h);
+                        px0 = __ldg(p); px1 = __ldg(p + 1); px2 = __ldg(p + 2);
+                    }
+                    pn = make_float2(0.f, 0.f);
+                    if (tid < TC_TW) { const int cn = b0_ + tid; if (cn >= 0 && cn < nb_frames) pn = __ldg(fn_b + cn); }
+                };
+                auto tc_store = [&]() {             // hi / lo split -> OpB (chunks 0-2 hi, 3-5 lo, 6 = [1 1 nh nl], 7 = 0)
+                    float h0, l0, h1, l1, h2, l2, h3, l3, h4, l4, h5, l5;
+                    tf32_split(px0.x, h0, l0); tf32_split(px0.y, h1, l1); tf32_split(px1.x, h2, l2);
+                    tf32_split(px1.y, h3, l3); tf32_split(px2.x, h4, l4); tf32_split(px2.y, h5, l5);
+                    if (ld_h == 0) {                // bins 0..5: chunk 0 whole, chunk 1 first half
+                        *reinterpret_cast<float4*>(ob_row) = make_float4(h0, h1, h2, h3);
+                        *reinterpret_cast<float2*>(ob_row + 1 * TC_BLK * 4) = make_float2(h4, h5);
+                        *reinterpret_cast<float4*>(ob_row + 3 * TC_BLK * 4) = make_float4(l0, l1, l2, l3);
+                        *reinterpret_cast<float2*>(ob_row + 4 * TC_BLK * 4) = make_float2(l4, l5);
+                    } else {                        // bins 6..11: chunk 1 second half, chunk 2 whole
+                        *reinterpret_cast<float2*>(ob_row + 1 * TC_BLK * 4 + 2) = make_float2(h0, h1);
+                        *reinterpret_cast<float4*>(ob_row + 2 * TC_BLK * 4) = make_float4(h2, h3, h4, h5);
+                        *reinterpret_cast<float2*>(ob_row + 4 * TC_BLK * 4 + 2) = make_float2(l0, l1);
+                        *reinterpret_cast<float4*>(ob_row + 5 * TC_BLK * 4) = make_float4(l2, l3, l4, l5);
                     }
                     if (tid < TC_TW) {
-                        const int col = b0 + tid;
-                        float2 nn = make_float2(0.f, 0.f);
-                        if (col >= 0 && col < nb_frames) nn = __ldg(fn_b + col);
-                        const int q = tid >> 7, m = tid & (TC_BLK - 1);
-                        float4* rowp = reinterpret_cast<float4*>(OpB + (size_t)q * (TC_CHUNKS * TC_BLK * 16) + (size_t)m * 16);
-                        rowp[6 * TC_BLK] = make_float4(1.f, 1.f, nn.x, nn.y);
-                        rowp[7 * TC_BLK] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        on_row[6 * TC_BLK] = make_float4(1.f, 1.f, pn.x, pn.y);
+                        on_row[7 * TC_BLK] = make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                     fence_proxy_async_smem();
-                    tc_fence_before();
-                    __syncthreads();
-                    if (tid == 0) {
-                        tc_fence_after();
-                        const uint32_t a_base = smem_u32(OpB), b_base = smem_u32(OpA);
+                };
+                auto tc_mma = [&]() {               // one thread: 2 blocks x 6 k-slices, then commit to the mbarrier
+                    tc_fence_after();
+                    const uint32_t a_base = smem_u32(OpB), b_base = smem_u32(OpA);
 #pragma unroll
-                        for (int q = 0; q < 2; ++q)
+                    for (int q = 0; q < 2; ++q)
 #pragma unroll
-                            for (int sl = 0; sl < TC_SLICES; ++sl) {
-                                const int c0 = (sl < 4) ? 2 * sl : 2 * (sl - 4);      // A-operand chunk pair of this slice
-                                const uint64_t ad = umma_desc(a_base + (uint32_t)((q * TC_CHUNKS + c0) * TC_BLK * 16), TC_BLK * 16, 128);
-                                const uint64_t bd = umma_desc(b_base + (uint32_t)(sl * 2 * TC_NROWS * 16), TC_NROWS * 16, 128);
-                                umma_tf32(tmem_base + (uint32_t)(q * TC_NROWS), ad, bd, sl > 0 ? 1u : 0u);
-                            }
-                        umma_commit(mbar);
-                    }
+                        for (int sl = 0; sl < TC_SLICES; ++sl) {
+                            const int c0 = (sl < 4) ? 2 * sl : 2 * (sl - 4);      // A-operand chunk pair of this slice
+                            const uint64_t ad = umma_desc(a_base + (uint32_t)((q * TC_CHUNKS + c0) * TC_BLK * 16), TC_BLK * 16, 128);
+                            const uint64_t bd = umma_desc(b_base + (uint32_t)(sl * 2 * TC_NROWS * 16), TC_NROWS * 16, 128);
+                            umma_tf32(tmem_base + (uint32_t)(q * TC_NROWS), ad, bd, sl > 0 ? 1u : 0u);
+                        }
+                    umma_commit(mbar);
+                };
+                // prologue: tile 0 -> OpB -> MMA
+                const int b_first = -(BAND_RS - 1);
+                tc_fetch(b_first);
+                tc_store();
+                tc_fence_before();
+                __syncthreads();
+                if (tid == 0) tc_mma();
+                for (int b0 = b_first; b0 < NB; b0 += TC_ND) {
+                    const bool more = (b0 + TC_ND < NB);
+                    if (more) tc_fetch(b0 + TC_ND);                 // global loads of the next tile fly during the wait below
                     mbar_wait(mbar, mma_phase);
                     mma_phase ^= 1u;
                     tc_fence_after();
@@ -248,17 +270,19 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
 #pragma unroll
                         for (int aa = 0; aa < 12; ++aa) {
                             const int a = half * 12 + aa;
-                            Gs[a * TC_TW + ((bl - a) & (TC_TW - 1))] = v[aa];
+                            GsT[a * TC_TW + ((bl - a) & (TC_TW - 1))] = v[aa];
                         }
                     }
+                    if (more) tc_store();                           // OpB is free: its MMAs have completed
                     tc_fence_before();
                     __syncthreads();
+                    if (more && tid == 0) tc_mma();                 // next tile's MMAs run under this tile's window sums
                     // diagonal window sums: thread (delta, h) -> rows 8 h .. 8 h + 7 of diagonal delta
                     if (tid < 2 * TC_ND) {
                         const int h = tid >= TC_ND ? 1 : 0, dl = tid - h * TC_ND;
                         float g[16];
 #pragma unroll
-                        for (int a = 0; a < 16; ++a) g[a] = Gs[(8 * h + a) * TC_TW + dl];
+                        for (int a = 0; a < 16; ++a) g[a] = GsT[(8 * h + a) * TC_TW + dl];
                         float t2[15], t4[13], t8[9];
 #pragma unroll
                         for (int a = 0; a < 15; ++a) t2[a] = g[a] + g[a + 1];
@@ -268,10 +292,15 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                         for (int a = 0; a < 9; ++a) t8[a] = t4[a] + t4[a + 4];
                         const int jb = b0 + dl;
                         float* vp = V + jb;
+                        if (full_rows && jb >= 0 && jb + BAND_RS <= NB) {
 #pragma unroll
-                        for (int ii = 0; ii < 8; ++ii) {
-                            const int i = 8 * h + ii, j = jb + i;
-                            if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[ii] + g[ii + 8];
+                            for (int ii = 0; ii < 8; ++ii) vp[(8 * h + ii) * (NBpad + 1)] = t8[ii] + g[ii + 8];
+                        } else {
+#pragma unroll
+                            for (int ii = 0; ii < 8; ++ii) {
+                                const int i = 8 * h + ii, j = jb + i;
+                                if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[ii] + g[ii + 8];
+                            }
                         }
                     }
                     __syncthreads();

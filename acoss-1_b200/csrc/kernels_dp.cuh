@@ -75,6 +75,57 @@ __device__ __forceinline__ uint32_t delta_to_bonus(uint32_t dl)
 
 template <int G, int P> struct StepUnroll;
 
+// One row of the recurrence for one warp: row i-1 is in Aprev, row i-2 in Bold; the new row i is written IN PLACE
+// over Bold (register P of the new row needs Bold[P-1] only, so descending P never clobbers a live value).
+// Calling it with the two arrays swapped on alternate rows removes every row-to-row register copy.
+template <int G, int NCH, int ALIGN>
+__device__ __forceinline__ void dp_row_step(uint32_t (&Aprev)[NCH][G], uint32_t (&Bold)[NCH][G], uint32_t (&carry)[NCH],
+                                            uint32_t (&Bon)[NCH][G], const RowBytes<G> (&cur)[NCH],
+                                            const uint32_t (&vmask)[ALIGN ? G : 1], int nch, int lane, uint32_t zmask,
+                                            uint32_t& rm)
+{
+    const int src = (lane + 31) & 31;
+    const bool edge = (lane == 31);
+    // chunks in DESCENDING order so that Aprev[ch-1] still holds row i-1
+#pragma unroll
+    for (int ch = NCH - 1; ch >= 0; --ch) {
+        if (ch < nch) {
+            // left neighbour group's edge registers of row i-1: lane 31 of chunk ch-1 is the left neighbour of lane 0
+            // of chunk ch; for ch == 0 lane 0 has no left neighbour (columns < 0 are zero)
+            const uint32_t e1 = (ch > 0) ? Aprev[ch > 0 ? ch - 1 : 0][G - 1] : 0u;
+            const uint32_t e2 = (ch > 0) ? Aprev[ch > 0 ? ch - 1 : 0][G - 2] : 0u;
+            const uint32_t g1 = edge ? e1 : Aprev[ch][G - 1];
+            const uint32_t g2 = edge ? e2 : Aprev[ch][G - 2];
+            const uint32_t n1 = __shfl_sync(0xffffffffu, g1, src);
+            const uint32_t n2 = __shfl_sync(0xffffffffu, g2, src);
+            const uint32_t s1_0 = prmt(n1, Aprev[ch][G - 1], 0x5432);   // (nbr cell 2G-1, own cell G-1)
+            const uint32_t s2_0 = prmt(n2, Aprev[ch][G - 2], 0x5432);   // (nbr cell 2G-2, own cell G-2)
+            uint32_t dsh = 0;   // chen17: packed delta of (i, j-1) for p = 0
+            if (ALIGN) {
+                const uint32_t dl_last = cur[ch].template delta<G - 1>();
+                const uint32_t dprev = (ch > 0) ? cur[ch > 0 ? ch - 1 : 0].template delta<G - 1>() : 0xFFFFFFFFu;
+                const uint32_t nd = __shfl_sync(0xffffffffu, edge ? dprev : dl_last, src);
+                dsh = prmt(nd, dl_last, 0x5432);
+            }
+            StepUnroll<G, G - 1>::template run<ALIGN>(Aprev[ch], Bold[ch], cur[ch], s1_0, s2_0, carry[ch], Bon[ch], dsh);
+            if (ch == 0) { Bold[0][0] &= zmask; Bold[0][1] &= zmask; }
+            carry[ch] = s1_0;
+            if (ALIGN) {
+                StepUnroll<G, G - 1>::bonus(cur[ch], Bon[ch]);
+                if (ch == nch - 1) {
+                    // a padded column can receive the +R bonus of the last valid column: keep it out of the maximum
+#pragma unroll
+                    for (int p = 0; p < G; p += 2)
+                        rm = __vimax3_s16x2(rm, Bold[ch][p] & vmask[p], Bold[ch][p + 1] & vmask[p + 1]);
+                    continue;
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < G; p += 2) rm = __vimax3_s16x2(rm, Bold[ch][p], Bold[ch][p + 1]);
+        }
+    }
+}
+
 // One warp per pair.  ALIGN: 0 = serra09 (Qmax), 1 = chen17 (Dmax).
 // Requirements: pitch % (64*G) == 0, N <= NCH*64*G, min(M,N) small enough for
 // int16 half units (host checks: 4*min(M,N) < 32000).
@@ -96,7 +147,7 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
         const int nch = (N + CHUNK - 1) / CHUNK;
         const uint8_t* base = crp + pd.crp_off + (int64_t)lane * LB;
 
-        uint32_t A[NCH][G], B[NCH][G], carry[NCH];     // rows i-1, i-2; carried (i-2) edge
+        uint32_t A[NCH][G], B[NCH][G], carry[NCH];     // rows i-1, i-2 (roles alternate); carried (i-2) edge
         uint32_t Bon[NCH][G];                          // chen17: +R of row i-1 (unshifted)
         uint32_t rm = 0;
 #pragma unroll
@@ -105,96 +156,66 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
 #pragma unroll
             for (int p = 0; p < G; ++p) { A[ch][p] = 0; B[ch][p] = 0; Bon[ch][p] = 0; }
         }
-        // valid-column masks of the last chunk (chen17 only: a padded column can
-        // receive the +R bonus of the last valid column)
+        // valid-column masks of the last chunk (chen17 only)
         uint32_t vmask[ALIGN ? G : 1];
         if (ALIGN) {
             const int c0 = (nch - 1) * CHUNK + lane * LB;
 #pragma unroll
             for (int p = 0; p < G; ++p)
                 vmask[p] = ((c0 + p < N) ? 0x0000FFFFu : 0u) | ((c0 + p + G < N) ? 0xFFFF0000u : 0u);
-        }
+        } else vmask[0] = 0;
 
-        RowBytes<G> cur[NCH];
+        RowBytes<G> r0[NCH], r1[NCH];
+        // chunks beyond the pair's width are never loaded: they stay "no recurrence" for the whole pair
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) { r0[ch].fill(0xFFFFFFFFu); r1[ch].fill(0xFFFFFFFFu); }
         if (M > 2) {
             if (ALIGN) {
                 // bonus of row 1
 #pragma unroll
                 for (int ch = 0; ch < NCH; ++ch)
                     if (ch < nch) {
-                        RowBytes<G> r1;
-                        r1.load(base + (int64_t)1 * pitch + ch * CHUNK);
-                        StepUnroll<G, G - 1>::bonus(r1, Bon[ch]);
+                        RowBytes<G> rb;
+                        rb.load(base + (int64_t)1 * pitch + ch * CHUNK);
+                        StepUnroll<G, G - 1>::bonus(rb, Bon[ch]);
                     }
             }
 #pragma unroll
-            for (int ch = 0; ch < NCH; ++ch) {
-                if (ch < nch) cur[ch].load(base + (int64_t)2 * pitch + ch * CHUNK);
-                else cur[ch].fill(0xFFFFFFFFu);
-            }
+            for (int ch = 0; ch < NCH; ++ch)
+                if (ch < nch) r0[ch].load(base + (int64_t)2 * pitch + ch * CHUNK);
         }
-        for (int i = 2; i < M; ++i) {
-            RowBytes<G> nxt[NCH];
-            const bool more = (i + 1 < M);
-#pragma unroll
-            for (int ch = 0; ch < NCH; ++ch) {
-                if (more && ch < nch) nxt[ch].load(base + (int64_t)(i + 1) * pitch + ch * CHUNK);
-                else nxt[ch].fill(0xFFFFFFFFu);
-            }
-            // L2 prefetch a few rows ahead (one 128 B line per 128/LB lanes)
-            if (i + 6 < M) {
+        const int64_t pitch64 = pitch;
+        const uint8_t* rp = base + 2 * pitch64;             // this lane's bytes of row i
+        const bool pf_lane = ((lane * LB) & 127) == 0;      // one L2 prefetch per 128-byte line
+        for (int i = 2; i < M; i += 2, rp += 2 * pitch64) {
+            // row i + 1 -> r1 while row i is processed
+            const bool more1 = (i + 1 < M);
+            if (more1) {
+                const uint8_t* p1 = rp + pitch64;
 #pragma unroll
                 for (int ch = 0; ch < NCH; ++ch)
-                    if (ch < nch && (lane * LB) % 128 == 0)
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (int64_t)(i + 6) * pitch + ch * CHUNK));
+                    if (ch < nch) r1[ch].load(p1 + ch * CHUNK);
             }
-            // chunks in DESCENDING order so that A[ch-1] still holds row i-1
+            if (pf_lane && i + 7 < M) {
+                const uint8_t* p6 = rp + 4 * pitch64;
+                const uint8_t* p7 = p6 + pitch64;
 #pragma unroll
-            for (int ch = NCH - 1; ch >= 0; --ch) {
-                if (ch < nch) {
-                    // left neighbour group's edge registers of row i-1
-                    uint32_t g1 = A[ch][G - 1], g2 = A[ch][G - 2];
-                    if (lane == 31) {
-                        g1 = (ch > 0) ? A[ch > 0 ? ch - 1 : 0][G - 1] : 0u;
-                        g2 = (ch > 0) ? A[ch > 0 ? ch - 1 : 0][G - 2] : 0u;
+                for (int ch = 0; ch < NCH; ++ch)
+                    if (ch < nch) {
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(p6 + ch * CHUNK));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(p7 + ch * CHUNK));
                     }
-                    // lane 31 of chunk ch-1 is the left neighbour of lane 0 of chunk ch;
-                    // for ch == 0 lane 0 has no left neighbour (columns < 0 are zero)
-                    uint32_t n1 = __shfl_sync(0xffffffffu, g1, (lane + 31) & 31);
-                    uint32_t n2 = __shfl_sync(0xffffffffu, g2, (lane + 31) & 31);
-                    // (lane 31's own value for lane 0's use was replaced above; lanes 1..31 read
-                    //  lanes 0..30, which hold their own A[ch])
-                    const uint32_t s1_0 = prmt(n1, A[ch][G - 1], 0x5432);   // (nbr cell 2G-1, own cell G-1)
-                    const uint32_t s2_0 = prmt(n2, A[ch][G - 2], 0x5432);   // (nbr cell 2G-2, own cell G-2)
-                    uint32_t dsh = 0;   // chen17: packed delta of (i, j-1) for p = 0
-                    if (ALIGN) {
-                        // current row's delta of the left neighbour's last register
-                        uint32_t dl_last = cur[ch].template delta<G - 1>();
-                        uint32_t dsrc = dl_last;
-                        if (lane == 31) dsrc = (ch > 0) ? cur[ch > 0 ? ch - 1 : 0].template delta<G - 1>() : 0xFFFFFFFFu;
-                        uint32_t nd = __shfl_sync(0xffffffffu, dsrc, (lane + 31) & 31);
-                        dsh = prmt(nd, dl_last, 0x5432);
-                    }
-                    uint32_t Nw[G];
-                    StepUnroll<G, G - 1>::template run<ALIGN>(A[ch], B[ch], cur[ch], s1_0, s2_0, carry[ch],
-                                                              Bon[ch], dsh, Nw);
-                    if (ch == 0) { Nw[0] &= zmask; Nw[1] &= zmask; }
+            }
+            dp_row_step<G, NCH, ALIGN>(A, B, carry, Bon, r0, vmask, nch, lane, zmask, rm);      // row i   -> B
+            if (more1) {
+                if (i + 2 < M) {
+                    const uint8_t* p2 = rp + 2 * pitch64;
 #pragma unroll
-                    for (int p = 0; p < G; ++p) { B[ch][p] = A[ch][p]; A[ch][p] = Nw[p]; }
-                    carry[ch] = s1_0;
-                    if (ALIGN) {
-                        StepUnroll<G, G - 1>::bonus(cur[ch], Bon[ch]);
-                        if (ch == nch - 1) {
-#pragma unroll
-                            for (int p = 0; p < G; ++p) Nw[p] &= vmask[p];
-                        }
-                    }
-#pragma unroll
-                    for (int p = 0; p < G; p += 2) rm = __vimax3_s16x2(rm, Nw[p], Nw[p + 1]);
+                    for (int ch = 0; ch < NCH; ++ch)
+                        if (ch < nch) r0[ch].load(p2 + ch * CHUNK);
                 }
+                dp_row_step<G, NCH, ALIGN>(B, A, carry, Bon, r1, vmask, nch, lane, zmask, rm);  // row i+1 -> A
             }
-#pragma unroll
-            for (int ch = 0; ch < NCH; ++ch) cur[ch] = nxt[ch];
         }
         int best = max((int)(rm & 0xFFFFu), (int)(rm >> 16));
         best = __reduce_max_sync(0xffffffffu, best);
@@ -202,14 +223,13 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
     }
 }
 
-// Fully unrolled per-register update, P = G-1 .. 0 (recursion keeps every
-// register index a compile-time constant).
+// Fully unrolled per-register update, P = G-1 .. 0 (recursion keeps every register index a compile-time
+// constant).  Writes the new row over B in place.
 template <int G, int P> struct StepUnroll {
     template <int ALIGN>
-    __device__ __forceinline__ static void run(const uint32_t (&A)[G], const uint32_t (&B)[G],
+    __device__ __forceinline__ static void run(const uint32_t (&A)[G], uint32_t (&B)[G],
                                                const RowBytes<G>& row, uint32_t s1_0, uint32_t s2_0,
-                                               uint32_t carry, const uint32_t (&Bon)[G],
-                                               uint32_t dsh, uint32_t (&Nw)[G])
+                                               uint32_t carry, const uint32_t (&Bon)[G], uint32_t dsh)
     {
         const uint32_t a1 = (P >= 1) ? A[P >= 1 ? P - 1 : 0] : s1_0;                 // row i-1, col j-1
         const uint32_t b1 = (P >= 1) ? B[P >= 1 ? P - 1 : 0] : carry;                // row i-2, col j-1
@@ -225,8 +245,8 @@ template <int G, int P> struct StepUnroll {
         } else {
             m = __vimax3_s16x2(a1, b1, a2);
         }
-        Nw[P] = __viaddmax_s16x2(m, dl, 0u);    // R=1: m+2 ; R=0: max(m-1, 0)
-        StepUnroll<G, P - 1>::template run<ALIGN>(A, B, row, s1_0, s2_0, carry, Bon, dsh, Nw);
+        B[P] = __viaddmax_s16x2(m, dl, 0u);    // R=1: m+2 ; R=0: max(m-1, 0)
+        StepUnroll<G, P - 1>::template run<ALIGN>(A, B, row, s1_0, s2_0, carry, Bon, dsh);
     }
     __device__ __forceinline__ static void bonus(const RowBytes<G>& row, uint32_t (&Bon)[G])
     {
@@ -236,9 +256,8 @@ template <int G, int P> struct StepUnroll {
 };
 template <int G> struct StepUnroll<G, -1> {
     template <int ALIGN>
-    __device__ __forceinline__ static void run(const uint32_t (&)[G], const uint32_t (&)[G], const RowBytes<G>&,
-                                               uint32_t, uint32_t, uint32_t, const uint32_t (&)[G],
-                                               uint32_t, uint32_t (&)[G]) {}
+    __device__ __forceinline__ static void run(const uint32_t (&)[G], uint32_t (&)[G], const RowBytes<G>&,
+                                               uint32_t, uint32_t, uint32_t, const uint32_t (&)[G], uint32_t) {}
     __device__ __forceinline__ static void bonus(const RowBytes<G>&, uint32_t (&)[G]) {}
 };
 
