@@ -266,12 +266,10 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                         const int quarter = warp & 3, q = (warp >> 2) & 1, half = warp >> 3;
                         float v[16];
                         tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(q * TC_NROWS + half * 12), v);
-                        const int bl = q * TC_BLK + quarter * 32 + lane;          // column within the tile
+                        // unskewed tile GsT[a][column]: lanes = consecutive columns, constant offsets per strip row
+                        float* gp = GsT + (half * 12) * TC_TW + q * TC_BLK + quarter * 32 + lane;
 #pragma unroll
-                        for (int aa = 0; aa < 12; ++aa) {
-                            const int a = half * 12 + aa;
-                            GsT[a * TC_TW + ((bl - a) & (TC_TW - 1))] = v[aa];
-                        }
+                        for (int aa = 0; aa < 12; ++aa) gp[aa * TC_TW] = v[aa];
                     }
                     if (more) tc_store();                           // OpB is free: its MMAs have completed
                     tc_fence_before();
@@ -281,8 +279,10 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                     if (tid < 2 * TC_ND) {
                         const int h = tid >= TC_ND ? 1 : 0, dl = tid - h * TC_ND;
                         float g[16];
+                        // diagonal delta of the tile: G2[8h + a][dl + 8h + a]  (lanes = consecutive diagonals)
+                        const float* gq = GsT + (8 * h) * (TC_TW + 1) + dl;
 #pragma unroll
-                        for (int a = 0; a < 16; ++a) g[a] = GsT[(8 * h + a) * TC_TW + dl];
+                        for (int a = 0; a < 16; ++a) g[a] = gq[a * (TC_TW + 1)];
                         float t2[15], t4[13], t8[9];
 #pragma unroll
                         for (int a = 0; a < 15; ++a) t2[a] = g[a] + g[a + 1];
@@ -291,15 +291,16 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
 #pragma unroll
                         for (int a = 0; a < 9; ++a) t8[a] = t4[a] + t4[a + 4];
                         const int jb = b0 + dl;
-                        float* vp = V + jb;
+                        float* vp = V + jb + (8 * h) * (NBpad + 1);
                         if (full_rows && jb >= 0 && jb + BAND_RS <= NB) {
 #pragma unroll
-                            for (int ii = 0; ii < 8; ++ii) vp[(8 * h + ii) * (NBpad + 1)] = t8[ii] + g[ii + 8];
+                            for (int ii = 0; ii < 8; ++ii) { *vp = t8[ii] + g[ii + 8]; vp += NBpad + 1; }
                         } else {
 #pragma unroll
                             for (int ii = 0; ii < 8; ++ii) {
                                 const int i = 8 * h + ii, j = jb + i;
-                                if (i < tk.nrows && j >= 0 && j < NB) vp[i * (NBpad + 1)] = t8[ii] + g[ii + 8];
+                                if (i < tk.nrows && j >= 0 && j < NB) *vp = t8[ii] + g[ii + 8];
+                                vp += NBpad + 1;
                             }
                         }
                     }
@@ -464,17 +465,23 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                     pa = (r_lo >= 0 && ba > 0) ? smin + (float)ba * hwidth : -INFINITY;
                     pb = (r_hi < BAND_SAMPLE && bb < 511) ? smin + (float)(bb + 1) * hwidth : INFINITY;
                     if (prof && attempt == 0) tc1 = clock64();
-                    // (c) pass A: per-lane counts, 8 loads in flight
+                    // (c) pass A: per-lane counts.  A lane owns 4-column groups (one LDS.128 each); rho~ may be slightly
+                    //     negative, so the comparisons stay in floating point; counts accumulate from the predicates.
+                    const int n_full = NB >> 2;                       // complete 4-column groups
+                    const float4* vr4 = reinterpret_cast<const float4*>(vr);
                     int ca_l = 0, cb_l = 0;
-                    int j = lane;
-                    for (; j + 7 * 32 < NB; j += 8 * 32) {
-                        float x[8];
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) x[q] = vr[j + q * 32];
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) { ca_l += (x[q] < pa); cb_l += (x[q] < pb); }
+                    int g = lane;
+                    for (; g + 32 < n_full; g += 64) {
+                        const float4 x0 = vr4[g], x1 = vr4[g + 32];
+                        ca_l += (x0.x < pa) + (x0.y < pa) + (x0.z < pa) + (x0.w < pa) + (x1.x < pa) + (x1.y < pa) + (x1.z < pa) + (x1.w < pa);
+                        cb_l += (x0.x < pb) + (x0.y < pb) + (x0.z < pb) + (x0.w < pb) + (x1.x < pb) + (x1.y < pb) + (x1.z < pb) + (x1.w < pb);
                     }
-                    for (; j < NB; j += 32) { const float x = vr[j]; ca_l += (x < pa); cb_l += (x < pb); }
+                    for (; g < n_full; g += 32) {
+                        const float4 x0 = vr4[g];
+                        ca_l += (x0.x < pa) + (x0.y < pa) + (x0.z < pa) + (x0.w < pa);
+                        cb_l += (x0.x < pb) + (x0.y < pb) + (x0.z < pb) + (x0.w < pb);
+                    }
+                    if (lane < (NB & 3)) { const float x = vr[4 * n_full + lane]; ca_l += (x < pa); cb_l += (x < pb); }
                     const int cab_l = cb_l - ca_l;
                     const int pk = __reduce_add_sync(0xffffffffu, ca_l | (cab_l << 16));
                     c_a = pk & 0xffff; c_ab = pk >> 16;
@@ -485,16 +492,19 @@ crp_strip_band_kernel(const PairDesc* __restrict__ descs,
                     for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
                     // pass B: every lane writes its in-band elements at its private offset
                     int off = incl - cab_l;
-                    j = lane;
-                    for (; j + 7 * 32 < NB; j += 8 * 32) {
-                        float x[8];
+                    for (g = lane; g < n_full; g += 32) {
+                        const float4 x0 = vr4[g];
+                        const float xs[4] = {x0.x, x0.y, x0.z, x0.w};
+                        if (fminf(fminf(x0.x, x0.y), fminf(x0.z, x0.w)) < pb) {
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) x[q] = vr[j + q * 32];
-#pragma unroll
-                        for (int q = 0; q < 8; ++q)
-                            if (x[q] >= pa && x[q] < pb) { lidx[off] = j + q * 32; lval[off] = x[q]; ++off; }
+                            for (int q = 0; q < 4; ++q)
+                                if (xs[q] >= pa && xs[q] < pb) { lidx[off] = 4 * g + q; lval[off] = xs[q]; ++off; }
+                        }
                     }
-                    for (; j < NB; j += 32) { const float x = vr[j]; if (x >= pa && x < pb) { lidx[off] = j; lval[off] = x; ++off; } }
+                    if (lane < (NB & 3)) {
+                        const float x = vr[4 * n_full + lane];
+                        if (x >= pa && x < pb) { lidx[off] = 4 * n_full + lane; lval[off] = x; ++off; }
+                    }
                     __syncwarp();
                 }
                 if (prof) tc2 = clock64();

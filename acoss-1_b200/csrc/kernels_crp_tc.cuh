@@ -19,7 +19,7 @@
 // Data path per tile of 256 side-B frames: raw frames (48 B) + per-frame |f|^2 split (8 B) from L2 ->
 // hi/lo split in registers -> canonical no-swizzle K-major UMMA layout in shared memory ->
 // 12 x tcgen05.mma.kind::tf32 (M=128, N=32, K=8) issued by one thread, accumulators in TMEM ->
-// tcgen05.commit on an mbarrier -> tcgen05.ld (32x32b) by all 16 warps -> skewed G2 tile in shared
+// tcgen05.commit on an mbarrier -> tcgen05.ld (32x32b) by all 16 warps -> G2 tile in shared
 // memory for the diagonal window sums.
 #pragma once
 #include "common.cuh"

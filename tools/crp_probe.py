@@ -1,0 +1,28 @@
+#!/usr/bin/env python
+"""Ad-hoc probe: CRP-stage throughput (cells/s) of the pair kernel at fixed track lengths."""
+import sys, os
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import acoss_b200
+from acoss_b200 import synth
+
+def main():
+    lens = [int(x) for x in sys.argv[1].split(",")]
+    mode = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+    n = 64
+    ctx = acoss_b200.Context(0)
+    for L in lens:
+        labels, works, tids, hp = synth.make_tracks(n // 2, 2, 0, 5, L, L)
+        hp = [h[:L] for h in hp]
+        ctx.upload_tracks(hp)
+        i, j = np.triu_indices(n, 1)
+        pairs = np.stack([i, j], 1).astype(np.int32)
+        prm = ctx.params(crp_mode=mode)
+        ctx.serra09_pairs(pairs, prm)
+        ctx.serra09_pairs(pairs, prm)
+        st = ctx.pair_stats()
+        print("L=%d mode=%d pairs=%d crp %.1f ms  %.3e cells/s   dp %.2f ms %.0f GCUPS  exact %.4f fallback %d" % (
+            L, mode, len(pairs), st["ms_crp"], st["crp_cells"] / st["ms_crp"] * 1e3, st["ms_dp"],
+            st["dp_cells"] / st["ms_dp"] / 1e6, st["n_exact_cells"] / (2.0 * st["crp_cells"]), st["n_fallback_rows"]))
+
+main()
