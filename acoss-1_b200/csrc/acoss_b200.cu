@@ -15,6 +15,7 @@
 #include "kernels_prep.cuh"
 #include "kernels_crp.cuh"
 #include "kernels_crp_band.cuh"
+#include "kernels_crp_gemm.cuh"
 #include "kernels_dp.cuh"
 #include "kernels_eval.cuh"
 #include "kernels_snf.cuh"
@@ -63,7 +64,7 @@ struct acoss_ctx {
     double ef_ms[3] = {0, 0, 0}, ef_flop = 0;
     int64_t ef_cells = 0;
     // per-call scratch
-    DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2, d_counters;
+    DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2, d_counters, d_lists;
     cudaEvent_t ev[8] = {};
     acoss_pair_stats stats = {};
     unsigned long long h_counters[16] = {};

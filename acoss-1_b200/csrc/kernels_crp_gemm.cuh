@@ -1,0 +1,795 @@
+// kernels_crp_gemm.cuh -- bit-exact CRP with the cross-similarity on the tensor cores (sm_100a, crp_mode 4).
+//
+// Same contract and the same exactness argument as kernels_crp_band.cuh (approximate radicand rho~,
+// rigorous error band E, exact re-check of everything inside the band), but rho~ of a whole
+// 128 x 256 block of cells is ONE accumulated tcgen05 GEMM:
+//     rho~(i, j) = |x_i|^2 + |y_j|^2 - 2 <x_i, y_j>,     x_i, y_j = 108-d delay embeddings (m = 9, tau = 1)
+// in TF32 with the split x = x_hi + x_lo (three products hh + hl + lh, the lo.lo term is inside E).
+//
+// Hankel operands.  Embedded row r is frames r .. r+8, so the K-major operand "row r, 16-byte chunk
+// (k, c3)" (time offset k < 9, bins 4 c3 .. 4 c3 + 3) is chunk c3 of frame r + k.  Shared memory holds
+// every frame ONCE, as six planes (hi / lo x c3) of 16-byte entries; the UMMA descriptor of the
+// k-slice {(k, c3), (k + 1, c3)} simply starts at plane + 16 k with LBO = 16: rows are 16 B apart
+// (the canonical no-swizzle core matrix), 8-row groups 128 B apart (SBO).  Nothing is expanded nine
+// times, neither in shared memory nor on the way from L2.  Per 128 x 256 tile: 36 MMAs (3 products x
+// 3 planes x 4 offset pairs) + 5 MMAs for offset 8 and the norm chunk = 41 x (M 128, N 256, K 8).
+//
+// Rows of the strip are TMEM lanes, so after tcgen05.ld a thread owns ONE strip row: counting against
+// its row's pivots, list insertion and binarisation are thread-local, no shuffles, no shared-memory
+// strip buffer.  Accumulators are double-buffered in TMEM (2 x 256 columns): the epilogue of tile t
+// overlaps the MMAs of tile t + 1.
+//
+// Per strip (128 rows of side A x all NB rows of side B):
+//   sample    256 spread columns, hi.hi product only (14 MMAs on an explicitly gathered operand)
+//             -> per-row pivots pa <= pb bracketing the wanted order statistics (sample histogram)
+//   count     stream all tiles: c_a = #(rho~ < pa), elements in [pa, pb) go to the row's list (global
+//             scratch, L2-resident)
+//   select    warp per row on its list: value bisection, candidates within 2E, exact 108-term chains
+//             (the oracle's op order), exact order statistics -> threshold
+//   binarise  (pass 2 only) stream all tiles again: rho~ against the band edges of both thresholds,
+//             ambiguous cells decided exactly afterwards; CRP bytes go straight from registers to HBM.
+#pragma once
+#include "common.cuh"
+#include "kernels_crp.cuh"
+#include "kernels_crp_tc.cuh"
+#include "kernels_crp_band.cuh"
+
+#define GM_ROWS 128                   // strip rows = MMA M = TMEM lanes
+#define GM_TN 256                     // side-B embedded rows per tile = MMA N = TMEM columns per buffer
+#define GM_THREADS 512
+#define GM_WARPS (GM_THREADS / 32)
+#define GM_S 512                      // sample columns per row (two MMA blocks of 256)
+#define GM_SPL (GM_S / 32)
+#define GM_SUBCAP 128                 // list capacity per (row, column group): private to the owning thread, no atomics
+#define GM_LCAP (4 * GM_SUBCAP)        // list slots per row
+#define GM_LPL (GM_LCAP / 32)
+#define GM_EPS_REL 1.220703125e-04f   // 2^-13, see the error budget below
+#define GM_NSIGMA 3.5f
+#define GM_MIN_NB 128                 // below this every row takes the exact-row path
+#define GM_MAX_NB 16384
+#define GM_APLANE ((GM_ROWS + 8) * 16)
+#define GM_BPLANE ((GM_TN + 8) * 16)
+#define GM_A_BYTES (6 * GM_APLANE + GM_ROWS * 16)       // 15 104
+#define GM_B_BYTES (6 * GM_BPLANE + GM_TN * 16)         // 29 440
+#define GM_SMP_CHUNKS 28
+#define GM_R1_BYTES (64 * GM_S * 4)                     // 131 072: sample operand / sample dump (64 rows) / B buffers + edges + ambiguity list / scratch
+#define GM_EDGE_OFF (2 * GM_B_BYTES)                    // column band edges lo[3][256], hi[3][256] (floats), slot = tile % 3
+#define GM_AMB_OFF 65536                                // ambiguity list (ints)
+#define GM_AMB_CAP ((GM_R1_BYTES - GM_AMB_OFF) / 4)
+#define GM_WSCR_WORDS 512                               // per-warp scratch: hist[256] | arow[108] cand[32]
+#define GM_ROWV_BYTES (GM_ROWS * 4)
+#define GM_ARAW_BYTES ((GM_ROWS + 8) * ACOSS_NBINS * 4)  // strip frames in the oracle's bin order, for the exact chains
+// shared memory: A planes | R1 | per-warp scratch | per-row arrays (pa pb thA xx loq hiq: float; cnta lcnt flag: int) | 2 mbarriers | tmem holder
+#define GM_SMEM_BYTES (GM_A_BYTES + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4 + 12 * GM_ROWV_BYTES + GM_ARAW_BYTES + 64)
+#define GM_TMEM_COLS 512
+#define GM_BIG 1.0e30f                 // norm entry of padding columns: rho~ = huge, never below a pivot or an edge
+#define GM_PMAX 1.0e29f                // "unbounded" pivots
+#define GM_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((GM_TN >> 3) << 17) | ((GM_ROWS >> 4) << 24))
+
+// Error budget of rho~ against the oracle's radicand, in units of u (xx + yy), u = 2^-24:
+//   oracle's own rounding (kernels_crp_band.cuh)                                       220
+//   norms taken from the oracle's self-dot tables (108-term chains) + hi/lo residual    112
+//   dropped lo.lo and residual cross terms of the three-product TF32 split               12
+//   fp32 accumulation inside the tensor core, assuming no better than truncation of
+//   every addend to the largest exponent: 41 MMAs x 9 addends x 2u x |partial| <= 2(xx+yy)   1476
+//   total 1820 u < 2048 u = 2^-13.   counters[14] records the largest error actually observed.
+
+__device__ __forceinline__ void gm_tmem_alloc(uint32_t* holder_smem)
+{
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(holder_smem)), "n"(GM_TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void gm_tmem_free(uint32_t taddr)
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(GM_TMEM_COLS) : "memory");
+}
+// One MMA.  The two shared-memory descriptors differ from call to call only in their low words (start address >> 4 in
+// bits 0-13, LBO >> 4 in bits 16-29); the high word (SBO = 128 B, descriptor version 1, no swizzle) is common.
+#define GM_DESC_HI (((128u >> 4) & 0x3FFFu) | (1u << 14))
+__device__ __forceinline__ void gm_mma(uint32_t d_tmem, uint32_t adesc_lo, uint32_t bdesc_lo, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b64 da, {%1, %5};\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem), "r"(adesc_lo), "r"(bdesc_lo), "r"((uint32_t)GM_IDESC), "r"(accumulate), "r"((uint32_t)GM_DESC_HI) : "memory");
+}
+// low descriptor word of (base + byte offset, LBO): additive in the offset because shared memory addresses stay below 256 KB
+#define GM_DLO(base_lo, off, lbo) ((base_lo) + (((uint32_t)(off)) >> 4) + ((((uint32_t)(lbo)) >> 4) << 16))
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, float (&v)[32])
+{
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(r[q]);
+}
+
+// the 41 MMAs of one 128 x 256 tile.  a0 / b0: shared-memory byte addresses of the A planes / of the B buffer.
+// A plane order: H0 H1 H2 L0 L1 L2 NRM;  B plane order: L0 L1 L2 H0 H1 H2 NRM (so that every paired
+// chunk of the offset-8 leftovers has a non-negative LBO on both operands).
+__device__ __forceinline__ void gm_issue_tile(uint32_t d_tmem, uint32_t a0, uint32_t b0)
+{
+    const uint32_t al = (a0 & 0x3FFFFu) >> 4, bl = (b0 & 0x3FFFFu) >> 4;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int prod = 0; prod < 3; ++prod) {              // 0: hi.hi  1: hi.lo  2: lo.hi
+#pragma unroll
+        for (int c3 = 0; c3 < 3; ++c3) {
+            const int ap = ((prod == 2 ? 3 : 0) + c3) * GM_APLANE;
+            const int bp = ((prod == 1 ? 0 : 3) + c3) * GM_BPLANE;
+#pragma unroll
+            for (int kp = 0; kp < 4; ++kp) {
+                gm_mma(d_tmem, GM_DLO(al, ap + 32 * kp, 16), GM_DLO(bl, bp + 32 * kp, 16), acc);
+                acc = 1;
+            }
+        }
+    }
+    const int aH0 = 128, aH2 = 2 * GM_APLANE + 128, aL0 = 3 * GM_APLANE + 128;
+    const int bL0 = 128, bL2 = 2 * GM_BPLANE + 128, bH0 = 3 * GM_BPLANE + 128, bH2 = 5 * GM_BPLANE + 128;
+    gm_mma(d_tmem, GM_DLO(al, aH0, GM_APLANE), GM_DLO(bl, bH0, GM_BPLANE), 1);                  // (H0,H0) (H1,H1)
+    gm_mma(d_tmem, GM_DLO(al, aH0, GM_APLANE), GM_DLO(bl, bL0, GM_BPLANE), 1);                  // (H0,L0) (H1,L1)
+    gm_mma(d_tmem, GM_DLO(al, aL0, GM_APLANE), GM_DLO(bl, bH0, GM_BPLANE), 1);                  // (L0,H0) (L1,H1)
+    gm_mma(d_tmem, GM_DLO(al, aH2, 3 * GM_APLANE), GM_DLO(bl, bL2, 3 * GM_BPLANE), 1);          // (H2,L2) (L2,H2)
+    gm_mma(d_tmem, GM_DLO(al, aH2, 4 * GM_APLANE - 128), GM_DLO(bl, bH2, GM_BPLANE - 128), 1);  // (H2,H2) norms
+}
+
+// the 14 MMAs of a sample block: A = hi planes, B = gathered sample operand, chunk column q at s0 + q * 4096:
+// q = 8 c3 + k (k < 8), 24..26 = (c3, 8), 27 = norms
+__device__ __forceinline__ void gm_issue_sample(uint32_t d_tmem, uint32_t a0, uint32_t s0)
+{
+    const uint32_t al = (a0 & 0x3FFFFu) >> 4, sl = (s0 & 0x3FFFFu) >> 4;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int c3 = 0; c3 < 3; ++c3) {
+#pragma unroll
+        for (int kp = 0; kp < 4; ++kp) {
+            gm_mma(d_tmem, GM_DLO(al, c3 * GM_APLANE + 32 * kp, 16), GM_DLO(sl, (8 * c3 + 2 * kp) * (GM_TN * 16), GM_TN * 16), acc);
+            acc = 1;
+        }
+    }
+    gm_mma(d_tmem, GM_DLO(al, 128, GM_APLANE), GM_DLO(sl, 24 * (GM_TN * 16), GM_TN * 16), 1);
+    gm_mma(d_tmem, GM_DLO(al, 2 * GM_APLANE + 128, 4 * GM_APLANE - 128), GM_DLO(sl, 26 * (GM_TN * 16), GM_TN * 16), 1);
+}
+
+// counters: [0] exact cells  [1] fallback rows  [2..6] cycles (thread 0): stage+sample, pivots, count pass, select, binarise
+//           [7] tasks  [11] too many candidates  [12] window not inside the list  [13] bracket miss  [15] list overflow
+//           [14] max observed |rho~ - rho_oracle| / (xx + yy) (float bits)
+__global__ void __launch_bounds__(GM_THREADS, 1)
+crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
+                      const StripTask* __restrict__ tasks, int n_tasks,
+                      const float* __restrict__ frames,
+                      const float* __restrict__ selfdot,
+                      float* __restrict__ thr, uint8_t* __restrict__ crp,
+                      int side_a_is_query, float qf,
+                      float2* __restrict__ lists,            // [gridDim.x][GM_ROWS][4][GM_SUBCAP] (rho~, column) of the listed elements
+                      unsigned long long* __restrict__ counters, int dbg)
+{
+    extern __shared__ __align__(128) unsigned char gsm[];
+    unsigned char* Apl = gsm;
+    unsigned char* R1 = gsm + GM_A_BYTES;
+    unsigned* wscr = reinterpret_cast<unsigned*>(R1 + GM_R1_BYTES) + (threadIdx.x >> 5) * GM_WSCR_WORDS;
+    float* rowv = reinterpret_cast<float*>(R1 + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4);
+    float* s_pa = rowv;
+    float* s_pb = rowv + GM_ROWS;
+    float* s_th = rowv + 2 * GM_ROWS;
+    float* s_xx = rowv + 3 * GM_ROWS;
+    float* s_loq = rowv + 4 * GM_ROWS;
+    float* s_hiq = rowv + 5 * GM_ROWS;
+    int* s_cnta = reinterpret_cast<int*>(rowv + 6 * GM_ROWS);
+    int* s_lcnt = s_cnta + GM_ROWS;
+    int* s_flag = s_lcnt + 4 * GM_ROWS;                                  // s_lcnt: [row][column group]
+    float* Araw = reinterpret_cast<float*>(s_flag + GM_ROWS);            // [GM_ROWS + 8][12]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(Araw + (GM_ROWS + 8) * ACOSS_NBINS);      // [2]
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 2);
+    float* s_red = reinterpret_cast<float*>(tmem_holder + 1);            // 8 words: reductions, ambiguity counter
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lq = warp & 3, cg = warp >> 2;          // TMEM lane quarter (strip rows 32 lq ..), column group (64 cg ..)
+    const int myrow = 32 * lq + lane;
+    unsigned long long n_exact = 0;
+    uint32_t par0 = 0, par1 = 0;                      // mbarrier phase parities
+    float max_err = 0.0f;
+
+    if (warp == 0) gm_tmem_alloc(tmem_holder);
+    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+    const uint32_t my_taddr = tmem_base + ((uint32_t)(32 * lq) << 16) + 16 * cg;
+    const uint32_t a_saddr = smem_u32(Apl), r1_saddr = smem_u32(R1);
+    float2* my_lists = lists + (size_t)blockIdx.x * GM_ROWS * GM_LCAP;
+
+    for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
+        const StripTask tk = tasks[task];
+        const PairDesc pd = descs[tk.pair];
+        const int rot = pd.oti % ACOSS_NBINS;
+        const int NB = side_a_is_query ? pd.N : pd.M;
+        const int na_frames = side_a_is_query ? pd.nq : pd.nr;
+        const int nb_frames = side_a_is_query ? pd.nr : pd.nq;
+        const int64_t a_f0 = side_a_is_query ? pd.q_frame_off : pd.r_frame_off;
+        const int64_t b_f0 = side_a_is_query ? pd.r_frame_off : pd.q_frame_off;
+        // <roll(ref, rot), query>: the B frames stay unrotated; the A frames are staged pre-rotated:
+        // by +rot when A is the reference, by -rot when A is the query.
+        const int rot_a = side_a_is_query ? (ACOSS_NBINS - rot) % ACOSS_NBINS : rot;
+        const float* sdA = selfdot + (side_a_is_query ? pd.q_sd_off : pd.r_sd_off + (int64_t)rot * pd.N);
+        const float* sdB = selfdot + (side_a_is_query ? pd.r_sd_off + (int64_t)rot * pd.N : pd.q_sd_off);
+        const float* fr_a = frames + a_f0 * ACOSS_NBINS;
+        const float* fr_b = frames + b_f0 * ACOSS_NBINS;
+        const int n_tiles = (NB + GM_TN - 1) / GM_TN;
+        const bool rowvalid = myrow < tk.nrows;
+        const PercentileRank pr = percentile_rank(NB, qf);
+        float* thr_out = thr + (side_a_is_query ? pd.thr_q_off : pd.thr_r_off);
+        const bool tiny = NB < GM_MIN_NB;
+
+        __syncthreads();
+        long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
+        if (tid == 0) { ph0 = clock64(); ph1 = ph0; ph2 = ph0; }
+        // ---- stage the A planes: entry e = frame row0 + e (e < 136), chunk c3: -2 * rotated bins, hi / lo; norms
+        for (int e = tid; e < (GM_ROWS + 8) * 3; e += GM_THREADS) {
+            const int fe = e / 3, c3 = e - 3 * fe;
+            const int f = tk.row0 + fe;
+            float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
+            if (f < na_frames) {
+                const float* fp = fr_a + (int64_t)f * ACOSS_NBINS;
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 0, rot_a)], hi.x, lo.x);
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 1, rot_a)], hi.y, lo.y);
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 2, rot_a)], hi.z, lo.z);
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 3, rot_a)], hi.w, lo.w);
+            }
+            *reinterpret_cast<float4*>(Apl + c3 * GM_APLANE + fe * 16) = hi;
+            *reinterpret_cast<float4*>(Apl + (3 + c3) * GM_APLANE + fe * 16) = lo;
+        }
+        for (int e = tid; e < (GM_ROWS + 8) * ACOSS_NBINS; e += GM_THREADS) {
+            const int fe = e / ACOSS_NBINS, c = e - fe * ACOSS_NBINS;
+            const int f = tk.row0 + fe;
+            Araw[e] = (f < na_frames) ? fr_a[(int64_t)f * ACOSS_NBINS + (side_a_is_query ? c : rot_src(c, rot))] : 0.0f;
+        }
+        if (tid < GM_ROWS) {
+            float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
+            float xx = 0.0f;
+            if (tid < tk.nrows) { xx = sdA[tk.row0 + tid]; tf32_split(xx, nv.x, nv.y); nv.z = 1.0f; nv.w = 1.0f; }
+            *reinterpret_cast<float4*>(Apl + 6 * GM_APLANE + tid * 16) = nv;
+            s_xx[tid] = xx; s_flag[tid] = 0; s_cnta[tid] = 0;
+            s_pa[tid] = -GM_PMAX; s_pb[tid] = GM_PMAX;
+        }
+        float ymax = 0.0f, xmax = 0.0f;
+        for (int j = tid; j < NB; j += GM_THREADS) ymax = fmaxf(ymax, __ldg(sdB + j));
+        if (tid < tk.nrows) xmax = sdA[tk.row0 + tid];
+        for (int o = 16; o > 0; o >>= 1) {
+            ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+            xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+        }
+        float* red = reinterpret_cast<float*>(R1);       // R1 is free here
+        if (lane == 0) { red[warp] = ymax; red[GM_WARPS + warp] = xmax; }
+        __syncthreads();
+        ymax = red[0]; xmax = red[GM_WARPS];
+#pragma unroll
+        for (int w = 1; w < GM_WARPS; ++w) { ymax = fmaxf(ymax, red[w]); xmax = fmaxf(xmax, red[GM_WARPS + w]); }
+        const float E = GM_EPS_REL * (xmax + ymax);       // one bound for the whole strip (conservative)
+        __syncthreads();
+
+        if (!tiny) {
+            // ---- sample: gather 2 x 256 spread columns into an explicit K-major operand (hi parts only; the pivots only
+            //      have to be roughly right, the count pass verifies the bracket), 14 MMAs per half into TMEM buffer 0 / 1
+            for (int half = 0; half < 2; ++half) {
+                for (int e = tid; e < GM_SMP_CHUNKS * GM_TN; e += GM_THREADS) {
+                    const int s = e & (GM_TN - 1), q = e >> 8;
+                    const int pos = (int)(((long long)(half * GM_TN + s) * NB) >> 9);            // / GM_S
+                    float4 o;
+                    if (q < 27) {
+                        const int c3 = q < 24 ? (q >> 3) : q - 24, k = q < 24 ? (q & 7) : 8;
+                        const float4 x = __ldg(reinterpret_cast<const float4*>(fr_b + (int64_t)(pos + k) * ACOSS_NBINS + 4 * c3));
+                        o = make_float4(tf32_rna(x.x), tf32_rna(x.y), tf32_rna(x.z), tf32_rna(x.w));
+                    } else {
+                        o.x = 1.0f; o.y = 1.0f;
+                        tf32_split(__ldg(sdB + pos), o.z, o.w);
+                    }
+                    *reinterpret_cast<float4*>(R1 + q * (GM_TN * 16) + s * 16) = o;
+                }
+                fence_proxy_async_smem();
+                tc_fence_before();
+                __syncthreads();
+                if (tid == 0) {
+                    tc_fence_after();
+                    gm_issue_sample(tmem_base + half * GM_TN, a_saddr, r1_saddr);
+                    umma_commit(mbar);
+                }
+                mbar_wait(mbar, par0); par0 ^= 1;       // the operand buffer is rebuilt for the second half
+                tc_fence_after();
+            }
+            if (tid == 0) ph1 = clock64();
+            // ---- pivots, 64 strip rows per round: the owners dump their 128 sample values per row from TMEM to shared
+            //      memory (XOR swizzle of the low 5 column bits: the 32 rows of a warp hit 32 different banks), then
+            //      warp per row: 16 samples per lane, 512-bin packed histogram of the sample (two 16-bit counters per
+            //      word) -> pa / pb at bin edges
+            for (int round = 0; round < 2; ++round) {
+                if ((lq >> 1) == round) {
+                    float* smp = reinterpret_cast<float*>(R1) + (myrow & 63) * GM_S;
+#pragma unroll
+                    for (int b = 0; b < 2; ++b)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            float v[32];
+                            gm_tmem_ld32(my_taddr + 48 * cg + b * GM_TN + 32 * h, v);
+#pragma unroll
+                            for (int q = 0; q < 32; ++q) smp[b * GM_TN + 64 * cg + 32 * h + (q ^ lane)] = v[q];
+                        }
+                }
+                tc_fence_before();
+                __syncthreads();
+                const float* smp = reinterpret_cast<const float*>(R1);
+                unsigned* hist = wscr;
+                const float frac = ((float)pr.lo + 0.5f) / (float)NB;
+                const float rs = frac * (float)GM_S;
+                const float sg = sqrtf(fmaxf(rs * (1.0f - frac), 1.0f));
+                const int r_lo = (int)floorf(rs - GM_NSIGMA * sg) - 1;       // sample ranks the bracket must enclose
+                const int r_hi = (int)ceilf(rs + GM_NSIGMA * sg) + 1;
+                for (int r = 64 * round + warp; r < min(tk.nrows, 64 * round + 64); r += GM_WARPS) {
+                    float sm[GM_SPL];
+                    float smin = INFINITY, smax = -INFINITY;
+#pragma unroll
+                    for (int q = 0; q < GM_SPL; ++q) {
+                        sm[q] = smp[(r & 63) * GM_S + q * 32 + lane];
+                        smin = fminf(smin, sm[q]); smax = fmaxf(smax, sm[q]);
+                    }
+                    for (int o = 16; o > 0; o >>= 1) {
+                        smin = fminf(smin, __shfl_xor_sync(0xffffffffu, smin, o));
+                        smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, o));
+                    }
+                    const float hscale = (smax > smin) ? 512.0f / (smax - smin) : 0.0f;
+                    const float hwidth = (smax - smin) * (1.0f / 512.0f);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) hist[q * 32 + lane] = 0u;
+                    __syncwarp();
+#pragma unroll
+                    for (int q = 0; q < GM_SPL; ++q) {
+                        const int bin = min(511, (int)((sm[q] - smin) * hscale));
+                        atomicAdd(&hist[bin >> 1], 1u << (16 * (bin & 1)));
+                    }
+                    __syncwarp();
+                    int hc[16], hpre;                        // lane owns bins 16 lane .. 16 lane + 15
+                    {
+                        const uint4 h0 = *reinterpret_cast<const uint4*>(hist + 8 * lane);
+                        const uint4 h1 = *reinterpret_cast<const uint4*>(hist + 8 * lane + 4);
+                        const unsigned hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+                        int tot = 0;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) { hc[2 * q] = hw[q] & 0xffffu; hc[2 * q + 1] = hw[q] >> 16; tot += hc[2 * q] + hc[2 * q + 1]; }
+                        int incl = tot;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                        hpre = incl - tot;                   // samples in bins < 16 lane
+                    }
+                    // pa = lower edge of the last bin b with #(samples in bins < b) <= r_lo;
+                    // pb = upper edge of the first bin b with #(samples in bins <= b) > r_hi
+                    int ba = -1, bb = 512;
+                    {
+                        int run = hpre;
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) {
+                            if (run <= r_lo) ba = 16 * lane + q;
+                            run += hc[q];
+                            if (run > r_hi && bb == 512) bb = 16 * lane + q;
+                        }
+                        ba = __reduce_max_sync(0xffffffffu, ba);
+                        bb = __reduce_min_sync(0xffffffffu, bb);
+                    }
+                    if (lane == 0) {
+                        s_pa[r] = (r_lo >= 0 && ba > 0) ? fmaxf(smin + (float)ba * hwidth, -GM_PMAX) : -GM_PMAX;
+                        s_pb[r] = (r_hi < GM_S && bb < 511) ? fminf(smin + (float)(bb + 1) * hwidth, GM_PMAX) : GM_PMAX;
+                    }
+                    __syncwarp();
+                }
+                __syncthreads();
+            }
+        }
+        if (tid == 0) ph2 = clock64();
+
+        // ---- tile streaming machinery
+        const float* thB = thr + pd.thr_r_off;            // column thresholds (pass 2)
+        // band edges of the column thresholds of a tile, slot = tile % 3: the slot written for tile t + 1 is read by
+        // neither the epilogue of tile t - 1 (slow warps) nor that of tile t
+        float* loC = reinterpret_cast<float*>(R1 + GM_EDGE_OFF);
+        float* hiC = loC + 3 * GM_TN;
+        // side-B planes of tile t (frames 256 t .. 256 t + 263, hi / lo split in registers), norms, column band edges
+        auto build_b = [&](int buf, int t, bool edges) {
+            unsigned char* Bb = R1 + buf * GM_B_BYTES;
+            const int j0 = t * GM_TN;
+            for (int e = tid; e < (GM_TN + 8) + GM_TN; e += GM_THREADS) {
+                if (e < GM_TN + 8) {
+                    const int f = j0 + e;
+                    float4 x[3];
+                    if (f < nb_frames) {
+                        const float4* fp = reinterpret_cast<const float4*>(fr_b + (int64_t)f * ACOSS_NBINS);
+                        x[0] = __ldg(fp); x[1] = __ldg(fp + 1); x[2] = __ldg(fp + 2);
+                    } else {
+                        x[0] = x[1] = x[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int c3 = 0; c3 < 3; ++c3) {
+                        float4 hi, lo;
+                        tf32_split(x[c3].x, hi.x, lo.x); tf32_split(x[c3].y, hi.y, lo.y);
+                        tf32_split(x[c3].z, hi.z, lo.z); tf32_split(x[c3].w, hi.w, lo.w);
+                        *reinterpret_cast<float4*>(Bb + c3 * GM_BPLANE + e * 16) = lo;
+                        *reinterpret_cast<float4*>(Bb + (3 + c3) * GM_BPLANE + e * 16) = hi;
+                    }
+                } else {
+                    const int c = e - (GM_TN + 8), j = j0 + c;
+                    float4 nv = make_float4(1.0f, 1.0f, GM_BIG, 0.f);     // padding columns: rho~ huge
+                    float lo = -INFINITY, hi = -INFINITY;          // ... and never "in", always "out"
+                    if (j < NB) {
+                        nv.x = 1.0f; nv.y = 1.0f;
+                        tf32_split(__ldg(sdB + j), nv.z, nv.w);
+                        if (edges) {
+                            const float tb = __ldg(thB + j);
+                            const float Tr = xmul(tb, tb);
+                            const float mr = E + Tr * 4.76837158203125e-07f;        // E + 8uT
+                            lo = Tr - mr; hi = Tr + mr;
+                        }
+                    }
+                    *reinterpret_cast<float4*>(Bb + 6 * GM_BPLANE + c * 16) = nv;
+                    if (edges) { loC[(t % 3) * GM_TN + c] = lo; hiC[(t % 3) * GM_TN + c] = hi; }
+                }
+            }
+        };
+        // double-buffered pipeline: MMAs of tile t + 1 run under the epilogue of tile t
+        auto stream = [&](auto&& epi, bool edges) {
+            build_b(0, 0, edges);
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncthreads();
+            if (tid == 0) { tc_fence_after(); if (!(dbg & 2)) gm_issue_tile(tmem_base, a_saddr, r1_saddr); umma_commit(mbar); }
+            for (int t = 0; t < n_tiles; ++t) {
+                const int buf = t & 1;
+                if (t + 1 < n_tiles && !(dbg & 4)) { build_b(buf ^ 1, t + 1, edges); fence_proxy_async_smem(); }
+                tc_fence_before();
+                __syncthreads();
+                if (t + 1 < n_tiles && tid == 0) {
+                    tc_fence_after();
+                    if (!(dbg & 2)) gm_issue_tile(tmem_base + (buf ^ 1) * GM_TN, a_saddr, r1_saddr + (buf ^ 1) * GM_B_BYTES);
+                    umma_commit(mbar + (buf ^ 1));
+                }
+                if (buf == 0) { mbar_wait(mbar, par0); par0 ^= 1; } else { mbar_wait(mbar + 1, par1); par1 ^= 1; }
+                tc_fence_after();
+                // column ownership interleaved in runs of 16: thread (row, cg) reads columns 16 (4 i + cg) .. + 15, so that a
+                // cluster of consecutive in-band columns spreads over the four owners of the row
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float v[16];
+                    tmem_ld16(my_taddr + buf * GM_TN + 64 * i, v);
+                    if (!(dbg & 1)) epi(t * GM_TN + 64 * i + 16 * cg, t % 3, 64 * i + 16 * cg, v);
+                }
+            }
+            tc_fence_before();
+            __syncthreads();
+        };
+
+        if (!tiny) {
+            // ---- count pass: c_a = #(rho~ < pa); elements of [pa, pb) go to the row's list
+            const float pa = s_pa[myrow], pb = s_pb[myrow];
+            int ca = 0, ln = 0;
+            float2* ml = my_lists + myrow * GM_LCAP + cg * GM_SUBCAP;       // private to this thread: no atomics
+            stream([&](int jbase, int, int, const float (&v)[16]) {
+                if (!rowvalid) return;
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const float x = v[q];
+                    const bool below = x < pa;
+                    ca += below;
+                    if (!below && x < pb) {
+                        ml[min(ln, GM_SUBCAP - 1)] = make_float2(x, __int_as_float(jbase + q));     // overflow is detected from ln
+                        ++ln;
+                    }
+                }
+            }, false);
+            if (rowvalid) s_lcnt[myrow * 4 + cg] = ln;
+            if (rowvalid) atomicAdd(&s_cnta[myrow], ca);
+            __threadfence_block();
+            __syncthreads();
+        }
+        if (tid == 0) ph3 = clock64();
+
+        // ---- select.  (A) warp per row: value bisection on the row's list, candidates (everything within 2E of the
+        //      wanted order statistics) go to a pool in shared memory;  (B) thread per candidate: the exact 108-term
+        //      chain in the oracle's op order;  (C) warp per row: exact order statistics among its candidates.
+        int* pool_col = reinterpret_cast<int*>(R1);                       // [GM_ROWS][32]
+        float* pool_val = reinterpret_cast<float*>(R1) + GM_ROWS * 32;     // rho~ (error statistics only)
+        float* pool_dex = pool_val + GM_ROWS * 32;                        // exact distances
+        int* s_off = reinterpret_cast<int*>(pool_dex + GM_ROWS * 32);     // [GM_ROWS + 1] candidate offsets
+        if (!tiny) {
+            for (int r = warp; r < tk.nrows; r += GM_WARPS) {
+                const int4 c4 = *reinterpret_cast<const int4*>(s_lcnt + 4 * r);
+                const int c_a = s_cnta[r], c_ab = c4.x + c4.y + c4.z + c4.w;
+                const bool ovf = max(max(c4.x, c4.y), max(c4.z, c4.w)) > GM_SUBCAP;
+                bool ok = (c_a <= pr.lo) && (c_a + c_ab >= pr.hi + 1) && !ovf;
+                if (!ok && lane == 0) atomicAdd(&counters[ovf ? 15 : 13], 1ull);
+                const float pa = s_pa[r], pb = s_pb[r];
+                float w_lo = 0.f, w_hi = 0.f;
+                float lv[GM_LPL];
+                int li[GM_LPL];
+                int n_c = 0, kx = 0;
+                if (ok) {
+                    const float2* lst = my_lists + r * GM_LCAP;
+                    const int cseg[4] = {c4.x, c4.y, c4.z, c4.w};
+                    float vmin = INFINITY, vmax = -INFINITY;
+#pragma unroll
+                    for (int q = 0; q < GM_LPL; ++q) {
+                        const int e = q * 32 + lane;                  // slot e: segment q / 4, offset (q % 4) * 32 + lane
+                        lv[q] = INFINITY; li[q] = 0;
+                        if ((q & 3) * 32 + lane < cseg[q >> 2]) {
+                            const float2 ent = lst[e];
+                            lv[q] = ent.x; li[q] = __float_as_int(ent.y);
+                            vmin = fminf(vmin, lv[q]); vmax = fmaxf(vmax, lv[q]);
+                        }
+                    }
+                    for (int o = 16; o > 0; o >>= 1) {
+                        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+                        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+                    }
+                    // shrink [w_lo, w_hi) by value bisection while it keeps the wanted order statistic (rank kk of the
+                    // list), until it holds few elements.  invariant: #(list < w_lo) <= kk < #(list < w_hi)
+                    const int kk = pr.lo - c_a;
+                    w_lo = vmin; w_hi = INFINITY;
+                    int c_lo = 0, c_hi = c_ab;
+                    float b_hi = vmax;
+                    for (int it = 0; it < 24 && c_hi - c_lo > 3; ++it) {
+                        const float mid = 0.5f * (w_lo + b_hi);
+                        if (!(mid > w_lo) || !(mid < b_hi)) break;
+                        int cm = 0;
+#pragma unroll
+                        for (int q = 0; q < GM_LPL; ++q) cm += (lv[q] < mid);
+                        cm = __reduce_add_sync(0xffffffffu, cm);
+                        if (cm <= kk) { w_lo = mid; c_lo = cm; }
+                        else { w_hi = mid; b_hi = mid; c_hi = cm; }
+                    }
+                    // the upper wanted order statistic (rank kk + 1) is inside the window or is the smallest element >= w_hi
+                    if (pr.hi != pr.lo && c_hi < kk + 2) {
+                        float nx = INFINITY;
+#pragma unroll
+                        for (int q = 0; q < GM_LPL; ++q) if (lv[q] >= w_hi) nx = fminf(nx, lv[q]);
+                        for (int o = 16; o > 0; o >>= 1) nx = fminf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
+                        w_hi = nx;
+                    }
+                    // the candidate window (+- 2E) must lie strictly inside the list's value range [pa, pb)
+                    const float hi_edge = (w_hi == INFINITY) ? vmax : w_hi;
+                    ok = (w_lo - 2.0f * E > pa || pa == -GM_PMAX) && (hi_edge + 2.0f * E < pb || pb == GM_PMAX);
+                    if (!ok && lane == 0) atomicAdd(&counters[12], 1ull);
+                }
+                if (ok) {
+                    // candidates = list elements in [w_lo - 2E, w_hi + 2E]; every exact order statistic is among them
+                    const float c_min = w_lo - 2.0f * E;
+                    const float c_max = (w_hi == INFINITY) ? INFINITY : w_hi + 2.0f * E;
+                    int n_below = c_a;
+#pragma unroll
+                    for (int q = 0; q < GM_LPL; ++q) {
+                        const bool valid = lv[q] != INFINITY;
+                        const bool below = valid && lv[q] < c_min;
+                        const bool cand = valid && !below && lv[q] <= c_max;
+                        n_below += __popc(__ballot_sync(0xffffffffu, below));
+                        const unsigned mc = __ballot_sync(0xffffffffu, cand);
+                        if (cand) {
+                            const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
+                            if (slot < 32) { pool_col[r * 32 + slot] = li[q]; pool_val[r * 32 + slot] = lv[q]; }
+                        }
+                        n_c += __popc(mc);
+                    }
+                    kx = pr.lo - n_below;
+                    if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) { ok = false; if (lane == 0) atomicAdd(&counters[11], 1ull); }
+                }
+                if (lane == 0) {
+                    s_lcnt[4 * r] = ok ? n_c : 0;
+                    s_lcnt[4 * r + 1] = kx;
+                    if (!ok) { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); }
+                }
+            }
+            __syncthreads();
+            // offsets of the rows' candidates in the flat task list
+            if (warp == 0) {
+                int c[4], tot = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { const int r = 4 * lane + q; c[q] = (r < tk.nrows) ? s_lcnt[4 * r] : 0; tot += c[q]; }
+                int incl = tot;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                int run = incl - tot;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { s_off[4 * lane + q] = run; run += c[q]; }
+                if (lane == 31) s_off[GM_ROWS] = run;
+            }
+            __syncthreads();
+            {
+                int cbs[ACOSS_NBINS];                                     // oracle bin c -> bin of the side-B frame
+#pragma unroll
+                for (int c = 0; c < ACOSS_NBINS; ++c) cbs[c] = side_a_is_query ? rot_src(c, rot) : c;
+                const int n_tasks_c = s_off[GM_ROWS];
+                for (int idx = tid; idx < n_tasks_c; idx += GM_THREADS) {
+                    int r = 0;                                            // last row with s_off[r] <= idx
+#pragma unroll
+                    for (int st = 64; st > 0; st >>= 1) if (s_off[r + st] <= idx) r += st;
+                    const int slot = idx - s_off[r];
+                    const int jj = pool_col[r * 32 + slot];
+                    const float* bp = fr_b + (int64_t)jj * ACOSS_NBINS;
+                    const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
+                    float acc = 0.0f;
+#pragma unroll 3
+                    for (int s_ = 0; s_ < 9; ++s_) {
+                        const float4 a0 = as[3 * s_], a1 = as[3 * s_ + 1], a2 = as[3 * s_ + 2];
+                        const float* bs = bp + s_ * ACOSS_NBINS;
+                        acc = xadd(acc, xmul(a0.x, __ldg(bs + cbs[0])));
+                        acc = xadd(acc, xmul(a0.y, __ldg(bs + cbs[1])));
+                        acc = xadd(acc, xmul(a0.z, __ldg(bs + cbs[2])));
+                        acc = xadd(acc, xmul(a0.w, __ldg(bs + cbs[3])));
+                        acc = xadd(acc, xmul(a1.x, __ldg(bs + cbs[4])));
+                        acc = xadd(acc, xmul(a1.y, __ldg(bs + cbs[5])));
+                        acc = xadd(acc, xmul(a1.z, __ldg(bs + cbs[6])));
+                        acc = xadd(acc, xmul(a1.w, __ldg(bs + cbs[7])));
+                        acc = xadd(acc, xmul(a2.x, __ldg(bs + cbs[8])));
+                        acc = xadd(acc, xmul(a2.y, __ldg(bs + cbs[9])));
+                        acc = xadd(acc, xmul(a2.z, __ldg(bs + cbs[10])));
+                        acc = xadd(acc, xmul(a2.w, __ldg(bs + cbs[11])));
+                    }
+                    const float sa = s_xx[r], sb = __ldg(sdB + jj);
+                    const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
+                    float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
+                    max_err = fmaxf(max_err, fabsf(item - pool_val[r * 32 + slot]) / (sa + sb));
+                    if (item < 0.0f) item = 0.0f;
+                    pool_dex[r * 32 + slot] = __fsqrt_rn(item);
+                    ++n_exact;
+                }
+            }
+            __syncthreads();
+            for (int r = warp; r < tk.nrows; r += GM_WARPS) {
+                const int n_c = s_lcnt[4 * r], kx = s_lcnt[4 * r + 1];
+                if (n_c == 0) continue;
+                const float dex = (lane < n_c) ? pool_dex[r * 32 + lane] : INFINITY;
+                // rank by comparison through shuffles (ties by lane), pick ranks kx and kx + 1
+                int rank = 0;
+                for (int b = 0; b < n_c; ++b) {
+                    const float db = __shfl_sync(0xffffffffu, dex, b);
+                    rank += (db < dex) || (db == dex && b < lane);
+                }
+                const unsigned m0 = __ballot_sync(0xffffffffu, lane < n_c && rank == kx);
+                const unsigned m1 = __ballot_sync(0xffffffffu, lane < n_c && rank == kx + 1);
+                const float v_lo = __shfl_sync(0xffffffffu, dex, __ffs(m0) - 1);
+                const float v_hi = m1 ? __shfl_sync(0xffffffffu, dex, __ffs(m1) - 1) : v_lo;
+                if (lane == 0) { const float t = percentile_combine(pr, v_lo, v_hi); s_th[r] = t; thr_out[tk.row0 + r] = t; }
+            }
+        } else if (tid < GM_ROWS) {
+            s_flag[tid] = 1;
+        }
+        __syncthreads();
+        // ---- rows that could not be bracketed (and tiny pairs): the whole row exactly, one row at a time
+        for (int r = 0; r < tk.nrows; ++r) {
+            if (!s_flag[r]) continue;
+            float* vr = reinterpret_cast<float*>(R1);
+            for (int j = tid; j < NB; j += GM_THREADS) {
+                vr[j] = side_a_is_query ? exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j)
+                                        : exact_dist(frames, pd, rot, selfdot, j, tk.row0 + r);
+                ++n_exact;
+            }
+            __syncthreads();
+            if (warp == 0) {
+                float v_hi;
+                const float v_lo = warp_select_pair(vr, NB, pr.lo, lane, v_hi);
+                const float t = percentile_combine(pr, v_lo, v_hi);
+                if (lane == 0) { s_th[r] = t; thr_out[tk.row0 + r] = t; }
+            }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            ph4 = clock64();
+            atomicAdd(&counters[2], (unsigned long long)(ph1 - ph0));
+            atomicAdd(&counters[3], (unsigned long long)(ph2 - ph1));
+            atomicAdd(&counters[4], (unsigned long long)(ph3 - ph2));
+            atomicAdd(&counters[5], (unsigned long long)(ph4 - ph3));
+            atomicAdd(&counters[7], 1ull);
+        }
+        if (!side_a_is_query) continue;
+
+        // ---- pass 2: binarise.  Per cell: sure-in <=> rho~ < min(lo_q, lo_r[j]), sure-out <=> rho~ > min(hi_q, hi_r[j]);
+        //      anything else is decided exactly afterwards.  A thread owns one CRP row: 32 bytes per tcgen05.ld go
+        //      straight from registers to HBM.
+        int* amb = reinterpret_cast<int*>(R1 + GM_AMB_OFF);
+        int* amb_cnt = reinterpret_cast<int*>(s_red);
+        if (tid == 0) *amb_cnt = 0;
+        if (tid < GM_ROWS) {
+            const float ta = (tid < tk.nrows) ? s_th[tid] : 0.0f;
+            const float Tq = xmul(ta, ta);
+            const float mq = E + Tq * 4.76837158203125e-07f;
+            s_loq[tid] = Tq - mq;
+            s_hiq[tid] = Tq + mq;
+        }
+        __syncthreads();
+        {
+            const float lo_q = s_loq[myrow], hi_q = s_hiq[myrow];
+            const uint32_t zero_word = (CRP_DELTA_ZERO) | (CRP_DELTA_ZERO << 8) | (CRP_DELTA_ZERO << 16) | (CRP_DELTA_ZERO << 24);
+            const uint32_t flip = CRP_DELTA_ZERO ^ CRP_DELTA_ONE;
+            uint8_t* orow = crp + pd.crp_off + (int64_t)(tk.row0 + myrow) * pd.pitch;
+            const int pitch = pd.pitch;
+            stream([&](int jbase, int slot, int cbase, const float (&v)[16]) {
+                const float4* lc = reinterpret_cast<const float4*>(loC + slot * GM_TN + cbase);
+                const float4* hc = reinterpret_cast<const float4*>(hiC + slot * GM_TN + cbase);
+                uint32_t w[4];
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const float4 l4 = lc[g], h4 = hc[g];
+                    const float x0 = v[4 * g], x1 = v[4 * g + 1], x2 = v[4 * g + 2], x3 = v[4 * g + 3];
+                    const bool i0 = x0 < fminf(lo_q, l4.x), i1 = x1 < fminf(lo_q, l4.y);
+                    const bool i2 = x2 < fminf(lo_q, l4.z), i3 = x3 < fminf(lo_q, l4.w);
+                    const bool o0 = x0 > fminf(hi_q, h4.x), o1 = x1 > fminf(hi_q, h4.y);
+                    const bool o2 = x2 > fminf(hi_q, h4.z), o3 = x3 > fminf(hi_q, h4.w);
+                    w[g] = zero_word ^ ((i0 ? flip : 0u) | (i1 ? flip << 8 : 0u) | (i2 ? flip << 16 : 0u) | (i3 ? flip << 24 : 0u));
+                    if (!((i0 | o0) & (i1 | o1) & (i2 | o2) & (i3 | o3)) && rowvalid) {
+                        const bool am[4] = {!(i0 | o0), !(i1 | o1), !(i2 | o2), !(i3 | o3)};
+#pragma unroll
+                        for (int b = 0; b < 4; ++b)
+                            if (am[b]) {
+                                const int slot_ = atomicAdd(amb_cnt, 1);
+                                if (slot_ < GM_AMB_CAP) amb[slot_] = (myrow << 24) | (jbase + 4 * g + b);
+                            }
+                    }
+                }
+                if (rowvalid && jbase + 16 <= pitch) *reinterpret_cast<uint4*>(orow + jbase) = make_uint4(w[0], w[1], w[2], w[3]);
+            }, true);
+            // columns past the last tile up to the pitch
+            const int done = n_tiles * GM_TN;
+            if (done < pitch) {
+                const int wrem = (pitch - done) >> 2;
+                for (int idx = tid; idx < tk.nrows * wrem; idx += GM_THREADS) {
+                    const int r = idx / wrem, w = idx - r * wrem;
+                    reinterpret_cast<uint32_t*>(crp + pd.crp_off + (int64_t)(tk.row0 + r) * pitch + done)[w] = zero_word;
+                }
+            }
+        }
+        __syncthreads();
+        {
+            const int na = *amb_cnt;
+            if (na > GM_AMB_CAP) {
+                // pathological (massive exact ties): decide every row of the strip exactly
+                for (int r = 0; r < tk.nrows; ++r) {
+                    uint8_t* out = crp + pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch;
+                    for (int j = tid; j < NB; j += GM_THREADS) {
+                        const float dv = exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j);
+                        ++n_exact;
+                        out[j] = (dv <= s_th[r] && dv <= thB[j]) ? (uint8_t)CRP_DELTA_ONE : (uint8_t)CRP_DELTA_ZERO;
+                    }
+                }
+            } else {
+                for (int e = tid; e < na; e += GM_THREADS) {
+                    const int code = amb[e];
+                    const int r = code >> 24, j = code & 0xFFFFFF;
+                    const float dv = exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j);
+                    ++n_exact;
+                    if (dv <= s_th[r] && dv <= thB[j])
+                        crp[pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch + j] = (uint8_t)CRP_DELTA_ONE;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) atomicAdd(&counters[6], (unsigned long long)(clock64() - ph4));
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o);
+        max_err = fmaxf(max_err, __shfl_xor_sync(0xffffffffu, max_err, o));
+    }
+    if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
+    if (lane == 0 && max_err > 0.0f) atomicMax(&counters[14], (unsigned long long)__float_as_uint(max_err));
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) gm_tmem_free(tmem_base);
+}

@@ -133,7 +133,7 @@ def test_crp_exact_ties_duplicate_frames(ctx, oracle):
     assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]) and np.array_equal(R, Ro)
 
 
-@pytest.mark.parametrize("mode", [1, 2, 3])
+@pytest.mark.parametrize("mode", [1, 2, 3, 4])
 def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
     """exact-everywhere strips (mode 1) and approximate + band + exact re-check (mode 2) give the
     same bits as the oracle; sizes large enough for the band path (NB >= 128), ragged tiles."""
@@ -161,7 +161,7 @@ def test_crp_band_degenerate_inputs(ctx, oracle):
     half = np.concatenate([const[:150], rng.random((200, 12)).astype(np.float32)], 0)
     tracks = [const, silent, dup, half, _tracks(rng, [400])[0]]
     ctx.upload_tracks(tracks)
-    for mode in (2, 3):
+    for mode in (2, 3, 4):
         prm = ctx.params(crp_mode=mode)
         for (x, y) in [(0, 0), (0, 1), (1, 1), (2, 2), (2, 4), (3, 0), (3, 2), (4, 3), (1, 4)]:
             R, tq, tr, o = ctx.crp_pair(x, y, prm)
@@ -179,13 +179,13 @@ def test_band_vs_exact_mode_scores_large(ctx):
     ctx.upload_tracks(tracks)
     pairs = np.array([(i, j) for i in range(10) for j in range(10) if i < j], np.int32)
     q1, d1 = ctx.serra09_pairs(pairs, ctx.params(crp_mode=1), want_dmax=True)
-    for mode in (2, 3):
+    for mode in (2, 3, 4):
         q2, d2 = ctx.serra09_pairs(pairs, ctx.params(crp_mode=mode), want_dmax=True)
         st = ctx.pair_stats()
         assert np.array_equal(q1, q2) and np.array_equal(d1, d2), mode
         assert st["n_exact_cells"] < 0.02 * st["crp_cells"], (mode, st)
     R1 = ctx.crp_pair(0, 1, ctx.params(crp_mode=1))
-    for mode in (2, 3):
+    for mode in (2, 3, 4):
         R2 = ctx.crp_pair(0, 1, ctx.params(crp_mode=mode))
         assert all(np.array_equal(x, y) for x, y in zip(R1[:3], R2[:3])), mode
 

@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""Ad-hoc: per-phase cycle counters of the mode-4 CRP kernel at one track length."""
+import sys, os
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import acoss_b200
+from acoss_b200 import synth
+
+L = int(sys.argv[1]); mode = int(sys.argv[2])
+n = 64
+ctx = acoss_b200.Context(0)
+labels, works, tids, hp = synth.make_tracks(n // 2, 2, 0, 5, L, L)
+hp = [h[:L] for h in hp]
+ctx.upload_tracks(hp)
+i, j = np.triu_indices(n, 1)
+pairs = np.stack([i, j], 1).astype(np.int32)
+prm = ctx.params(crp_mode=mode)
+ctx.serra09_pairs(pairs, prm)
+ctx.serra09_pairs(pairs, prm)
+st = ctx.pair_stats(); c = ctx.debug_counters()
+tasks = max(1, c[7]); tiles = (L - 8 + 255) // 256
+print("dbg=%s L=%d crp %.1f ms; per strip kclk: sample %.1f pivots %.1f count %.1f (%.2f/tile) select %.1f binarise(pass2 strips) %.1f (%.2f/tile); fallback %d ovf %d miss %d" % (
+    os.environ.get("ACOSS_GEMM_DBG"), L, st["ms_crp"], c[2] / tasks / 1e3, c[3] / tasks / 1e3, c[4] / tasks / 1e3, c[4] / tasks / 1e3 / tiles,
+    c[5] / tasks / 1e3, c[6] / (tasks / 2) / 1e3, c[6] / (tasks / 2) / 1e3 / tiles, c[1], c[15], c[13]))
