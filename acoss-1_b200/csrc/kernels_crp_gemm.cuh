@@ -176,7 +176,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                       const float* __restrict__ selfdot,
                       float* __restrict__ thr, uint8_t* __restrict__ crp,
                       int side_a_is_query, float qf,
-                      float2* __restrict__ lists,            // [gridDim.x][GM_ROWS][4][GM_SUBCAP] (rho~, column) of the listed elements
+                      float2* __restrict__ lists,            // [gridDim.x][4][GM_SUBCAP][GM_ROWS] (rho~, column) of the listed elements
                       unsigned long long* __restrict__ counters, int dbg)
 {
     extern __shared__ __align__(128) unsigned char gsm[];
@@ -192,6 +192,8 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
     float* s_hiq = rowv + 5 * GM_ROWS;
     int* s_cnta = reinterpret_cast<int*>(rowv + 6 * GM_ROWS);
     int* s_lcnt = s_cnta + GM_ROWS;
+    int* s_nc = reinterpret_cast<int*>(s_loq);                           // candidates per row / rank among them: live before the
+    int* s_kx = reinterpret_cast<int*>(s_hiq);                           // binarise pass sets the band edges
     int* s_flag = s_lcnt + 4 * GM_ROWS;                                  // s_lcnt: [row][column group]
     float* Araw = reinterpret_cast<float*>(s_flag + GM_ROWS);            // [GM_ROWS + 8][12]
     uint64_t* mbar = reinterpret_cast<uint64_t*>(Araw + (GM_ROWS + 8) * ACOSS_NBINS);      // [2]
@@ -479,11 +481,12 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             __syncthreads();
         };
 
+        int ca = 0, ln = 0;      // count pass results of this thread: #(rho~ < pa), listed elements
         if (!tiny) {
             // ---- count pass: c_a = #(rho~ < pa); elements of [pa, pb) go to the row's list
             const float pa = s_pa[myrow], pb = s_pb[myrow];
-            int ca = 0, ln = 0;
-            float2* ml = my_lists + myrow * GM_LCAP + cg * GM_SUBCAP;       // private to this thread: no atomics
+            float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;        // slot s at ml[s * GM_ROWS]: private to this thread, no atomics;
+                                                                              // rows are adjacent, so reading a slot is coalesced across a warp
             stream([&](int jbase, int, int, const float (&v)[16]) {
                 if (!rowvalid) return;
 #pragma unroll
@@ -492,7 +495,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     const bool below = x < pa;
                     ca += below;
                     if (!below && x < pb) {
-                        ml[min(ln, GM_SUBCAP - 1)] = make_float2(x, __int_as_float(jbase + q));     // overflow is detected from ln
+                        ml[min(ln, GM_SUBCAP - 1) * GM_ROWS] = make_float2(x, __int_as_float(jbase + q));     // overflow is detected from ln
                         ++ln;
                     }
                 }
@@ -507,102 +510,244 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         // ---- select.  (A) warp per row: value bisection on the row's list, candidates (everything within 2E of the
         //      wanted order statistics) go to a pool in shared memory;  (B) thread per candidate: the exact 108-term
         //      chain in the oracle's op order;  (C) warp per row: exact order statistics among its candidates.
-        int* pool_col = reinterpret_cast<int*>(R1);                       // [GM_ROWS][32]
-        float* pool_val = reinterpret_cast<float*>(R1) + GM_ROWS * 32;     // rho~ (error statistics only)
-        float* pool_dex = pool_val + GM_ROWS * 32;                        // exact distances
-        int* s_off = reinterpret_cast<int*>(pool_dex + GM_ROWS * 32);     // [GM_ROWS + 1] candidate offsets
+        int* pool_col = reinterpret_cast<int*>(R1 + 98304);               // [GM_ROWS][32] candidate columns
+        float* pool_dex = reinterpret_cast<float*>(R1 + 114688);          // [GM_ROWS][32] rho~ of the candidate, then its exact distance
+        int* s_off = reinterpret_cast<int*>(R1 + GM_R1_BYTES + 4096);     // [GM_ROWS + 1] candidate offsets (behind the exchange buffers)
         if (!tiny) {
-            for (int r = warp; r < tk.nrows; r += GM_WARPS) {
-                const int4 c4 = *reinterpret_cast<const int4*>(s_lcnt + 4 * r);
-                const int c_a = s_cnta[r], c_ab = c4.x + c4.y + c4.z + c4.w;
-                const bool ovf = max(max(c4.x, c4.y), max(c4.z, c4.w)) > GM_SUBCAP;
-                bool ok = (c_a <= pr.lo) && (c_a + c_ab >= pr.hi + 1) && !ovf;
-                if (!ok && lane == 0) atomicAdd(&counters[ovf ? 15 : 13], 1ull);
-                const float pa = s_pa[r], pb = s_pb[r];
-                float w_lo = 0.f, w_hi = 0.f;
-                float lv[GM_LPL];
-                int li[GM_LPL];
-                int n_c = 0, kx = 0;
-                if (ok) {
-                    const float2* lst = my_lists + r * GM_LCAP;
-                    const int cseg[4] = {c4.x, c4.y, c4.z, c4.w};
-                    float vmin = INFINITY, vmax = -INFINITY;
+            // (A) four owner threads per row, each on its own sub-list (the elements it listed in the count pass; slots are
+            //     row-adjacent in memory, so a warp reads them coalesced).  One binning pass refines the bracket: 128
+            //     equal-width buckets over the list's value range (the list is close to uniform inside the narrow bracket, so
+            //     a bucket holds about two elements), per-row histograms in shared memory, a scan finds the bucket(s) of the
+            //     wanted ranks; a second pass collects the candidates: everything within 2E of those buckets.
+            int* xc = reinterpret_cast<int*>(R1 + GM_R1_BYTES);           // [2][GM_THREADS] exchange buffers (the per-warp scratch is free here)
+            float* xf = reinterpret_cast<float*>(xc);
+            unsigned* hist = reinterpret_cast<unsigned*>(R1);             // [GM_ROWS][64]: 128 packed 16-bit counters per row
+            const int xi = myrow * 4;
+            int4 c4 = make_int4(0, 0, 0, 0);
+            if (rowvalid) c4 = *reinterpret_cast<const int4*>(s_lcnt + 4 * myrow);
+            const int c_a = s_cnta[myrow], c_ab = c4.x + c4.y + c4.z + c4.w;
+            const bool ovf = max(max(c4.x, c4.y), max(c4.z, c4.w)) > GM_SUBCAP;
+            bool ok = rowvalid && (c_a <= pr.lo) && (c_a + c_ab >= pr.hi + 1) && !ovf;
+            if (rowvalid && !ok && cg == 0) atomicAdd(&counters[ovf ? 15 : 13], 1ull);
+            const float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;
+            const int n = ok ? ln : 0;
+            const float pa = s_pa[myrow], pb = s_pb[myrow];
+            for (int e = tid; e < GM_ROWS * 64; e += GM_THREADS) hist[e] = 0u;
+            // the sub-list goes to registers (64 values, all loads in flight at once) and shared memory (the next 48);
+            // the rare rest is re-read from L2
+            float* tailv = reinterpret_cast<float*>(R1 + 32768);          // [48][GM_THREADS]: sub-list entries 64 .. 111
+            float lv[64];
 #pragma unroll
-                    for (int q = 0; q < GM_LPL; ++q) {
-                        const int e = q * 32 + lane;                  // slot e: segment q / 4, offset (q % 4) * 32 + lane
-                        lv[q] = INFINITY; li[q] = 0;
-                        if ((q & 3) * 32 + lane < cseg[q >> 2]) {
-                            const float2 ent = lst[e];
-                            lv[q] = ent.x; li[q] = __float_as_int(ent.y);
-                            vmin = fminf(vmin, lv[q]); vmax = fmaxf(vmax, lv[q]);
-                        }
-                    }
-                    for (int o = 16; o > 0; o >>= 1) {
-                        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
-                        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-                    }
-                    // shrink [w_lo, w_hi) by value bisection while it keeps the wanted order statistic (rank kk of the
-                    // list), until it holds few elements.  invariant: #(list < w_lo) <= kk < #(list < w_hi)
-                    const int kk = pr.lo - c_a;
-                    w_lo = vmin; w_hi = INFINITY;
-                    int c_lo = 0, c_hi = c_ab;
-                    float b_hi = vmax;
-                    for (int it = 0; it < 24 && c_hi - c_lo > 3; ++it) {
-                        const float mid = 0.5f * (w_lo + b_hi);
-                        if (!(mid > w_lo) || !(mid < b_hi)) break;
-                        int cm = 0;
+            for (int q = 0; q < 64; ++q) lv[q] = (q < n) ? ml[q * GM_ROWS].x : INFINITY;
+            const int nmax_w = __reduce_max_sync(0xffffffffu, n);
+            for (int q0 = 64; q0 < min(nmax_w, 112); q0 += 16) {
+                float t[16];
 #pragma unroll
-                        for (int q = 0; q < GM_LPL; ++q) cm += (lv[q] < mid);
-                        cm = __reduce_add_sync(0xffffffffu, cm);
-                        if (cm <= kk) { w_lo = mid; c_lo = cm; }
-                        else { w_hi = mid; b_hi = mid; c_hi = cm; }
-                    }
-                    // the upper wanted order statistic (rank kk + 1) is inside the window or is the smallest element >= w_hi
-                    if (pr.hi != pr.lo && c_hi < kk + 2) {
-                        float nx = INFINITY;
+                for (int q = 0; q < 16; ++q) t[q] = (q0 + q < n) ? ml[(q0 + q) * GM_ROWS].x : INFINITY;
 #pragma unroll
-                        for (int q = 0; q < GM_LPL; ++q) if (lv[q] >= w_hi) nx = fminf(nx, lv[q]);
-                        for (int o = 16; o > 0; o >>= 1) nx = fminf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
-                        w_hi = nx;
-                    }
-                    // the candidate window (+- 2E) must lie strictly inside the list's value range [pa, pb)
-                    const float hi_edge = (w_hi == INFINITY) ? vmax : w_hi;
-                    ok = (w_lo - 2.0f * E > pa || pa == -GM_PMAX) && (hi_edge + 2.0f * E < pb || pb == GM_PMAX);
-                    if (!ok && lane == 0) atomicAdd(&counters[12], 1ull);
+                for (int q = 0; q < 16; ++q) tailv[(q0 + q - 64) * GM_THREADS + tid] = t[q];
+            }
+            // value range of the list: the pivots, unless a pivot is the "unbounded" sentinel
+            float vmin = pa, vmax = pb;
+            {
+                float lmin = INFINITY, lmax = -INFINITY;
+                const bool need = ok && (pa == -GM_PMAX || pb == GM_PMAX);
+                if (need)
+                    for (int q = 0; q < n; ++q) { const float x = ml[q * GM_ROWS].x; lmin = fminf(lmin, x); lmax = fmaxf(lmax, x); }
+                xf[xi + cg] = lmin; xf[GM_THREADS + xi + cg] = lmax;
+                __syncthreads();
+                if (need) {
+                    const float4 a = *reinterpret_cast<const float4*>(xf + xi), b = *reinterpret_cast<const float4*>(xf + GM_THREADS + xi);
+                    vmin = fminf(fminf(a.x, a.y), fminf(a.z, a.w));
+                    vmax = fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w));
+                    vmax = vmax + fabsf(vmax) * 1.0e-6f + 1.0e-30f;          // strictly above every element
                 }
+            }
+            // binning pass (monotone map value -> bucket)
+            const float bw = (vmax - vmin) * (1.0f / 128.0f);
+            const float bscale = (bw > 0.0f) ? 1.0f / bw : 0.0f;
+            {
+                unsigned* hrow = hist + myrow * 64;
+#pragma unroll
+                for (int q = 0; q < 64; ++q)
+                    if (q < n) {
+                        const int b = min(127, max(0, (int)((lv[q] - vmin) * bscale)));
+                        atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
+                    }
+                for (int q = 64; q < min(n, 112); ++q) {
+                    const int b = min(127, max(0, (int)((tailv[(q - 64) * GM_THREADS + tid] - vmin) * bscale)));
+                    atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
+                }
+                for (int q = 112; q < n; ++q) {
+                    const int b = min(127, max(0, (int)((ml[q * GM_ROWS].x - vmin) * bscale)));
+                    atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
+                }
+            }
+            __syncthreads();
+            // scan: owner cg takes buckets 32 cg .. 32 cg + 31; bucket b_lo holds rank kk, b_hi rank kk + (pr.hi - pr.lo)
+            const int kk = pr.lo - c_a, kk2 = kk + (pr.hi - pr.lo);
+            int hc[32], mysum = 0;
+            {
+                const uint4* hp = reinterpret_cast<const uint4*>(hist + myrow * 64 + 16 * cg);
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const uint4 h = hp[g];
+                    const unsigned hw[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { hc[8 * g + 2 * k] = hw[k] & 0xffffu; hc[8 * g + 2 * k + 1] = hw[k] >> 16; mysum += hc[8 * g + 2 * k] + hc[8 * g + 2 * k + 1]; }
+                }
+            }
+            xc[xi + cg] = mysum;
+            __syncthreads();
+            int b_lo = -1, b_hi = -1;
+            {
+                const int4 c = *reinterpret_cast<const int4*>(xc + xi);
+                const int cc[4] = {c.x, c.y, c.z, c.w};
+                int run = 0;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) if (g < cg) run += cc[g];
+#pragma unroll
+                for (int b = 0; b < 32; ++b) {
+                    const int nxt = run + hc[b];
+                    if (run <= kk && kk < nxt) b_lo = 32 * cg + b;
+                    if (run <= kk2 && kk2 < nxt) b_hi = 32 * cg + b;
+                    run = nxt;
+                }
+            }
+            __syncthreads();                 // xc is rewritten
+            xc[xi + cg] = b_lo; xc[GM_THREADS + xi + cg] = b_hi;
+            __syncthreads();
+            float c_min = 0.0f, c_max = 0.0f;
+            if (ok) {
+                const int4 a = *reinterpret_cast<const int4*>(xc + xi), b = *reinterpret_cast<const int4*>(xc + GM_THREADS + xi);
+                b_lo = max(max(a.x, a.y), max(a.z, a.w));
+                b_hi = max(max(b.x, b.y), max(b.z, b.w));
+                // bucket edges with 1 % slack for the rounding of the binning map, then the 2E band
+                const float w_lo = vmin + ((float)b_lo - 0.01f) * bw, w_hi = vmin + ((float)b_hi + 1.01f) * bw;
+                c_min = w_lo - 2.0f * E; c_max = w_hi + 2.0f * E;
+                // the candidate window must lie strictly inside the list's value range [pa, pb)
+                const bool inside = b_lo >= 0 && b_hi >= 0 && (c_min > pa || pa == -GM_PMAX) && (c_max < pb || pb == GM_PMAX);
+                if (!inside) { ok = false; if (cg == 0) atomicAdd(&counters[12], 1ull); }
+            }
+            // candidates = list elements in [c_min, c_max]; every exact order statistic is among them
+            {
+                int nb_l = 0, nc_l = 0;
                 if (ok) {
-                    // candidates = list elements in [w_lo - 2E, w_hi + 2E]; every exact order statistic is among them
+#pragma unroll
+                    for (int q = 0; q < 64; ++q) { nb_l += (lv[q] < c_min); nc_l += (lv[q] >= c_min && lv[q] <= c_max); }
+                    for (int q = 64; q < min(n, 112); ++q) { const float x = tailv[(q - 64) * GM_THREADS + tid]; nb_l += (x < c_min); nc_l += (x >= c_min && x <= c_max); }
+                    for (int q = 112; q < n; ++q) { const float x = ml[q * GM_ROWS].x; nb_l += (x < c_min); nc_l += (x >= c_min && x <= c_max); }
+                }
+                __syncthreads();             // xc is rewritten
+                xc[xi + cg] = nb_l | (nc_l << 16);
+                __syncthreads();
+                if (ok) {
+                    const int4 c = *reinterpret_cast<const int4*>(xc + xi);
+                    const int cc[4] = {c.x, c.y, c.z, c.w};
+                    int n_c = 0, n_b = 0, slot = 0;
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) { if (g < cg) slot += cc[g] >> 16; n_c += cc[g] >> 16; n_b += cc[g] & 0xffff; }
+                    const int kx = pr.lo - (c_a + n_b);
+                    if (kx < 0 || kx + (pr.hi - pr.lo) >= n_c) { ok = false; if (cg == 0) atomicAdd(&counters[9], 1ull); }
+                    else if (n_c > 32) { if (cg == 0) { s_nc[myrow] = 0; s_flag[myrow] = 2; } }      // non-uniform list: bisection below
+                    else {
+                        if (nc_l) {
+#pragma unroll
+                            for (int q = 0; q < 64; ++q)
+                                if (lv[q] >= c_min && lv[q] <= c_max) {
+                                    pool_col[myrow * 32 + slot] = __float_as_int(ml[q * GM_ROWS].y); pool_dex[myrow * 32 + slot] = lv[q]; ++slot;
+                                }
+                            for (int q = 64; q < n; ++q) {
+                                const float2 ent = ml[q * GM_ROWS];
+                                if (ent.x >= c_min && ent.x <= c_max) { pool_col[myrow * 32 + slot] = __float_as_int(ent.y); pool_dex[myrow * 32 + slot] = ent.x; ++slot; }
+                            }
+                        }
+                        if (cg == 0) { s_nc[myrow] = n_c; s_kx[myrow] = kx; }
+                    }
+                }
+                if (rowvalid && !ok && cg == 0) { s_nc[myrow] = 0; s_flag[myrow] = 1; atomicAdd(&counters[1], 1ull); }
+            }
+            __syncthreads();
+            // (A') rows whose bucket window held too many elements (the list is far from uniform): warp per row, value
+            //      bisection on the whole list until the window holds at most three elements
+            for (int r = warp; r < tk.nrows; r += GM_WARPS) {
+                if (s_flag[r] != 2) continue;
+                const int4 c4r = *reinterpret_cast<const int4*>(s_lcnt + 4 * r);
+                const int cseg[4] = {c4r.x, c4r.y, c4r.z, c4r.w};
+                const int c_ar = s_cnta[r], c_abr = c4r.x + c4r.y + c4r.z + c4r.w;
+                const float par = s_pa[r], pbr = s_pb[r];
+                const float2* lst = my_lists + r;
+                float l2[GM_LPL];
+                float vmn = INFINITY, vmx = -INFINITY;
+#pragma unroll
+                for (int q = 0; q < GM_LPL; ++q) {              // slot (q % 4) * 32 + lane of segment q / 4
+                    const int sl = (q & 3) * 32 + lane;
+                    l2[q] = INFINITY;
+                    if (sl < cseg[q >> 2]) { l2[q] = lst[((q >> 2) * GM_SUBCAP + sl) * GM_ROWS].x; vmn = fminf(vmn, l2[q]); vmx = fmaxf(vmx, l2[q]); }
+                }
+                for (int o = 16; o > 0; o >>= 1) {
+                    vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
+                    vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
+                }
+                const int kkr = pr.lo - c_ar;                   // invariant: #(list < w_lo) <= kkr < #(list < w_hi)
+                float w_lo = vmn, w_hi = INFINITY, b_hi = vmx;
+                int c_lo = 0, c_hi = c_abr;
+                for (int it = 0; it < 32 && c_hi - c_lo > 3; ++it) {
+                    const float mid = 0.5f * (w_lo + b_hi);
+                    if (!(mid > w_lo) || !(mid < b_hi)) break;
+                    int cm = 0;
+#pragma unroll
+                    for (int q = 0; q < GM_LPL; ++q) cm += (l2[q] < mid);
+                    cm = __reduce_add_sync(0xffffffffu, cm);
+                    if (cm <= kkr) { w_lo = mid; c_lo = cm; }
+                    else { w_hi = mid; b_hi = mid; c_hi = cm; }
+                }
+                if (pr.hi != pr.lo && c_hi < kkr + 2) {         // rank kkr + 1 is the smallest element >= w_hi
+                    float nx = INFINITY;
+#pragma unroll
+                    for (int q = 0; q < GM_LPL; ++q) if (l2[q] >= w_hi) nx = fminf(nx, l2[q]);
+                    for (int o = 16; o > 0; o >>= 1) nx = fminf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
+                    w_hi = nx;
+                }
+                const float hi_edge = (w_hi == INFINITY) ? vmx : w_hi;
+                bool okr = (w_lo - 2.0f * E > par || par == -GM_PMAX) && (hi_edge + 2.0f * E < pbr || pbr == GM_PMAX);
+                int n_c = 0, kx = 0;
+                if (okr) {
                     const float c_min = w_lo - 2.0f * E;
                     const float c_max = (w_hi == INFINITY) ? INFINITY : w_hi + 2.0f * E;
-                    int n_below = c_a;
+                    int n_below = c_ar;
 #pragma unroll
                     for (int q = 0; q < GM_LPL; ++q) {
-                        const bool valid = lv[q] != INFINITY;
-                        const bool below = valid && lv[q] < c_min;
-                        const bool cand = valid && !below && lv[q] <= c_max;
+                        const bool valid = l2[q] != INFINITY;
+                        const bool below = valid && l2[q] < c_min;
+                        const bool cand = valid && !below && l2[q] <= c_max;
                         n_below += __popc(__ballot_sync(0xffffffffu, below));
                         const unsigned mc = __ballot_sync(0xffffffffu, cand);
                         if (cand) {
                             const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
-                            if (slot < 32) { pool_col[r * 32 + slot] = li[q]; pool_val[r * 32 + slot] = lv[q]; }
+                            if (slot < 32) {
+                                pool_col[r * 32 + slot] = __float_as_int(lst[((q >> 2) * GM_SUBCAP + (q & 3) * 32 + lane) * GM_ROWS].y);
+                                pool_dex[r * 32 + slot] = l2[q];
+                            }
                         }
                         n_c += __popc(mc);
                     }
                     kx = pr.lo - n_below;
-                    if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) { ok = false; if (lane == 0) atomicAdd(&counters[11], 1ull); }
+                    if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) okr = false;
                 }
                 if (lane == 0) {
-                    s_lcnt[4 * r] = ok ? n_c : 0;
-                    s_lcnt[4 * r + 1] = kx;
-                    if (!ok) { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); }
+                    if (okr) { s_nc[r] = n_c; s_kx[r] = kx; s_flag[r] = 0; }
+                    else { s_nc[r] = 0; s_flag[r] = 1; atomicAdd(&counters[1], 1ull); atomicAdd(&counters[9], 1ull); }
                 }
             }
             __syncthreads();
+            long long sA = 0, sB = 0;
+            if (tid == 0) sA = clock64();
             // offsets of the rows' candidates in the flat task list
             if (warp == 0) {
                 int c[4], tot = 0;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) { const int r = 4 * lane + q; c[q] = (r < tk.nrows) ? s_lcnt[4 * r] : 0; tot += c[q]; }
+                for (int q = 0; q < 4; ++q) { const int r = 4 * lane + q; c[q] = (r < tk.nrows) ? s_nc[r] : 0; tot += c[q]; }
                 int incl = tot;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
@@ -646,15 +791,16 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     const float sa = s_xx[r], sb = __ldg(sdB + jj);
                     const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
                     float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
-                    max_err = fmaxf(max_err, fabsf(item - pool_val[r * 32 + slot]) / (sa + sb));
+                    max_err = fmaxf(max_err, fabsf(item - pool_dex[r * 32 + slot]) / (sa + sb));
                     if (item < 0.0f) item = 0.0f;
                     pool_dex[r * 32 + slot] = __fsqrt_rn(item);
                     ++n_exact;
                 }
             }
             __syncthreads();
+            if (tid == 0) { sB = clock64(); atomicAdd(&counters[10], (unsigned long long)(sA - ph3)); atomicAdd(&counters[11], (unsigned long long)(sB - sA)); }
             for (int r = warp; r < tk.nrows; r += GM_WARPS) {
-                const int n_c = s_lcnt[4 * r], kx = s_lcnt[4 * r + 1];
+                const int n_c = s_nc[r], kx = s_kx[r];
                 if (n_c == 0) continue;
                 const float dex = (lane < n_c) ? pool_dex[r * 32 + lane] : INFINITY;
                 // rank by comparison through shuffles (ties by lane), pick ranks kx and kx + 1
@@ -674,7 +820,8 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         }
         __syncthreads();
         // ---- rows that could not be bracketed (and tiny pairs): the whole row exactly, one row at a time
-        for (int r = 0; r < tk.nrows; ++r) {
+        const int any_flag = __syncthreads_or(tid < tk.nrows && s_flag[tid]);
+        for (int r = 0; any_flag && r < tk.nrows; ++r) {
             if (!s_flag[r]) continue;
             float* vr = reinterpret_cast<float*>(R1);
             for (int j = tid; j < NB; j += GM_THREADS) {
