@@ -38,6 +38,8 @@
 #define GM_TN 256                     // side-B embedded rows per tile = MMA N = TMEM columns per buffer
 #define GM_THREADS 512
 #define GM_WARPS (GM_THREADS / 32)
+#define GM_BLOCK (GM_THREADS + 128)   // + one MMA-issuing warp (tcgen05.mma issue blocks ~100 clk per instruction while the pipe is
+                                      // busy); warps are allocated in fours, the other three exit at once
 #define GM_S 512                      // sample columns per row (two MMA blocks of 256)
 #define GM_SPL (GM_S / 32)
 #define GM_SUBCAP 128                 // list capacity per (row, column group): private to the owning thread, no atomics
@@ -52,15 +54,15 @@
 #define GM_A_BYTES (6 * GM_APLANE + GM_ROWS * 16)       // 15 104
 #define GM_B_BYTES (6 * GM_BPLANE + GM_TN * 16)         // 29 440
 #define GM_SMP_CHUNKS 28
-#define GM_R1_BYTES (64 * GM_S * 4)                     // 131 072: sample operand / sample dump (64 rows) / B buffers + edges + ambiguity list / scratch
-#define GM_EDGE_OFF (2 * GM_B_BYTES)                    // column band edges lo[3][256], hi[3][256] (floats), slot = tile % 3
-#define GM_AMB_OFF 65536                                // ambiguity list (ints)
+#define GM_R1_BYTES (64 * GM_S * 4)                     // 131 072: sample operand / sample dump (64 rows) / 3 B buffers + edges + ambiguity list / scratch
+#define GM_EDGE_OFF (3 * GM_B_BYTES)                    // column band edges lo[4][256] (floats), slot = tile % 4
+#define GM_AMB_OFF 93184                                // ambiguity list (ints)
 #define GM_AMB_CAP ((GM_R1_BYTES - GM_AMB_OFF) / 4)
 #define GM_WSCR_WORDS 512                               // per-warp scratch: hist[256] | arow[108] cand[32]
 #define GM_ROWV_BYTES (GM_ROWS * 4)
 #define GM_ARAW_BYTES ((GM_ROWS + 8) * ACOSS_NBINS * 4)  // strip frames in the oracle's bin order, for the exact chains
 // shared memory: A planes | R1 | per-warp scratch | per-row arrays (pa pb thA xx loq hiq: float; cnta lcnt flag: int) | 2 mbarriers | tmem holder
-#define GM_SMEM_BYTES (GM_A_BYTES + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4 + 12 * GM_ROWV_BYTES + GM_ARAW_BYTES + 64)
+#define GM_SMEM_BYTES (GM_A_BYTES + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4 + 12 * GM_ROWV_BYTES + GM_ARAW_BYTES + 128)
 #define GM_TMEM_COLS 512
 #define GM_BIG 1.0e30f                 // norm entry of padding columns: rho~ = huge, never below a pivot or an edge
 #define GM_PMAX 1.0e29f                // "unbounded" pivots
@@ -100,6 +102,36 @@ __device__ __forceinline__ void gm_mma(uint32_t d_tmem, uint32_t adesc_lo, uint3
 }
 // low descriptor word of (base + byte offset, LBO): additive in the offset because shared memory addresses stay below 256 KB
 #define GM_DLO(base_lo, off, lbo) ((base_lo) + (((uint32_t)(off)) >> 4) + ((((uint32_t)(lbo)) >> 4) << 16))
+// barrier over the 16 consumer warps only (the producer warp never joins it)
+__device__ __forceinline__ void gm_csync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
+__device__ __forceinline__ int gm_csync_or(int pred)
+{
+    int r;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %1, 0;\n\t"
+        "bar.red.or.pred q, 1, 512, p;\n\t"
+        "selp.b32 %0, 1, 0, q;\n\t"
+        "}\n" : "=r"(r) : "r"(pred) : "memory");
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool gm_elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n" : "=r"(pred));
+    return pred != 0;
+}
+
 // 32 consecutive accumulator columns of this thread's TMEM lane
 __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, float (&v)[32])
 {
@@ -169,7 +201,7 @@ __device__ __forceinline__ void gm_issue_sample(uint32_t d_tmem, uint32_t a0, ui
 // counters: [0] exact cells  [1] fallback rows  [2..6] cycles (thread 0): stage+sample, pivots, count pass, select, binarise
 //           [7] tasks  [11] too many candidates  [12] window not inside the list  [13] bracket miss  [15] list overflow
 //           [14] max observed |rho~ - rho_oracle| / (xx + yy) (float bits)
-__global__ void __launch_bounds__(GM_THREADS, 1)
+__global__ void __launch_bounds__(GM_BLOCK, 1)
 crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                       const StripTask* __restrict__ tasks, int n_tasks,
                       const float* __restrict__ frames,
@@ -196,18 +228,25 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
     int* s_kx = reinterpret_cast<int*>(s_hiq);                           // binarise pass sets the band edges
     int* s_flag = s_lcnt + 4 * GM_ROWS;                                  // s_lcnt: [row][column group]
     float* Araw = reinterpret_cast<float*>(s_flag + GM_ROWS);            // [GM_ROWS + 8][12]
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(Araw + (GM_ROWS + 8) * ACOSS_NBINS);      // [2]
-    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 2);
-    float* s_red = reinterpret_cast<float*>(tmem_holder + 1);            // 8 words: reductions, ambiguity counter
+    // mbarriers: full[2] (MMAs of a tile done, by tcgen05.commit), empty[2] (a TMEM buffer has been read; one arrival per
+    // warp), built[3] (a side-B operand buffer has been written; one arrival per warp), smp (sample MMAs done)
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(Araw + (GM_ROWS + 8) * ACOSS_NBINS);
+    uint64_t* mb_full = mbar, *mb_empty = mbar + 2, *mb_built = mbar + 4, *mb_smp = mbar + 7;
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 8);
+    float* s_red = reinterpret_cast<float*>(tmem_holder + 2);            // 8 words: ambiguity counter, strip error bound for the producer
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lq = warp & 3, cg = warp >> 2;          // TMEM lane quarter (strip rows 32 lq ..), column group (64 cg ..)
     const int myrow = 32 * lq + lane;
     unsigned long long n_exact = 0;
-    uint32_t par0 = 0, par1 = 0;                      // mbarrier phase parities
+    uint32_t pf0 = 0, pf1 = 0, psmp = 0;              // mbarrier phase parities: full (every thread), sample
     float max_err = 0.0f;
 
     if (warp == 0) gm_tmem_alloc(tmem_holder);
-    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    if (tid == 0) {
+        mbar_init(mb_full, 1); mbar_init(mb_full + 1, 1); mbar_init(mb_empty, GM_WARPS); mbar_init(mb_empty + 1, GM_WARPS);
+        mbar_init(mb_built, GM_WARPS); mbar_init(mb_built + 1, GM_WARPS); mbar_init(mb_built + 2, GM_WARPS); mbar_init(mb_smp, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -216,6 +255,36 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
     const uint32_t a_saddr = smem_u32(Apl), r1_saddr = smem_u32(R1);
     float2* my_lists = lists + (size_t)blockIdx.x * GM_ROWS * GM_LCAP;
 
+    if (warp > GM_WARPS) {
+        // spare warps of the allocation quad: nothing to do
+    } else if (warp == GM_WARPS) {
+        // ================= MMA-issuing warp =================
+        // Mirrors the consumers' sequence of streaming passes (count pass unless the pair is tiny, binarise pass in pass 2).
+        // Per tile: wait until all 16 consumer warps have written their share of the side-B planes (built) and have read
+        // the TMEM buffer's previous contents (empty), then issue the 41 MMAs from one elected lane and commit to full.
+        uint32_t pbi = 0, pe0 = 1, pe1 = 1;               // a fresh mbarrier passes a wait on parity 1
+        for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
+            const StripTask tk = tasks[task];
+            const PairDesc pd = descs[tk.pair];
+            const int NB = side_a_is_query ? pd.N : pd.M;
+            const int n_tiles = (NB + GM_TN - 1) / GM_TN;
+            const bool tiny = NB < GM_MIN_NB;
+            for (int pass = 0; pass < 2; ++pass) {
+                if (pass == 0 ? tiny : !side_a_is_query) continue;
+                for (int t = 0; t < n_tiles; ++t) {
+                    const int buf = t & 1, sb = t % 3;
+                    mbar_wait(mb_built + sb, (pbi >> sb) & 1u); pbi ^= 1u << sb;
+                    if (buf == 0) { mbar_wait(mb_empty, pe0); pe0 ^= 1; } else { mbar_wait(mb_empty + 1, pe1); pe1 ^= 1; }
+                    tc_fence_after();
+                    if (gm_elect_one()) {
+                        if (!(dbg & 2)) gm_issue_tile(tmem_base + buf * GM_TN, a_saddr, r1_saddr + sb * GM_B_BYTES);
+                        umma_commit(mb_full + buf);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
     for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
         const StripTask tk = tasks[task];
         const PairDesc pd = descs[tk.pair];
@@ -238,7 +307,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         float* thr_out = thr + (side_a_is_query ? pd.thr_q_off : pd.thr_r_off);
         const bool tiny = NB < GM_MIN_NB;
 
-        __syncthreads();
+        gm_csync();
         long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
         if (tid == 0) { ph0 = clock64(); ph1 = ph0; ph2 = ph0; }
         // ---- stage the A planes: entry e = frame row0 + e (e < 136), chunk c3: -2 * rotated bins, hi / lo; norms
@@ -267,7 +336,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             if (tid < tk.nrows) { xx = sdA[tk.row0 + tid]; tf32_split(xx, nv.x, nv.y); nv.z = 1.0f; nv.w = 1.0f; }
             *reinterpret_cast<float4*>(Apl + 6 * GM_APLANE + tid * 16) = nv;
             s_xx[tid] = xx; s_flag[tid] = 0; s_cnta[tid] = 0;
-            s_pa[tid] = -GM_PMAX; s_pb[tid] = GM_PMAX;
+            s_pa[tid] = 0.0f; s_pb[tid] = 0.0f;
         }
         float ymax = 0.0f, xmax = 0.0f;
         for (int j = tid; j < NB; j += GM_THREADS) ymax = fmaxf(ymax, __ldg(sdB + j));
@@ -278,12 +347,13 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         }
         float* red = reinterpret_cast<float*>(R1);       // R1 is free here
         if (lane == 0) { red[warp] = ymax; red[GM_WARPS + warp] = xmax; }
-        __syncthreads();
+        gm_csync();
         ymax = red[0]; xmax = red[GM_WARPS];
 #pragma unroll
         for (int w = 1; w < GM_WARPS; ++w) { ymax = fmaxf(ymax, red[w]); xmax = fmaxf(xmax, red[GM_WARPS + w]); }
         const float E = GM_EPS_REL * (xmax + ymax);       // one bound for the whole strip (conservative)
-        __syncthreads();
+        const float plow = -(4.0f * (xmax + ymax) + 1.0e-30f);    // "unbounded below" pivot: under every rho~, small enough for rho~ - plow to be meaningful
+        gm_csync();
 
         if (!tiny) {
             // ---- sample: gather 2 x 256 spread columns into an explicit K-major operand (hi parts only; the pivots only
@@ -305,13 +375,13 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
                 fence_proxy_async_smem();
                 tc_fence_before();
-                __syncthreads();
+                gm_csync();
                 if (tid == 0) {
                     tc_fence_after();
                     gm_issue_sample(tmem_base + half * GM_TN, a_saddr, r1_saddr);
-                    umma_commit(mbar);
+                    umma_commit(mb_smp);
                 }
-                mbar_wait(mbar, par0); par0 ^= 1;       // the operand buffer is rebuilt for the second half
+                mbar_wait(mb_smp, psmp); psmp ^= 1;     // the operand buffer is rebuilt for the second half
                 tc_fence_after();
             }
             if (tid == 0) ph1 = clock64();
@@ -333,7 +403,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                         }
                 }
                 tc_fence_before();
-                __syncthreads();
+                gm_csync();
                 const float* smp = reinterpret_cast<const float*>(R1);
                 unsigned* hist = wscr;
                 const float frac = ((float)pr.lo + 0.5f) / (float)NB;
@@ -392,31 +462,34 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                         bb = __reduce_min_sync(0xffffffffu, bb);
                     }
                     if (lane == 0) {
-                        s_pa[r] = (r_lo >= 0 && ba > 0) ? fmaxf(smin + (float)ba * hwidth, -GM_PMAX) : -GM_PMAX;
+                        s_pa[r] = (r_lo >= 0 && ba > 0) ? fmaxf(smin + (float)ba * hwidth, plow) : plow;
                         s_pb[r] = (r_hi < GM_S && bb < 511) ? fminf(smin + (float)(bb + 1) * hwidth, GM_PMAX) : GM_PMAX;
                     }
                     __syncwarp();
                 }
-                __syncthreads();
+                gm_csync();
             }
         }
         if (tid == 0) ph2 = clock64();
 
-        // ---- tile streaming machinery
+        // ---- tile streaming.  Everything inside a pass is ordered by mbarriers, not CTA barriers: a warp runs the epilogue of
+        //      tile t out of TMEM buffer t % 2, releases it (empty), writes its share of the side-B planes of tile t + 2 into
+        //      shared-memory buffer (t + 2) % 3 (free: the MMAs of tile t - 1 are done) and signals built; the issuing warp
+        //      waits for all shares and for the TMEM buffer and issues the MMAs of tile t + 2.  The MMAs of tile t + 1 run
+        //      meanwhile.
         const float* thB = thr + pd.thr_r_off;            // column thresholds (pass 2)
-        // band edges of the column thresholds of a tile, slot = tile % 3: the slot written for tile t + 1 is read by
-        // neither the epilogue of tile t - 1 (slow warps) nor that of tile t
-        float* loC = reinterpret_cast<float*>(R1 + GM_EDGE_OFF);
-        float* hiC = loC + 3 * GM_TN;
+        float* loC = reinterpret_cast<float*>(R1 + GM_EDGE_OFF);      // [4][256] lower band edges of the column thresholds, slot = tile % 4:
+                                                                      // a warp writing tile t + 2 may run beside warps still reading tiles t - 1 and t
         // side-B planes of tile t (frames 256 t .. 256 t + 263, hi / lo split in registers), norms, column band edges
-        auto build_b = [&](int buf, int t, bool edges) {
-            unsigned char* Bb = R1 + buf * GM_B_BYTES;
+        auto build_b = [&](int t, bool edges) {
+            const int sb = t % 3;
+            unsigned char* Bb = R1 + sb * GM_B_BYTES;
             const int j0 = t * GM_TN;
             for (int e = tid; e < (GM_TN + 8) + GM_TN; e += GM_THREADS) {
                 if (e < GM_TN + 8) {
                     const int f = j0 + e;
                     float4 x[3];
-                    if (f < nb_frames) {
+                    if (f < nb_frames && !(dbg & 16)) {
                         const float4* fp = reinterpret_cast<const float4*>(fr_b + (int64_t)f * ACOSS_NBINS);
                         x[0] = __ldg(fp); x[1] = __ldg(fp + 1); x[2] = __ldg(fp + 2);
                     } else {
@@ -433,40 +506,29 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 } else {
                     const int c = e - (GM_TN + 8), j = j0 + c;
                     float4 nv = make_float4(1.0f, 1.0f, GM_BIG, 0.f);     // padding columns: rho~ huge
-                    float lo = -INFINITY, hi = -INFINITY;          // ... and never "in", always "out"
+                    float lo = -INFINITY;                          // ... and never "in", always "out"
                     if (j < NB) {
-                        nv.x = 1.0f; nv.y = 1.0f;
                         tf32_split(__ldg(sdB + j), nv.z, nv.w);
                         if (edges) {
                             const float tb = __ldg(thB + j);
                             const float Tr = xmul(tb, tb);
-                            const float mr = E + Tr * 4.76837158203125e-07f;        // E + 8uT
-                            lo = Tr - mr; hi = Tr + mr;
+                            lo = Tr - (E + Tr * 4.76837158203125e-07f);        // E + 8uT
                         }
                     }
                     *reinterpret_cast<float4*>(Bb + 6 * GM_BPLANE + c * 16) = nv;
-                    if (edges) { loC[(t % 3) * GM_TN + c] = lo; hiC[(t % 3) * GM_TN + c] = hi; }
+                    if (edges) loC[(t & 3) * GM_TN + c] = lo;
                 }
             }
-        };
-        // double-buffered pipeline: MMAs of tile t + 1 run under the epilogue of tile t
-        auto stream = [&](auto&& epi, bool edges) {
-            build_b(0, 0, edges);
             fence_proxy_async_smem();
-            tc_fence_before();
-            __syncthreads();
-            if (tid == 0) { tc_fence_after(); if (!(dbg & 2)) gm_issue_tile(tmem_base, a_saddr, r1_saddr); umma_commit(mbar); }
+        };
+        auto built = [&](int t) { __syncwarp(); if (lane == 0) mbar_arrive(mb_built + t % 3); };
+        auto stream = [&](auto&& epi, bool edges) {
+            gm_csync();                                   // every warp is done with R1 and with TMEM
+            build_b(0, edges); built(0);
+            if (n_tiles > 1) { build_b(1, edges); built(1); }
             for (int t = 0; t < n_tiles; ++t) {
                 const int buf = t & 1;
-                if (t + 1 < n_tiles && !(dbg & 4)) { build_b(buf ^ 1, t + 1, edges); fence_proxy_async_smem(); }
-                tc_fence_before();
-                __syncthreads();
-                if (t + 1 < n_tiles && tid == 0) {
-                    tc_fence_after();
-                    if (!(dbg & 2)) gm_issue_tile(tmem_base + (buf ^ 1) * GM_TN, a_saddr, r1_saddr + (buf ^ 1) * GM_B_BYTES);
-                    umma_commit(mbar + (buf ^ 1));
-                }
-                if (buf == 0) { mbar_wait(mbar, par0); par0 ^= 1; } else { mbar_wait(mbar + 1, par1); par1 ^= 1; }
+                if (buf == 0) { mbar_wait(mb_full, pf0); pf0 ^= 1; } else { mbar_wait(mb_full + 1, pf1); pf1 ^= 1; }
                 tc_fence_after();
                 // column ownership interleaved in runs of 16: thread (row, cg) reads columns 16 (4 i + cg) .. + 15, so that a
                 // cluster of consecutive in-band columns spreads over the four owners of the row
@@ -474,11 +536,14 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 for (int i = 0; i < 4; ++i) {
                     float v[16];
                     tmem_ld16(my_taddr + buf * GM_TN + 64 * i, v);
-                    if (!(dbg & 1)) epi(t * GM_TN + 64 * i + 16 * cg, t % 3, 64 * i + 16 * cg, v);
+                    if (!(dbg & 1)) epi(t * GM_TN + 64 * i + 16 * cg, t & 3, 64 * i + 16 * cg, v);
                 }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(mb_empty + buf);
+                if (t + 2 < n_tiles) { build_b(t + 2, edges); built(t + 2); }
             }
-            tc_fence_before();
-            __syncthreads();
+            gm_csync();
         };
 
         int ca = 0, ln = 0;      // count pass results of this thread: #(rho~ < pa), listed elements
@@ -487,15 +552,18 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             const float pa = s_pa[myrow], pb = s_pb[myrow];
             float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;        // slot s at ml[s * GM_ROWS]: private to this thread, no atomics;
                                                                               // rows are adjacent, so reading a slot is coalesced across a warp
+            // d = rho~ - pa: "below" is the sign bit of d, "inside [pa, pb)" is one unsigned compare of d's bit pattern against
+            // that of pb - pa (a negative d has the top bit set).  Elements within a rounding error of pb may be left out;
+            // the selection only trusts the list at least 2E away from pb.
+            const uint32_t wbits = __float_as_uint(pb - pa);
             stream([&](int jbase, int, int, const float (&v)[16]) {
                 if (!rowvalid) return;
 #pragma unroll
                 for (int q = 0; q < 16; ++q) {
-                    const float x = v[q];
-                    const bool below = x < pa;
-                    ca += below;
-                    if (!below && x < pb) {
-                        ml[min(ln, GM_SUBCAP - 1) * GM_ROWS] = make_float2(x, __int_as_float(jbase + q));     // overflow is detected from ln
+                    const uint32_t u = __float_as_uint(v[q] - pa);
+                    ca += u >> 31;
+                    if (u < wbits) {
+                        if (!(dbg & 8)) ml[min(ln, GM_SUBCAP - 1) * GM_ROWS] = make_float2(v[q], __int_as_float(jbase + q));     // overflow is detected from ln
                         ++ln;
                     }
                 }
@@ -503,7 +571,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             if (rowvalid) s_lcnt[myrow * 4 + cg] = ln;
             if (rowvalid) atomicAdd(&s_cnta[myrow], ca);
             __threadfence_block();
-            __syncthreads();
+            gm_csync();
         }
         if (tid == 0) ph3 = clock64();
 
@@ -528,7 +596,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             const int c_a = s_cnta[myrow], c_ab = c4.x + c4.y + c4.z + c4.w;
             const bool ovf = max(max(c4.x, c4.y), max(c4.z, c4.w)) > GM_SUBCAP;
             bool ok = rowvalid && (c_a <= pr.lo) && (c_a + c_ab >= pr.hi + 1) && !ovf;
-            if (rowvalid && !ok && cg == 0) atomicAdd(&counters[ovf ? 15 : 13], 1ull);
+            if (rowvalid && !ok && cg == 0 && ovf) atomicAdd(&counters[15], 1ull);
             const float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;
             const int n = ok ? ln : 0;
             const float pa = s_pa[myrow], pb = s_pb[myrow];
@@ -551,11 +619,11 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             float vmin = pa, vmax = pb;
             {
                 float lmin = INFINITY, lmax = -INFINITY;
-                const bool need = ok && (pa == -GM_PMAX || pb == GM_PMAX);
+                const bool need = ok && (pa == plow || pb == GM_PMAX);
                 if (need)
                     for (int q = 0; q < n; ++q) { const float x = ml[q * GM_ROWS].x; lmin = fminf(lmin, x); lmax = fmaxf(lmax, x); }
                 xf[xi + cg] = lmin; xf[GM_THREADS + xi + cg] = lmax;
-                __syncthreads();
+                gm_csync();
                 if (need) {
                     const float4 a = *reinterpret_cast<const float4*>(xf + xi), b = *reinterpret_cast<const float4*>(xf + GM_THREADS + xi);
                     vmin = fminf(fminf(a.x, a.y), fminf(a.z, a.w));
@@ -583,7 +651,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
                 }
             }
-            __syncthreads();
+            gm_csync();
             // scan: owner cg takes buckets 32 cg .. 32 cg + 31; bucket b_lo holds rank kk, b_hi rank kk + (pr.hi - pr.lo)
             const int kk = pr.lo - c_a, kk2 = kk + (pr.hi - pr.lo);
             int hc[32], mysum = 0;
@@ -598,7 +666,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
             }
             xc[xi + cg] = mysum;
-            __syncthreads();
+            gm_csync();
             int b_lo = -1, b_hi = -1;
             {
                 const int4 c = *reinterpret_cast<const int4*>(xc + xi);
@@ -614,9 +682,9 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     run = nxt;
                 }
             }
-            __syncthreads();                 // xc is rewritten
+            gm_csync();                 // xc is rewritten
             xc[xi + cg] = b_lo; xc[GM_THREADS + xi + cg] = b_hi;
-            __syncthreads();
+            gm_csync();
             float c_min = 0.0f, c_max = 0.0f;
             if (ok) {
                 const int4 a = *reinterpret_cast<const int4*>(xc + xi), b = *reinterpret_cast<const int4*>(xc + GM_THREADS + xi);
@@ -626,8 +694,8 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 const float w_lo = vmin + ((float)b_lo - 0.01f) * bw, w_hi = vmin + ((float)b_hi + 1.01f) * bw;
                 c_min = w_lo - 2.0f * E; c_max = w_hi + 2.0f * E;
                 // the candidate window must lie strictly inside the list's value range [pa, pb)
-                const bool inside = b_lo >= 0 && b_hi >= 0 && (c_min > pa || pa == -GM_PMAX) && (c_max < pb || pb == GM_PMAX);
-                if (!inside) { ok = false; if (cg == 0) atomicAdd(&counters[12], 1ull); }
+                const bool inside = b_lo >= 0 && b_hi >= 0 && (c_min > pa || pa == plow) && (c_max < pb || pb == GM_PMAX);
+                if (!inside) { ok = false;  }
             }
             // candidates = list elements in [c_min, c_max]; every exact order statistic is among them
             {
@@ -638,9 +706,9 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     for (int q = 64; q < min(n, 112); ++q) { const float x = tailv[(q - 64) * GM_THREADS + tid]; nb_l += (x < c_min); nc_l += (x >= c_min && x <= c_max); }
                     for (int q = 112; q < n; ++q) { const float x = ml[q * GM_ROWS].x; nb_l += (x < c_min); nc_l += (x >= c_min && x <= c_max); }
                 }
-                __syncthreads();             // xc is rewritten
+                gm_csync();             // xc is rewritten
                 xc[xi + cg] = nb_l | (nc_l << 16);
-                __syncthreads();
+                gm_csync();
                 if (ok) {
                     const int4 c = *reinterpret_cast<const int4*>(xc + xi);
                     const int cc[4] = {c.x, c.y, c.z, c.w};
@@ -648,7 +716,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
 #pragma unroll
                     for (int g = 0; g < 4; ++g) { if (g < cg) slot += cc[g] >> 16; n_c += cc[g] >> 16; n_b += cc[g] & 0xffff; }
                     const int kx = pr.lo - (c_a + n_b);
-                    if (kx < 0 || kx + (pr.hi - pr.lo) >= n_c) { ok = false; if (cg == 0) atomicAdd(&counters[9], 1ull); }
+                    if (kx < 0 || kx + (pr.hi - pr.lo) >= n_c) { ok = false;  }
                     else if (n_c > 32) { if (cg == 0) { s_nc[myrow] = 0; s_flag[myrow] = 2; } }      // non-uniform list: bisection below
                     else {
                         if (nc_l) {
@@ -667,7 +735,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
                 if (rowvalid && !ok && cg == 0) { s_nc[myrow] = 0; s_flag[myrow] = 1; atomicAdd(&counters[1], 1ull); }
             }
-            __syncthreads();
+            gm_csync();
             // (A') rows whose bucket window held too many elements (the list is far from uniform): warp per row, value
             //      bisection on the whole list until the window holds at most three elements
             for (int r = warp; r < tk.nrows; r += GM_WARPS) {
@@ -710,7 +778,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     w_hi = nx;
                 }
                 const float hi_edge = (w_hi == INFINITY) ? vmx : w_hi;
-                bool okr = (w_lo - 2.0f * E > par || par == -GM_PMAX) && (hi_edge + 2.0f * E < pbr || pbr == GM_PMAX);
+                bool okr = (w_lo - 2.0f * E > par || par == plow) && (hi_edge + 2.0f * E < pbr || pbr == GM_PMAX);
                 int n_c = 0, kx = 0;
                 if (okr) {
                     const float c_min = w_lo - 2.0f * E;
@@ -737,12 +805,10 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
                 if (lane == 0) {
                     if (okr) { s_nc[r] = n_c; s_kx[r] = kx; s_flag[r] = 0; }
-                    else { s_nc[r] = 0; s_flag[r] = 1; atomicAdd(&counters[1], 1ull); atomicAdd(&counters[9], 1ull); }
+                    else { s_nc[r] = 0; s_flag[r] = 1; atomicAdd(&counters[1], 1ull); }
                 }
             }
-            __syncthreads();
-            long long sA = 0, sB = 0;
-            if (tid == 0) sA = clock64();
+            gm_csync();
             // offsets of the rows' candidates in the flat task list
             if (warp == 0) {
                 int c[4], tot = 0;
@@ -756,7 +822,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 for (int q = 0; q < 4; ++q) { s_off[4 * lane + q] = run; run += c[q]; }
                 if (lane == 31) s_off[GM_ROWS] = run;
             }
-            __syncthreads();
+            gm_csync();
             {
                 int cbs[ACOSS_NBINS];                                     // oracle bin c -> bin of the side-B frame
 #pragma unroll
@@ -797,8 +863,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     ++n_exact;
                 }
             }
-            __syncthreads();
-            if (tid == 0) { sB = clock64(); atomicAdd(&counters[10], (unsigned long long)(sA - ph3)); atomicAdd(&counters[11], (unsigned long long)(sB - sA)); }
+            gm_csync();
             for (int r = warp; r < tk.nrows; r += GM_WARPS) {
                 const int n_c = s_nc[r], kx = s_kx[r];
                 if (n_c == 0) continue;
@@ -818,9 +883,9 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         } else if (tid < GM_ROWS) {
             s_flag[tid] = 1;
         }
-        __syncthreads();
+        gm_csync();
         // ---- rows that could not be bracketed (and tiny pairs): the whole row exactly, one row at a time
-        const int any_flag = __syncthreads_or(tid < tk.nrows && s_flag[tid]);
+        const int any_flag = gm_csync_or(tid < tk.nrows && s_flag[tid]);
         for (int r = 0; any_flag && r < tk.nrows; ++r) {
             if (!s_flag[r]) continue;
             float* vr = reinterpret_cast<float*>(R1);
@@ -829,14 +894,14 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                                         : exact_dist(frames, pd, rot, selfdot, j, tk.row0 + r);
                 ++n_exact;
             }
-            __syncthreads();
+            gm_csync();
             if (warp == 0) {
                 float v_hi;
                 const float v_lo = warp_select_pair(vr, NB, pr.lo, lane, v_hi);
                 const float t = percentile_combine(pr, v_lo, v_hi);
                 if (lane == 0) { s_th[r] = t; thr_out[tk.row0 + r] = t; }
             }
-            __syncthreads();
+            gm_csync();
         }
         if (tid == 0) {
             ph4 = clock64();
@@ -859,39 +924,44 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             const float Tq = xmul(ta, ta);
             const float mq = E + Tq * 4.76837158203125e-07f;
             s_loq[tid] = Tq - mq;
-            s_hiq[tid] = Tq + mq;
         }
-        __syncthreads();
+        gm_csync();
         {
-            const float lo_q = s_loq[myrow], hi_q = s_hiq[myrow];
+            const float lo_q = s_loq[myrow];
             const uint32_t zero_word = (CRP_DELTA_ZERO) | (CRP_DELTA_ZERO << 8) | (CRP_DELTA_ZERO << 16) | (CRP_DELTA_ZERO << 24);
             const uint32_t flip = CRP_DELTA_ZERO ^ CRP_DELTA_ONE;
             uint8_t* orow = crp + pd.crp_off + (int64_t)(tk.row0 + myrow) * pd.pitch;
             const int pitch = pd.pitch;
+            // d = rho~ - min(lo_q, lo_r[j]): the sign bit of d is "surely in"; 0 <= d <= W (one unsigned compare on the bit
+            // pattern) is "ambiguous", where W bounds the width of every band (hi - lo <= 2 (E + 8u T) < 2.2 E).  The four sign
+            // bits of a group become the four CRP bytes with three PRMTs (sign replication) and one LOP3.
+            const uint32_t wamb = __float_as_uint(2.2f * E);
             stream([&](int jbase, int slot, int cbase, const float (&v)[16]) {
                 const float4* lc = reinterpret_cast<const float4*>(loC + slot * GM_TN + cbase);
-                const float4* hc = reinterpret_cast<const float4*>(hiC + slot * GM_TN + cbase);
-                uint32_t w[4];
+                uint32_t w[4], amask = 0;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    const float4 l4 = lc[g], h4 = hc[g];
-                    const float x0 = v[4 * g], x1 = v[4 * g + 1], x2 = v[4 * g + 2], x3 = v[4 * g + 3];
-                    const bool i0 = x0 < fminf(lo_q, l4.x), i1 = x1 < fminf(lo_q, l4.y);
-                    const bool i2 = x2 < fminf(lo_q, l4.z), i3 = x3 < fminf(lo_q, l4.w);
-                    const bool o0 = x0 > fminf(hi_q, h4.x), o1 = x1 > fminf(hi_q, h4.y);
-                    const bool o2 = x2 > fminf(hi_q, h4.z), o3 = x3 > fminf(hi_q, h4.w);
-                    w[g] = zero_word ^ ((i0 ? flip : 0u) | (i1 ? flip << 8 : 0u) | (i2 ? flip << 16 : 0u) | (i3 ? flip << 24 : 0u));
-                    if (!((i0 | o0) & (i1 | o1) & (i2 | o2) & (i3 | o3)) && rowvalid) {
-                        const bool am[4] = {!(i0 | o0), !(i1 | o1), !(i2 | o2), !(i3 | o3)};
-#pragma unroll
-                        for (int b = 0; b < 4; ++b)
-                            if (am[b]) {
-                                const int slot_ = atomicAdd(amb_cnt, 1);
-                                if (slot_ < GM_AMB_CAP) amb[slot_] = (myrow << 24) | (jbase + 4 * g + b);
-                            }
-                    }
+                    const float4 l4 = lc[g];
+                    const uint32_t u0 = __float_as_uint(v[4 * g] - fminf(lo_q, l4.x)), u1 = __float_as_uint(v[4 * g + 1] - fminf(lo_q, l4.y));
+                    const uint32_t u2 = __float_as_uint(v[4 * g + 2] - fminf(lo_q, l4.z)), u3 = __float_as_uint(v[4 * g + 3] - fminf(lo_q, l4.w));
+                    uint32_t s01, s23, sg;
+                    asm("prmt.b32 %0, %1, %2, 0x00fb;" : "=r"(s01) : "r"(u0), "r"(u1));      // sign-replicated top bytes of u0, u1
+                    asm("prmt.b32 %0, %1, %2, 0x00fb;" : "=r"(s23) : "r"(u2), "r"(u3));
+                    asm("prmt.b32 %0, %1, %2, 0x5410;" : "=r"(sg) : "r"(s01), "r"(s23));
+                    w[g] = zero_word ^ (sg & (flip * 0x01010101u));
+                    if (min(min(u0, u1), min(u2, u3)) <= wamb)
+                        amask |= ((uint32_t)(u0 <= wamb) | ((uint32_t)(u1 <= wamb) << 1) | ((uint32_t)(u2 <= wamb) << 2) | ((uint32_t)(u3 <= wamb) << 3)) << (4 * g);
                 }
                 if (rowvalid && jbase + 16 <= pitch) *reinterpret_cast<uint4*>(orow + jbase) = make_uint4(w[0], w[1], w[2], w[3]);
+                if (amask && rowvalid) {
+                    int at = atomicAdd(amb_cnt, __popc(amask));
+                    while (amask) {
+                        const int b = __ffs(amask) - 1;
+                        amask &= amask - 1;
+                        if (at < GM_AMB_CAP) amb[at] = (myrow << 24) | (jbase + b);
+                        ++at;
+                    }
+                }
             }, true);
             // columns past the last tile up to the pitch
             const int done = n_tiles * GM_TN;
@@ -903,7 +973,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
             }
         }
-        __syncthreads();
+        gm_csync();
         {
             const int na = *amb_cnt;
             if (na > GM_AMB_CAP) {
@@ -927,7 +997,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
             }
         }
-        __syncthreads();
+        gm_csync();
         if (tid == 0) atomicAdd(&counters[6], (unsigned long long)(clock64() - ph4));
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -936,6 +1006,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
     }
     if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
     if (lane == 0 && max_err > 0.0f) atomicMax(&counters[14], (unsigned long long)__float_as_uint(max_err));
+    }
     tc_fence_before();
     __syncthreads();
     if (warp == 0) gm_tmem_free(tmem_base);

@@ -22,4 +22,3 @@ tasks = max(1, c[7]); tiles = (L - 8 + 255) // 256
 print("dbg=%s L=%d crp %.1f ms; per strip kclk: sample %.1f pivots %.1f count %.1f (%.2f/tile) select %.1f binarise(pass2 strips) %.1f (%.2f/tile); fallback %d ovf %d miss %d" % (
     os.environ.get("ACOSS_GEMM_DBG"), L, st["ms_crp"], c[2] / tasks / 1e3, c[3] / tasks / 1e3, c[4] / tasks / 1e3, c[4] / tasks / 1e3 / tiles,
     c[5] / tasks / 1e3, c[6] / (tasks / 2) / 1e3, c[6] / (tasks / 2) / 1e3 / tiles, c[1], c[15], c[13]))
-print("   select: A total %.1f kclk, B %.1f kclk; fail reasons: window %d candidates %d" % (c[10] / tasks / 1e3, c[11] / tasks / 1e3, c[12], c[9]))
