@@ -308,10 +308,15 @@ def run_ours(args, rank, world, local_rank):
         {"kernel": "dp_rowpar_kernel (Qmax)", "bound": "hbm", "achieved": dp_gbs, "peak": pk["hbm"], "unit": "GB/s",
          "frac": dp_gbs / pk["hbm"], "traffic": None, "ms_per_step": ms_dp, "launches_per_step": n_dp_launch,
          "gcups": gcups, "share_of_step": ms_dp / ms_tot},
-        {"kernel": "crp_strip kernels (cross-similarity + thresholds + binarise)", "bound": "tensor", "achieved": crp_tflops,
+        {"kernel": "crp_strip_gemm_kernel x2 (cross-similarity + thresholds + binarise)" if args.crp_mode in (0, 4)
+                   else "crp_strip kernels (cross-similarity + thresholds + binarise)",
+         "bound": "tensor", "achieved": crp_tflops,
          "peak": pk["bf16_sus"], "unit": "TFLOP/s", "frac": crp_tflops / pk["bf16_sus"], "traffic": None,
          "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
-         "note": "algorithmic flop = (2*108+5)*M*N per pair; runs on the fp32 CUDA cores (bit-exact op order), see DESIGN.md"},
+         "note": "algorithmic flop = (2*108+5)*M*N per pair (SURVEY 8(d)), peak = measured dense bf16. The kernel runs the "
+                 "contraction 2.5 times (column thresholds, row thresholds, binarise) as 3-product TF32 splits on tcgen05 "
+                 "(41 MMAs of 128x256x8 per tile = 664 executed flop per cell and pass, dense TF32 peak is half the bf16 "
+                 "figure) and decides everything near a threshold with exact fp32 chains; see DESIGN.md"},
     ]
     dominant = max(kernels, key=lambda k: k["ms_per_step"])
     roofline = {k: dominant[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}

@@ -51,7 +51,10 @@ typedef struct acoss_crp_params {
     float   dis_onset;      /* CoverSongSimilarity disOnset, default 0.5      */
     float   dis_extension;  /* CoverSongSimilarity disExtension, default 0.5  */
     int32_t crp_mode;       /* 0 = auto, 1 = exact-everywhere strips,
-                               2 = approximate + rigorous band + exact recheck */
+                               2 = approximate (FMA sliding Gram) + rigorous band + exact recheck,
+                               3 = same with tcgen05 G2 tiles, 4 = tcgen05 GEMM cross-similarity
+                               (128 x 256 tiles, Hankel operands) + band + exact recheck.
+                               Every mode returns the same bits.                 */
 } acoss_crp_params;
 
 /* Timing / accounting of the last pair call (device time by CUDA events on the
