@@ -198,6 +198,32 @@ __device__ __forceinline__ void gm_issue_sample(uint32_t d_tmem, uint32_t a0, ui
     gm_mma(d_tmem, GM_DLO(al, 2 * GM_APLANE + 128, 4 * GM_APLANE - 128), GM_DLO(sl, 26 * (GM_TN * 16), GM_TN * 16), 1);
 }
 
+// One frame (12 terms) of the oracle's sequential chain: acc += a[c] * b[(c + OFF) % 12], c ascending, no FMA.
+template <int OFF>
+__device__ __forceinline__ float gm_chain12(float acc, const float (&a)[12], const float (&b)[12])
+{
+#pragma unroll
+    for (int c = 0; c < 12; ++c) acc = xadd(acc, xmul(a[c], b[(c + OFF) % 12]));
+    return acc;
+}
+__device__ __forceinline__ float gm_chain12_rot(float acc, const float (&a)[12], const float (&b)[12], int off)
+{
+    switch (off) {          // uniform per task
+    case 0: return gm_chain12<0>(acc, a, b);
+    case 1: return gm_chain12<1>(acc, a, b);
+    case 2: return gm_chain12<2>(acc, a, b);
+    case 3: return gm_chain12<3>(acc, a, b);
+    case 4: return gm_chain12<4>(acc, a, b);
+    case 5: return gm_chain12<5>(acc, a, b);
+    case 6: return gm_chain12<6>(acc, a, b);
+    case 7: return gm_chain12<7>(acc, a, b);
+    case 8: return gm_chain12<8>(acc, a, b);
+    case 9: return gm_chain12<9>(acc, a, b);
+    case 10: return gm_chain12<10>(acc, a, b);
+    default: return gm_chain12<11>(acc, a, b);
+    }
+}
+
 // counters: [0] exact cells  [1] fallback rows  [2..6] cycles (thread 0): stage+sample, pivots, count pass, select, binarise
 //           [7] tasks  [11] too many candidates  [12] window not inside the list  [13] bracket miss  [15] list overflow
 //           [14] max observed |rho~ - rho_oracle| / (xx + yy) (float bits)
@@ -824,9 +850,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             }
             gm_csync();
             {
-                int cbs[ACOSS_NBINS];                                     // oracle bin c -> bin of the side-B frame
-#pragma unroll
-                for (int c = 0; c < ACOSS_NBINS; ++c) cbs[c] = side_a_is_query ? rot_src(c, rot) : c;
+                const int boff = side_a_is_query ? (ACOSS_NBINS - rot) % ACOSS_NBINS : 0;     // rot_src(c, rot) = (c + boff) % 12
                 const int n_tasks_c = s_off[GM_ROWS];
                 for (int idx = tid; idx < n_tasks_c; idx += GM_THREADS) {
                     int r = 0;                                            // last row with s_off[r] <= idx
@@ -834,25 +858,18 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     for (int st = 64; st > 0; st >>= 1) if (s_off[r + st] <= idx) r += st;
                     const int slot = idx - s_off[r];
                     const int jj = pool_col[r * 32 + slot];
-                    const float* bp = fr_b + (int64_t)jj * ACOSS_NBINS;
+                    const float4* bp = reinterpret_cast<const float4*>(fr_b + (int64_t)jj * ACOSS_NBINS);
                     const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
                     float acc = 0.0f;
+                    // oracle bin c of the side-B frame is its bin cbs[c] = (c + boff) % 12: whole frames are loaded as three
+                    // 16-byte vectors and the rotation is resolved at compile time inside a uniform switch
 #pragma unroll 3
                     for (int s_ = 0; s_ < 9; ++s_) {
                         const float4 a0 = as[3 * s_], a1 = as[3 * s_ + 1], a2 = as[3 * s_ + 2];
-                        const float* bs = bp + s_ * ACOSS_NBINS;
-                        acc = xadd(acc, xmul(a0.x, __ldg(bs + cbs[0])));
-                        acc = xadd(acc, xmul(a0.y, __ldg(bs + cbs[1])));
-                        acc = xadd(acc, xmul(a0.z, __ldg(bs + cbs[2])));
-                        acc = xadd(acc, xmul(a0.w, __ldg(bs + cbs[3])));
-                        acc = xadd(acc, xmul(a1.x, __ldg(bs + cbs[4])));
-                        acc = xadd(acc, xmul(a1.y, __ldg(bs + cbs[5])));
-                        acc = xadd(acc, xmul(a1.z, __ldg(bs + cbs[6])));
-                        acc = xadd(acc, xmul(a1.w, __ldg(bs + cbs[7])));
-                        acc = xadd(acc, xmul(a2.x, __ldg(bs + cbs[8])));
-                        acc = xadd(acc, xmul(a2.y, __ldg(bs + cbs[9])));
-                        acc = xadd(acc, xmul(a2.z, __ldg(bs + cbs[10])));
-                        acc = xadd(acc, xmul(a2.w, __ldg(bs + cbs[11])));
+                        const float4 b0 = __ldg(bp + 3 * s_), b1 = __ldg(bp + 3 * s_ + 1), b2 = __ldg(bp + 3 * s_ + 2);
+                        const float av[12] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w};
+                        const float bv[12] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+                        acc = gm_chain12_rot(acc, av, bv, boff);
                     }
                     const float sa = s_xx[r], sb = __ldg(sdB + jj);
                     const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
