@@ -1004,10 +1004,25 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     }
                 }
             } else {
+                // pass 2: side A = query (rows staged in Araw in the oracle's order), side B = reference, rotated by boff
+                const int boff = (ACOSS_NBINS - rot) % ACOSS_NBINS;
                 for (int e = tid; e < na; e += GM_THREADS) {
                     const int code = amb[e];
                     const int r = code >> 24, j = code & 0xFFFFFF;
-                    const float dv = exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j);
+                    const float4* bp = reinterpret_cast<const float4*>(fr_b + (int64_t)j * ACOSS_NBINS);
+                    const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
+                    float acc = 0.0f;
+#pragma unroll 3
+                    for (int s_ = 0; s_ < 9; ++s_) {
+                        const float4 a0 = as[3 * s_], a1 = as[3 * s_ + 1], a2 = as[3 * s_ + 2];
+                        const float4 b0 = __ldg(bp + 3 * s_), b1 = __ldg(bp + 3 * s_ + 1), b2 = __ldg(bp + 3 * s_ + 2);
+                        const float av[12] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w};
+                        const float bv[12] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+                        acc = gm_chain12_rot(acc, av, bv, boff);
+                    }
+                    float item = xadd(xsub(s_xx[r], xmul(2.0f, acc)), __ldg(sdB + j));
+                    if (item < 0.0f) item = 0.0f;
+                    const float dv = __fsqrt_rn(item);
                     ++n_exact;
                     if (dv <= s_th[r] && dv <= thB[j])
                         crp[pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch + j] = (uint8_t)CRP_DELTA_ONE;
