@@ -151,6 +151,22 @@ def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
             assert np.array_equal(R, Ro), (mode, a, b)
 
 
+@pytest.mark.parametrize("kappa", [0.004, 0.02, 0.5, 0.93, 1.0, 0.0])
+def test_crp_gemm_extreme_percentiles(ctx, oracle, kappa):
+    """tensor-core kernel with brackets that are unbounded below / above (tiny and huge percentiles), ragged last tiles
+    and strips, against the oracle"""
+    rng = np.random.default_rng(77)
+    tracks = _tracks(rng, [300, 521, 777], noise=0.12)
+    ctx.upload_tracks(tracks)
+    prm = ctx.params(kappa=kappa, crp_mode=4)
+    for (a, b) in [(0, 1), (1, 2), (2, 0)]:
+        R, tq, tr, o = ctx.crp_pair(a, b, prm)
+        Ro, info = oracle.chroma_cross_similarity(tracks[a], tracks[b], kappa=kappa, full=True)
+        assert o == info["oti"]
+        assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]), (kappa, a, b)
+        assert np.array_equal(R, Ro), (kappa, a, b)
+
+
 def test_crp_band_degenerate_inputs(ctx, oracle):
     """constant / silent / duplicated frames: massive exact ties force the band kernel's fallbacks"""
     rng = np.random.default_rng(12)
