@@ -40,7 +40,11 @@
 #define GM_WARPS (GM_THREADS / 32)
 #define GM_BLOCK (GM_THREADS + 128)   // + one MMA-issuing warp (tcgen05.mma issue blocks ~100 clk per instruction while the pipe is
                                       // busy); warps are allocated in fours, the other three exit at once
-#define GM_S 512                      // sample columns per row (two MMA blocks of 256)
+#ifndef GM_S
+#define GM_S 512                      // sample columns per row (MMA blocks of 256); 256 overflows the per-owner lists
+#endif
+#define GM_SHALVES (GM_S / GM_TN)
+#define GM_SROUND (32768 / GM_S)       // strip rows whose samples fit the 128 KB dump buffer at once
 #define GM_SPL (GM_S / 32)
 #define GM_SUBCAP 128                 // list capacity per (row, column group): private to the owning thread, no atomics
 #define GM_LCAP (4 * GM_SUBCAP)        // list slots per row
@@ -54,7 +58,7 @@
 #define GM_A_BYTES (6 * GM_APLANE + GM_ROWS * 16)       // 15 104
 #define GM_B_BYTES (6 * GM_BPLANE + GM_TN * 16)         // 29 440
 #define GM_SMP_CHUNKS 28
-#define GM_R1_BYTES (64 * GM_S * 4)                     // 131 072: sample operand / sample dump (64 rows) / 3 B buffers + edges + ambiguity list / scratch
+#define GM_R1_BYTES 131072                     // 131 072: sample operand / sample dump (64 rows) / 3 B buffers + edges + ambiguity list / scratch
 #define GM_EDGE_OFF (3 * GM_B_BYTES)                    // column band edges lo[4][256] (floats), slot = tile % 4
 #define GM_AMB_OFF 93184                                // ambiguity list (ints)
 #define GM_AMB_CAP ((GM_R1_BYTES - GM_AMB_OFF) / 4)
@@ -382,12 +386,12 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         gm_csync();
 
         if (!tiny) {
-            // ---- sample: gather 2 x 256 spread columns into an explicit K-major operand (hi parts only; the pivots only
+            // ---- sample: gather GM_S spread columns (blocks of 256) into an explicit K-major operand (hi parts only; the pivots only
             //      have to be roughly right, the count pass verifies the bracket), 14 MMAs per half into TMEM buffer 0 / 1
-            for (int half = 0; half < 2; ++half) {
+            for (int half = 0; half < GM_SHALVES; ++half) {
                 for (int e = tid; e < GM_SMP_CHUNKS * GM_TN; e += GM_THREADS) {
                     const int s = e & (GM_TN - 1), q = e >> 8;
-                    const int pos = (int)(((long long)(half * GM_TN + s) * NB) >> 9);            // / GM_S
+                    const int pos = (int)(((long long)(half * GM_TN + s) * NB) / GM_S);
                     float4 o;
                     if (q < 27) {
                         const int c3 = q < 24 ? (q >> 3) : q - 24, k = q < 24 ? (q & 7) : 8;
@@ -415,11 +419,11 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             //      memory (XOR swizzle of the low 5 column bits: the 32 rows of a warp hit 32 different banks), then
             //      warp per row: 16 samples per lane, 512-bin packed histogram of the sample (two 16-bit counters per
             //      word) -> pa / pb at bin edges
-            for (int round = 0; round < 2; ++round) {
-                if ((lq >> 1) == round) {
-                    float* smp = reinterpret_cast<float*>(R1) + (myrow & 63) * GM_S;
+            for (int round = 0; round < GM_ROWS / GM_SROUND; ++round) {
+                if (myrow / GM_SROUND == round) {
+                    float* smp = reinterpret_cast<float*>(R1) + (myrow % GM_SROUND) * GM_S;
 #pragma unroll
-                    for (int b = 0; b < 2; ++b)
+                    for (int b = 0; b < GM_SHALVES; ++b)
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
                             float v[32];
@@ -437,12 +441,12 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 const float sg = sqrtf(fmaxf(rs * (1.0f - frac), 1.0f));
                 const int r_lo = (int)floorf(rs - GM_NSIGMA * sg) - 1;       // sample ranks the bracket must enclose
                 const int r_hi = (int)ceilf(rs + GM_NSIGMA * sg) + 1;
-                for (int r = 64 * round + warp; r < min(tk.nrows, 64 * round + 64); r += GM_WARPS) {
+                for (int r = GM_SROUND * round + warp; r < min(tk.nrows, GM_SROUND * round + GM_SROUND); r += GM_WARPS) {
                     float sm[GM_SPL];
                     float smin = INFINITY, smax = -INFINITY;
 #pragma unroll
                     for (int q = 0; q < GM_SPL; ++q) {
-                        sm[q] = smp[(r & 63) * GM_S + q * 32 + lane];
+                        sm[q] = smp[(r % GM_SROUND) * GM_S + q * 32 + lane];
                         smin = fminf(smin, sm[q]); smax = fmaxf(smax, sm[q]);
                     }
                     for (int o = 16; o > 0; o >>= 1) {
