@@ -52,6 +52,7 @@ SYMBOLS = {
     "acoss_serra09_pairs_dev": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_vp, c_vp]),
     "acoss_get_pair_stats": (ctypes.c_int, [c_vp, ctypes.POINTER(PairStats)]),
     "acoss_debug_counters": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64)]),
+    "acoss_debug_counters_ext": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int32]),
     "acoss_crp_pair": (ctypes.c_int, [c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(CrpParams), c_u8p,
                                       c_i32p, c_i32p, c_f32p, c_f32p, c_i32p]),
     "acoss_cover_similarity_from_crp": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, ctypes.c_int32,
@@ -206,6 +207,11 @@ class Context(object):
     def debug_counters(self):
         out = (ctypes.c_uint64 * 16)()
         self._ck(self.lib.acoss_debug_counters(self.h, out))
+        return [int(x) for x in out]
+
+    def debug_counters_ext(self, n=48):
+        out = (ctypes.c_uint64 * n)()
+        self._ck(self.lib.acoss_debug_counters_ext(self.h, out, n))
         return [int(x) for x in out]
 
     def crp_pair(self, q, r, params=None):

@@ -67,7 +67,7 @@ struct acoss_ctx {
     DevBuf d_descs, d_tasks, d_thr, d_crp, d_scores, d_misc, d_misc2, d_counters, d_lists;
     cudaEvent_t ev[8] = {};
     acoss_pair_stats stats = {};
-    unsigned long long h_counters[16] = {};
+    unsigned long long h_counters[ACOSS_N_COUNTERS] = {};
     size_t crp_budget = (size_t)8 << 30;
     int max_smem = 0;
     int num_sms = ACOSS_NUM_SMS;

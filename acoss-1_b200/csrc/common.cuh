@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #define ACOSS_NBINS 12
+#define ACOSS_N_COUNTERS 48        // device profiling counters per context (debug ABI exposes them)
 #define ACOSS_NUM_SMS 148
 
 // One (query, reference) pair of a batch, filled by the host planner except `oti`.

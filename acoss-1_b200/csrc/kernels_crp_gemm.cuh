@@ -68,6 +68,7 @@
 // shared memory: A planes | R1 | per-warp scratch | per-row arrays (pa pb thA xx loq hiq: float; cnta lcnt flag: int) | 2 mbarriers | tmem holder
 #define GM_SMEM_BYTES (GM_A_BYTES + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4 + 12 * GM_ROWV_BYTES + GM_ARAW_BYTES + 128)
 #define GM_TMEM_COLS 512
+#define GM_POOL(r, slot) ((r) * 32 + (((slot) + (r)) & 31))   // candidate pool index: thread-per-row access is bank-conflict-free
 #define GM_BIG 1.0e30f                 // norm entry of padding columns: rho~ = huge, never below a pivot or an edge
 #define GM_PMAX 1.0e29f                // "unbounded" pivots
 #define GM_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((GM_TN >> 3) << 17) | ((GM_ROWS >> 4) << 24))
@@ -339,7 +340,9 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
 
         gm_csync();
         long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0;
-        if (tid == 0) { ph0 = clock64(); ph1 = ph0; ph2 = ph0; }
+        long long prb = 0;
+        if (tid == 0) { ph0 = clock64(); ph1 = ph0; ph2 = ph0; prb = ph0; }
+#define GM_PROBE(i) do { if (tid == 0) { const long long c_ = clock64(); atomicAdd(&counters[16 + (i)], (unsigned long long)(c_ - prb)); prb = c_; } } while (0)
         // ---- stage the A planes: entry e = frame row0 + e (e < 136), chunk c3: -2 * rotated bins, hi / lo; norms
         for (int e = tid; e < (GM_ROWS + 8) * 3; e += GM_THREADS) {
             const int fe = e / 3, c3 = e - 3 * fe;
@@ -384,28 +387,43 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         const float E = GM_EPS_REL * (xmax + ymax);       // one bound for the whole strip (conservative)
         const float plow = -(4.0f * (xmax + ymax) + 1.0e-30f);    // "unbounded below" pivot: under every rho~, small enough for rho~ - plow to be meaningful
         gm_csync();
+        GM_PROBE(0);
 
         if (!tiny) {
             // ---- sample: gather GM_S spread columns (blocks of 256) into an explicit K-major operand (hi parts only; the pivots only
             //      have to be roughly right, the count pass verifies the bracket), 14 MMAs per half into TMEM buffer 0 / 1
             for (int half = 0; half < GM_SHALVES; ++half) {
-                for (int e = tid; e < GM_SMP_CHUNKS * GM_TN; e += GM_THREADS) {
-                    const int s = e & (GM_TN - 1), q = e >> 8;
+                {
+                    // thread (s = tid % 256, parity = tid / 256) gathers chunks q = parity, parity + 2, ... of sample s: all
+                    // 14 loads are in flight at once (one L2 round trip per half instead of 14)
+                    static_assert(GM_THREADS == 2 * GM_TN && GM_SMP_CHUNKS == 28, "sample gather mapping");
+                    const int s = tid & (GM_TN - 1), qpar = tid >> 8;
                     const int pos = (int)(((long long)(half * GM_TN + s) * NB) / GM_S);
-                    float4 o;
-                    if (q < 27) {
-                        const int c3 = q < 24 ? (q >> 3) : q - 24, k = q < 24 ? (q & 7) : 8;
-                        const float4 x = __ldg(reinterpret_cast<const float4*>(fr_b + (int64_t)(pos + k) * ACOSS_NBINS + 4 * c3));
-                        o = make_float4(tf32_rna(x.x), tf32_rna(x.y), tf32_rna(x.z), tf32_rna(x.w));
-                    } else {
-                        o.x = 1.0f; o.y = 1.0f;
-                        tf32_split(__ldg(sdB + pos), o.z, o.w);
+                    const float4* fb = reinterpret_cast<const float4*>(fr_b + (int64_t)pos * ACOSS_NBINS);
+                    float4 x[14];
+#pragma unroll
+                    for (int it = 0; it < 14; ++it) {
+                        const int q = qpar + 2 * it;                  // warp-uniform
+                        if (q < 27) {
+                            const int c3 = q < 24 ? (q >> 3) : q - 24, k = q < 24 ? (q & 7) : 8;
+                            x[it] = __ldg(fb + 3 * k + c3);
+                        } else {
+                            x[it] = make_float4(1.0f, 1.0f, __ldg(sdB + pos), 0.0f);
+                        }
                     }
-                    *reinterpret_cast<float4*>(R1 + q * (GM_TN * 16) + s * 16) = o;
+#pragma unroll
+                    for (int it = 0; it < 14; ++it) {
+                        const int q = qpar + 2 * it;
+                        float4 o;
+                        if (q < 27) o = make_float4(tf32_rna(x[it].x), tf32_rna(x[it].y), tf32_rna(x[it].z), tf32_rna(x[it].w));
+                        else { o.x = 1.0f; o.y = 1.0f; tf32_split(x[it].z, o.z, o.w); }
+                        *reinterpret_cast<float4*>(R1 + q * (GM_TN * 16) + s * 16) = o;
+                    }
                 }
                 fence_proxy_async_smem();
                 tc_fence_before();
                 gm_csync();
+                GM_PROBE(1);
                 if (tid == 0) {
                     tc_fence_after();
                     gm_issue_sample(tmem_base + half * GM_TN, a_saddr, r1_saddr);
@@ -413,91 +431,112 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
                 mbar_wait(mb_smp, psmp); psmp ^= 1;     // the operand buffer is rebuilt for the second half
                 tc_fence_after();
+                GM_PROBE(2);
             }
             if (tid == 0) ph1 = clock64();
-            // ---- pivots, 64 strip rows per round: the owners dump their 128 sample values per row from TMEM to shared
-            //      memory (XOR swizzle of the low 5 column bits: the 32 rows of a warp hit 32 different banks), then
-            //      warp per row: 16 samples per lane, 512-bin packed histogram of the sample (two 16-bit counters per
-            //      word) -> pa / pb at bin edges
-            for (int round = 0; round < GM_ROWS / GM_SROUND; ++round) {
-                if (myrow / GM_SROUND == round) {
-                    float* smp = reinterpret_cast<float*>(R1) + (myrow % GM_SROUND) * GM_S;
+            // ---- pivots.  Per row the 256-bin histogram of its GM_S samples over [min, max] -> pa / pb at bin edges.  The four
+            //      owner threads of a row bin their own 128 samples straight out of TMEM into PRIVATE histograms with 8-bit
+            //      counters (64 words per thread, word w of lane l at hw[w * 32 + l]: bank = lane, conflict-free, no atomics --
+            //      shared-memory atomics were the whole cost of this phase); the scan adds the four owners' counters.
+            {
+                static_assert(GM_S == 512 && GM_THREADS == 512, "four owners x 128 samples per row");
+                unsigned* hall = reinterpret_cast<unsigned*>(R1);                       // [16 warps][64 words][32 lanes] = 128 KB
+                float* xf = reinterpret_cast<float*>(R1 + GM_R1_BYTES);                 // [2][GM_THREADS] exchange (the per-warp scratch is free here)
+                int* xc = reinterpret_cast<int*>(xf);
+                const int xi = myrow * 4;
 #pragma unroll
-                    for (int b = 0; b < GM_SHALVES; ++b)
+                for (int i = 0; i < 16; ++i) reinterpret_cast<uint4*>(hall + warp * 2048)[i * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
+                float smin = INFINITY, smax = -INFINITY;
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            float v[32];
-                            gm_tmem_ld32(my_taddr + 48 * cg + b * GM_TN + 32 * h, v);
+                for (int b = 0; b < GM_SHALVES; ++b)
 #pragma unroll
-                            for (int q = 0; q < 32; ++q) smp[b * GM_TN + 64 * cg + 32 * h + (q ^ lane)] = v[q];
-                        }
+                    for (int h = 0; h < 2; ++h) {
+                        float v[32];
+                        gm_tmem_ld32(my_taddr + 48 * cg + b * GM_TN + 32 * h, v);
+#pragma unroll
+                        for (int q = 0; q < 32; ++q) { smin = fminf(smin, v[q]); smax = fmaxf(smax, v[q]); }
+                    }
+                xf[xi + cg] = smin; xf[GM_THREADS + xi + cg] = smax;
+                gm_csync();
+                {
+                    const float4 a4 = *reinterpret_cast<const float4*>(xf + xi), b4 = *reinterpret_cast<const float4*>(xf + GM_THREADS + xi);
+                    smin = fminf(fminf(a4.x, a4.y), fminf(a4.z, a4.w));
+                    smax = fmaxf(fmaxf(b4.x, b4.y), fmaxf(b4.z, b4.w));
                 }
+                const float hscale = (smax > smin) ? 256.0f / (smax - smin) : 0.0f;
+                const float hwidth = (smax - smin) * (1.0f / 256.0f);
+                const float hoff = -smin * hscale;
+                unsigned char* hb = reinterpret_cast<unsigned char*>(hall + warp * 2048) + 4 * lane;     // bin b: byte b % 4 of word b / 4
+#pragma unroll
+                for (int b = 0; b < GM_SHALVES; ++b)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        float v[32];
+                        gm_tmem_ld32(my_taddr + 48 * cg + b * GM_TN + 32 * h, v);
+#pragma unroll
+                        for (int q = 0; q < 32; ++q) {
+                            // these phases are issue-bound (65 536 samples per strip): a byte-wide read-modify-write keeps
+                            // the instruction count per sample at its minimum
+                            const int bin = min(255, (int)fmaf(v[q], hscale, hoff));
+                            hb[(bin >> 2) * 128 + (bin & 3)] += 1;
+                        }
+                    }
                 tc_fence_before();
                 gm_csync();
-                const float* smp = reinterpret_cast<const float*>(R1);
-                unsigned* hist = wscr;
+                GM_PROBE(3);
                 const float frac = ((float)pr.lo + 0.5f) / (float)NB;
                 const float rs = frac * (float)GM_S;
                 const float sg = sqrtf(fmaxf(rs * (1.0f - frac), 1.0f));
                 const int r_lo = (int)floorf(rs - GM_NSIGMA * sg) - 1;       // sample ranks the bracket must enclose
                 const int r_hi = (int)ceilf(rs + GM_NSIGMA * sg) + 1;
-                for (int r = GM_SROUND * round + warp; r < min(tk.nrows, GM_SROUND * round + GM_SROUND); r += GM_WARPS) {
-                    float sm[GM_SPL];
-                    float smin = INFINITY, smax = -INFINITY;
+                // owner cg scans bins 64 cg .. 64 cg + 63 (words 16 cg .. 16 cg + 15 of the four owners' histograms)
+                unsigned lo[16], hi[16];
+                int tot = 0;
 #pragma unroll
-                    for (int q = 0; q < GM_SPL; ++q) {
-                        sm[q] = smp[(r % GM_SROUND) * GM_S + q * 32 + lane];
-                        smin = fminf(smin, sm[q]); smax = fmaxf(smax, sm[q]);
+                for (int k = 0; k < 16; ++k) {
+                    unsigned l = 0, h = 0;
+#pragma unroll
+                    for (int o = 0; o < 4; ++o) {
+                        const unsigned x = hall[(4 * o + lq) * 2048 + (16 * cg + k) * 32 + lane];
+                        l += x & 0x00ff00ffu; h += (x >> 8) & 0x00ff00ffu;
                     }
-                    for (int o = 16; o > 0; o >>= 1) {
-                        smin = fminf(smin, __shfl_xor_sync(0xffffffffu, smin, o));
-                        smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, o));
-                    }
-                    const float hscale = (smax > smin) ? 512.0f / (smax - smin) : 0.0f;
-                    const float hwidth = (smax - smin) * (1.0f / 512.0f);
+                    lo[k] = l; hi[k] = h;
+                    tot += (int)((l & 0xffffu) + (l >> 16) + (h & 0xffffu) + (h >> 16));
+                }
+                xc[xi + cg] = tot;           // the min / max exchange was read before the barrier above
+                gm_csync();
+                int ba = -1, bb = 256;
+                {
+                    const int4 c = *reinterpret_cast<const int4*>(xc + xi);
+                    const int cc[4] = {c.x, c.y, c.z, c.w};
+                    int run = 0;
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) hist[q * 32 + lane] = 0u;
-                    __syncwarp();
-#pragma unroll
-                    for (int q = 0; q < GM_SPL; ++q) {
-                        const int bin = min(511, (int)((sm[q] - smin) * hscale));
-                        atomicAdd(&hist[bin >> 1], 1u << (16 * (bin & 1)));
-                    }
-                    __syncwarp();
-                    int hc[16], hpre;                        // lane owns bins 16 lane .. 16 lane + 15
-                    {
-                        const uint4 h0 = *reinterpret_cast<const uint4*>(hist + 8 * lane);
-                        const uint4 h1 = *reinterpret_cast<const uint4*>(hist + 8 * lane + 4);
-                        const unsigned hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-                        int tot = 0;
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) { hc[2 * q] = hw[q] & 0xffffu; hc[2 * q + 1] = hw[q] >> 16; tot += hc[2 * q] + hc[2 * q + 1]; }
-                        int incl = tot;
-#pragma unroll
-                        for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
-                        hpre = incl - tot;                   // samples in bins < 16 lane
-                    }
+                    for (int g = 0; g < 4; ++g) if (g < cg) run += cc[g];
                     // pa = lower edge of the last bin b with #(samples in bins < b) <= r_lo;
                     // pb = upper edge of the first bin b with #(samples in bins <= b) > r_hi
-                    int ba = -1, bb = 512;
-                    {
-                        int run = hpre;
 #pragma unroll
-                        for (int q = 0; q < 16; ++q) {
-                            if (run <= r_lo) ba = 16 * lane + q;
-                            run += hc[q];
-                            if (run > r_hi && bb == 512) bb = 16 * lane + q;
+                    for (int k = 0; k < 16; ++k)
+#pragma unroll
+                        for (int f = 0; f < 4; ++f) {
+                            const int bin = 64 * cg + 4 * k + f;
+                            const int cnt = (int)(f == 0 ? (lo[k] & 0xffffu) : f == 1 ? (hi[k] & 0xffffu) : f == 2 ? (lo[k] >> 16) : (hi[k] >> 16));
+                            if (run <= r_lo) ba = bin;
+                            run += cnt;
+                            if (run > r_hi && bb == 256) bb = bin;
                         }
-                        ba = __reduce_max_sync(0xffffffffu, ba);
-                        bb = __reduce_min_sync(0xffffffffu, bb);
-                    }
-                    if (lane == 0) {
-                        s_pa[r] = (r_lo >= 0 && ba > 0) ? fmaxf(smin + (float)ba * hwidth, plow) : plow;
-                        s_pb[r] = (r_hi < GM_S && bb < 511) ? fminf(smin + (float)(bb + 1) * hwidth, GM_PMAX) : GM_PMAX;
-                    }
-                    __syncwarp();
+                }
+                gm_csync();                  // xc is rewritten
+                xc[xi + cg] = ba; xc[GM_THREADS + xi + cg] = bb;
+                gm_csync();
+                if (cg == 0) {
+                    const int4 a4 = *reinterpret_cast<const int4*>(xc + xi), b4 = *reinterpret_cast<const int4*>(xc + GM_THREADS + xi);
+                    ba = max(max(a4.x, a4.y), max(a4.z, a4.w));
+                    bb = min(min(b4.x, b4.y), min(b4.z, b4.w));
+                    s_pa[myrow] = (r_lo >= 0 && ba > 0) ? fmaxf(smin + (float)ba * hwidth, plow) : plow;
+                    s_pb[myrow] = (r_hi < GM_S && bb < 255) ? fminf(smin + (float)(bb + 1) * hwidth, GM_PMAX) : GM_PMAX;
                 }
                 gm_csync();
+                GM_PROBE(4);
             }
         }
         if (tid == 0) ph2 = clock64();
@@ -604,6 +643,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             gm_csync();
         }
         if (tid == 0) ph3 = clock64();
+        GM_PROBE(5);
 
         // ---- select.  (A) warp per row: value bisection on the row's list, candidates (everything within 2E of the
         //      wanted order statistics) go to a pool in shared memory;  (B) thread per candidate: the exact 108-term
@@ -615,11 +655,14 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             // (A) four owner threads per row, each on its own sub-list (the elements it listed in the count pass; slots are
             //     row-adjacent in memory, so a warp reads them coalesced).  One binning pass refines the bracket: 128
             //     equal-width buckets over the list's value range (the list is close to uniform inside the narrow bracket, so
-            //     a bucket holds about two elements), per-row histograms in shared memory, a scan finds the bucket(s) of the
-            //     wanted ranks; a second pass collects the candidates: everything within 2E of those buckets.
+            //     a bucket holds about two elements) into PRIVATE histograms with 8-bit counters (a sub-list holds at most 128
+            //     elements; word w of lane l of warp W at ph[(W * 32 + w) * 32 + l]: bank = lane, conflict-free, no atomics); a
+            //     scan over the four owners' counters finds the bucket(s) of the wanted ranks; a second pass over the values
+            //     (still in registers) collects the candidates: everything within 2E of those buckets.
             int* xc = reinterpret_cast<int*>(R1 + GM_R1_BYTES);           // [2][GM_THREADS] exchange buffers (the per-warp scratch is free here)
             float* xf = reinterpret_cast<float*>(xc);
-            unsigned* hist = reinterpret_cast<unsigned*>(R1);             // [GM_ROWS][64]: 128 packed 16-bit counters per row
+            unsigned* hall = reinterpret_cast<unsigned*>(R1);             // [16 warps][32 words][32 lanes] = 64 KB
+            unsigned char* pbyte = reinterpret_cast<unsigned char*>(hall + warp * 1024) + 4 * lane;      // bucket b: byte b % 4 of this thread's word b / 4
             const int xi = myrow * 4;
             int4 c4 = make_int4(0, 0, 0, 0);
             if (rowvalid) c4 = *reinterpret_cast<const int4*>(s_lcnt + 4 * myrow);
@@ -630,21 +673,13 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             const float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;
             const int n = ok ? ln : 0;
             const float pa = s_pa[myrow], pb = s_pb[myrow];
-            for (int e = tid; e < GM_ROWS * 64; e += GM_THREADS) hist[e] = 0u;
-            // the sub-list goes to registers (64 values, all loads in flight at once) and shared memory (the next 48);
-            // the rare rest is re-read from L2
-            float* tailv = reinterpret_cast<float*>(R1 + 32768);          // [48][GM_THREADS]: sub-list entries 64 .. 111
-            float lv[64];
 #pragma unroll
-            for (int q = 0; q < 64; ++q) lv[q] = (q < n) ? ml[q * GM_ROWS].x : INFINITY;
-            const int nmax_w = __reduce_max_sync(0xffffffffu, n);
-            for (int q0 = 64; q0 < min(nmax_w, 112); q0 += 16) {
-                float t[16];
-#pragma unroll
-                for (int q = 0; q < 16; ++q) t[q] = (q0 + q < n) ? ml[(q0 + q) * GM_ROWS].x : INFINITY;
-#pragma unroll
-                for (int q = 0; q < 16; ++q) tailv[(q0 + q - 64) * GM_THREADS + tid] = t[q];
-            }
+            for (int i = 0; i < 8; ++i) reinterpret_cast<uint4*>(hall + warp * 1024)[i * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
+            __syncwarp();
+            // The sub-list is streamed from L2 twice, in chunks of 16 loads in flight (binning pass, then candidate pass):
+            // holding it in "registers" put all 64 values of every thread in local memory (128 KB per CTA, more than the
+            // L1 left beside 200 KB of shared memory), which is where the time of this phase went.
+            float2* cstage = reinterpret_cast<float2*>(R1 + 65536);       // [8][GM_THREADS] (value, column) of a thread's first candidates
             // value range of the list: the pivots, unless a pivot is the "unbounded" sentinel
             float vmin = pa, vmax = pb;
             {
@@ -661,39 +696,37 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     vmax = vmax + fabsf(vmax) * 1.0e-6f + 1.0e-30f;          // strictly above every element
                 }
             }
+            GM_PROBE(6);
             // binning pass (monotone map value -> bucket)
             const float bw = (vmax - vmin) * (1.0f / 128.0f);
             const float bscale = (bw > 0.0f) ? 1.0f / bw : 0.0f;
-            {
-                unsigned* hrow = hist + myrow * 64;
+            for (int q0 = 0; q0 < n; q0 += 32) {
+                // unconditional loads (index clamped to the last element) so that all 32 are in flight at once; the
+                // increment carries the predicate
+                float t[32];
 #pragma unroll
-                for (int q = 0; q < 64; ++q)
-                    if (q < n) {
-                        const int b = min(127, max(0, (int)((lv[q] - vmin) * bscale)));
-                        atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
-                    }
-                for (int q = 64; q < min(n, 112); ++q) {
-                    const int b = min(127, max(0, (int)((tailv[(q - 64) * GM_THREADS + tid] - vmin) * bscale)));
-                    atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
-                }
-                for (int q = 112; q < n; ++q) {
-                    const int b = min(127, max(0, (int)((ml[q * GM_ROWS].x - vmin) * bscale)));
-                    atomicAdd(&hrow[b >> 1], 1u << (16 * (b & 1)));
+                for (int q = 0; q < 32; ++q) t[q] = ml[min(q0 + q, n - 1) * GM_ROWS].x;
+#pragma unroll
+                for (int q = 0; q < 32; ++q) {
+                    const int b = min(127, max(0, (int)((t[q] - vmin) * bscale)));
+                    pbyte[(b >> 2) * 128 + (b & 3)] += (unsigned char)(q0 + q < n);
                 }
             }
             gm_csync();
+            GM_PROBE(7);
             // scan: owner cg takes buckets 32 cg .. 32 cg + 31; bucket b_lo holds rank kk, b_hi rank kk + (pr.hi - pr.lo)
             const int kk = pr.lo - c_a, kk2 = kk + (pr.hi - pr.lo);
             int hc[32], mysum = 0;
-            {
-                const uint4* hp = reinterpret_cast<const uint4*>(hist + myrow * 64 + 16 * cg);
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    const uint4 h = hp[g];
-                    const unsigned hw[4] = {h.x, h.y, h.z, h.w};
+            for (int k = 0; k < 8; ++k) {
+                unsigned l = 0, h = 0;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) { hc[8 * g + 2 * k] = hw[k] & 0xffffu; hc[8 * g + 2 * k + 1] = hw[k] >> 16; mysum += hc[8 * g + 2 * k] + hc[8 * g + 2 * k + 1]; }
+                for (int o = 0; o < 4; ++o) {
+                    const unsigned x = hall[((4 * o + lq) * 32 + 8 * cg + k) * 32 + lane];
+                    l += x & 0x00ff00ffu; h += (x >> 8) & 0x00ff00ffu;
                 }
+                hc[4 * k] = (int)(l & 0xffffu); hc[4 * k + 1] = (int)(h & 0xffffu); hc[4 * k + 2] = (int)(l >> 16); hc[4 * k + 3] = (int)(h >> 16);
+                mysum += hc[4 * k] + hc[4 * k + 1] + hc[4 * k + 2] + hc[4 * k + 3];
             }
             xc[xi + cg] = mysum;
             gm_csync();
@@ -715,6 +748,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             gm_csync();                 // xc is rewritten
             xc[xi + cg] = b_lo; xc[GM_THREADS + xi + cg] = b_hi;
             gm_csync();
+            GM_PROBE(8);
             float c_min = 0.0f, c_max = 0.0f;
             if (ok) {
                 const int4 a = *reinterpret_cast<const int4*>(xc + xi), b = *reinterpret_cast<const int4*>(xc + GM_THREADS + xi);
@@ -727,15 +761,24 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 const bool inside = b_lo >= 0 && b_hi >= 0 && (c_min > pa || pa == plow) && (c_max < pb || pb == GM_PMAX);
                 if (!inside) { ok = false;  }
             }
-            // candidates = list elements in [c_min, c_max]; every exact order statistic is among them
+            // candidates = list elements in [c_min, c_max]; every exact order statistic is among them.  Second pass over the
+            // sub-list: count the elements below the window, stage the first eight candidates of this thread in shared memory
             {
                 int nb_l = 0, nc_l = 0;
-                if (ok) {
+                if (ok)
+                    for (int q0 = 0; q0 < n; q0 += 16) {
+                        float2 t[16];
 #pragma unroll
-                    for (int q = 0; q < 64; ++q) { nb_l += (lv[q] < c_min); nc_l += (lv[q] >= c_min && lv[q] <= c_max); }
-                    for (int q = 64; q < min(n, 112); ++q) { const float x = tailv[(q - 64) * GM_THREADS + tid]; nb_l += (x < c_min); nc_l += (x >= c_min && x <= c_max); }
-                    for (int q = 112; q < n; ++q) { const float x = ml[q * GM_ROWS].x; nb_l += (x < c_min); nc_l += (x >= c_min && x <= c_max); }
-                }
+                        for (int q = 0; q < 16; ++q) t[q] = ml[min(q0 + q, n - 1) * GM_ROWS];
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) {           // branch-free: predicated store into the staging slot
+                            const bool live = q0 + q < n;
+                            const bool cand = live && t[q].x >= c_min && t[q].x <= c_max;
+                            nb_l += (live && t[q].x < c_min);
+                            if (cand) cstage[min(nc_l, 7) * GM_THREADS + tid] = t[q];
+                            nc_l += cand;
+                        }
+                    }
                 gm_csync();             // xc is rewritten
                 xc[xi + cg] = nb_l | (nc_l << 16);
                 gm_csync();
@@ -749,15 +792,15 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     if (kx < 0 || kx + (pr.hi - pr.lo) >= n_c) { ok = false;  }
                     else if (n_c > 32) { if (cg == 0) { s_nc[myrow] = 0; s_flag[myrow] = 2; } }      // non-uniform list: bisection below
                     else {
-                        if (nc_l) {
-#pragma unroll
-                            for (int q = 0; q < 64; ++q)
-                                if (lv[q] >= c_min && lv[q] <= c_max) {
-                                    pool_col[myrow * 32 + slot] = __float_as_int(ml[q * GM_ROWS].y); pool_dex[myrow * 32 + slot] = lv[q]; ++slot;
-                                }
-                            for (int q = 64; q < n; ++q) {
+                        if (nc_l <= 8) {
+                            for (int k = 0; k < nc_l; ++k) {
+                                const float2 ent = cstage[k * GM_THREADS + tid];
+                                pool_col[GM_POOL(myrow, slot)] = __float_as_int(ent.y); pool_dex[GM_POOL(myrow, slot)] = ent.x; ++slot;
+                            }
+                        } else {
+                            for (int q = 0; q < n; ++q) {         // rare: more candidates than staging slots, read the sub-list again
                                 const float2 ent = ml[q * GM_ROWS];
-                                if (ent.x >= c_min && ent.x <= c_max) { pool_col[myrow * 32 + slot] = __float_as_int(ent.y); pool_dex[myrow * 32 + slot] = ent.x; ++slot; }
+                                if (ent.x >= c_min && ent.x <= c_max) { pool_col[GM_POOL(myrow, slot)] = __float_as_int(ent.y); pool_dex[GM_POOL(myrow, slot)] = ent.x; ++slot; }
                             }
                         }
                         if (cg == 0) { s_nc[myrow] = n_c; s_kx[myrow] = kx; }
@@ -766,6 +809,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 if (rowvalid && !ok && cg == 0) { s_nc[myrow] = 0; s_flag[myrow] = 1; atomicAdd(&counters[1], 1ull); }
             }
             gm_csync();
+            GM_PROBE(9);
             // (A') rows whose bucket window held too many elements (the list is far from uniform): warp per row, value
             //      bisection on the whole list until the window holds at most three elements
             for (int r = warp; r < tk.nrows; r += GM_WARPS) {
@@ -824,8 +868,8 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                         if (cand) {
                             const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
                             if (slot < 32) {
-                                pool_col[r * 32 + slot] = __float_as_int(lst[((q >> 2) * GM_SUBCAP + (q & 3) * 32 + lane) * GM_ROWS].y);
-                                pool_dex[r * 32 + slot] = l2[q];
+                                pool_col[GM_POOL(r, slot)] = __float_as_int(lst[((q >> 2) * GM_SUBCAP + (q & 3) * 32 + lane) * GM_ROWS].y);
+                                pool_dex[GM_POOL(r, slot)] = l2[q];
                             }
                         }
                         n_c += __popc(mc);
@@ -839,6 +883,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 }
             }
             gm_csync();
+            GM_PROBE(10);
             // offsets of the rows' candidates in the flat task list
             if (warp == 0) {
                 int c[4], tot = 0;
@@ -853,6 +898,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 if (lane == 31) s_off[GM_ROWS] = run;
             }
             gm_csync();
+            GM_PROBE(11);
             {
                 const int boff = side_a_is_query ? (ACOSS_NBINS - rot) % ACOSS_NBINS : 0;     // rot_src(c, rot) = (c + boff) % 12
                 const int n_tasks_c = s_off[GM_ROWS];
@@ -861,7 +907,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
 #pragma unroll
                     for (int st = 64; st > 0; st >>= 1) if (s_off[r + st] <= idx) r += st;
                     const int slot = idx - s_off[r];
-                    const int jj = pool_col[r * 32 + slot];
+                    const int jj = pool_col[GM_POOL(r, slot)];
                     const float4* bp = reinterpret_cast<const float4*>(fr_b + (int64_t)jj * ACOSS_NBINS);
                     const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
                     float acc = 0.0f;
@@ -878,33 +924,44 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     const float sa = s_xx[r], sb = __ldg(sdB + jj);
                     const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
                     float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
-                    max_err = fmaxf(max_err, fabsf(item - pool_dex[r * 32 + slot]) / (sa + sb));
+                    max_err = fmaxf(max_err, fabsf(item - pool_dex[GM_POOL(r, slot)]) / (sa + sb));
                     if (item < 0.0f) item = 0.0f;
-                    pool_dex[r * 32 + slot] = __fsqrt_rn(item);
+                    pool_dex[GM_POOL(r, slot)] = __fsqrt_rn(item);
                     ++n_exact;
                 }
             }
             gm_csync();
-            for (int r = warp; r < tk.nrows; r += GM_WARPS) {
-                const int n_c = s_nc[r], kx = s_kx[r];
-                if (n_c == 0) continue;
-                const float dex = (lane < n_c) ? pool_dex[r * 32 + lane] : INFINITY;
-                // rank by comparison through shuffles (ties by lane), pick ranks kx and kx + 1
-                int rank = 0;
-                for (int b = 0; b < n_c; ++b) {
-                    const float db = __shfl_sync(0xffffffffu, dex, b);
-                    rank += (db < dex) || (db == dex && b < lane);
+            GM_PROBE(12);
+            // (C) four threads per row: ranks kx and kx + 1 among the row's exact candidate distances (ties by slot); the row's
+            //     distances sit in registers, thread cg ranks candidates cg, cg + 4, ...
+            {
+                float* xlo = reinterpret_cast<float*>(R1 + GM_R1_BYTES);          // [GM_ROWS] (the exchange buffers are free here)
+                float* xhi = xlo + GM_THREADS;
+                const int n_c = rowvalid ? s_nc[myrow] : 0, kx = s_kx[myrow];
+                if (n_c > 0) {
+                    float d[32];
+#pragma unroll
+                    for (int b_ = 0; b_ < 32; ++b_) d[b_] = (b_ < n_c) ? pool_dex[GM_POOL(myrow, b_)] : INFINITY;
+                    for (int a_ = cg; a_ < n_c; a_ += 4) {
+                        const float da = pool_dex[GM_POOL(myrow, a_)];
+                        int rank = 0;
+#pragma unroll
+                        for (int b_ = 0; b_ < 32; ++b_) rank += (d[b_] < da) || (d[b_] == da && b_ < a_);
+                        if (rank == kx) { xlo[myrow] = da; if (kx + 1 >= n_c) xhi[myrow] = da; }
+                        if (rank == kx + 1) xhi[myrow] = da;
+                    }
                 }
-                const unsigned m0 = __ballot_sync(0xffffffffu, lane < n_c && rank == kx);
-                const unsigned m1 = __ballot_sync(0xffffffffu, lane < n_c && rank == kx + 1);
-                const float v_lo = __shfl_sync(0xffffffffu, dex, __ffs(m0) - 1);
-                const float v_hi = m1 ? __shfl_sync(0xffffffffu, dex, __ffs(m1) - 1) : v_lo;
-                if (lane == 0) { const float t = percentile_combine(pr, v_lo, v_hi); s_th[r] = t; thr_out[tk.row0 + r] = t; }
+                gm_csync();
+                if (cg == 0 && n_c > 0) {
+                    const float t = percentile_combine(pr, xlo[myrow], xhi[myrow]);
+                    s_th[myrow] = t; thr_out[tk.row0 + myrow] = t;
+                }
             }
         } else if (tid < GM_ROWS) {
             s_flag[tid] = 1;
         }
         gm_csync();
+        GM_PROBE(13);
         // ---- rows that could not be bracketed (and tiny pairs): the whole row exactly, one row at a time
         const int any_flag = gm_csync_or(tid < tk.nrows && s_flag[tid]);
         for (int r = 0; any_flag && r < tk.nrows; ++r) {
@@ -924,6 +981,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             }
             gm_csync();
         }
+        GM_PROBE(14);
         if (tid == 0) {
             ph4 = clock64();
             atomicAdd(&counters[2], (unsigned long long)(ph1 - ph0));
@@ -995,6 +1053,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             }
         }
         gm_csync();
+        GM_PROBE(15);
         {
             const int na = *amb_cnt;
             if (na > GM_AMB_CAP) {
@@ -1034,6 +1093,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             }
         }
         gm_csync();
+        GM_PROBE(16);
         if (tid == 0) atomicAdd(&counters[6], (unsigned long long)(clock64() - ph4));
     }
     for (int o = 16; o > 0; o >>= 1) {

@@ -134,6 +134,9 @@ int acoss_get_pair_stats(acoss_ctx *ctx, acoss_pair_stats *out);
 /* Profiling aid: raw device counters of the last pair call (clock64 cycles per phase of the
  * CRP strip kernel summed over CTAs; layout documented in kernels_crp_band.cuh). */
 int acoss_debug_counters(acoss_ctx *ctx, uint64_t *out16);
+/* Same, the first n of the extended set (slots 16.. hold the sub-phase cycle probes of
+ * crp_strip_gemm_kernel; layout in kernels_crp_gemm.cuh). */
+int acoss_debug_counters_ext(acoss_ctx *ctx, uint64_t *out, int32_t n);
 
 /* Test hook: the binary cross-recurrence plot of ONE pair, (M, N) uint8 0/1,
  * rows = query frames (ChromaCrossSimilarity output, rqa_serra09.py:66).

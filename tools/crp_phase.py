@@ -22,3 +22,7 @@ tasks = max(1, c[7]); tiles = (L - 8 + 255) // 256
 print("dbg=%s L=%d crp %.1f ms; per strip kclk: sample %.1f pivots %.1f count %.1f (%.2f/tile) select %.1f binarise(pass2 strips) %.1f (%.2f/tile); fallback %d ovf %d miss %d" % (
     os.environ.get("ACOSS_GEMM_DBG"), L, st["ms_crp"], c[2] / tasks / 1e3, c[3] / tasks / 1e3, c[4] / tasks / 1e3, c[4] / tasks / 1e3 / tiles,
     c[5] / tasks / 1e3, c[6] / (tasks / 2) / 1e3, c[6] / (tasks / 2) / 1e3 / tiles, c[1], c[15], c[13]))
+x = ctx.debug_counters_ext(48)[16:]
+names = ["stageA+ymax", "smp gather", "smp mma wait", "piv dump", "piv hist", "count pass", "sel list load", "sel binning", "sel scan",
+         "sel collect", "sel bisect rows", "sel offsets", "sel exact chains", "sel rank", "fallback rows", "bin stream", "bin exact"]
+print("sub-phases (kclk per strip): " + "; ".join("%s %.1f" % (nm, v / tasks / 1e3) for nm, v in zip(names, x)))
