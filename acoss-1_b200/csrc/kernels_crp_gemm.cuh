@@ -245,7 +245,6 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
     extern __shared__ __align__(128) unsigned char gsm[];
     unsigned char* Apl = gsm;
     unsigned char* R1 = gsm + GM_A_BYTES;
-    unsigned* wscr = reinterpret_cast<unsigned*>(R1 + GM_R1_BYTES) + (threadIdx.x >> 5) * GM_WSCR_WORDS;
     float* rowv = reinterpret_cast<float*>(R1 + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4);
     float* s_pa = rowv;
     float* s_pb = rowv + GM_ROWS;

@@ -58,6 +58,19 @@ def peaks():
     return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback (B200_PROFILING.md)")
 
 
+def measured_traffic():
+    """DRAM bytes per algorithmic unit from the committed `ncu --set full` capture of this round
+    (profiles/traffic.json, written by tools/ncu_traffic.py from dram__bytes_read.sum +
+    dram__bytes_write.sum of one launch); scaled below to the units one bench launch processes."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p))
+        except Exception:
+            return None
+    return None
+
+
 def make_workload(args):
     """Downsampled chroma of every track (what Serra09.load_features returns) + labels."""
     from acoss_b200 import synth
@@ -304,15 +317,21 @@ def run_ours(args, rank, world, local_rank):
     gcups = st["dp_cells"] / (ms_dp * 1e-3) / 1e9
     crp_flop = 2.0 * 108 * st["crp_cells"] + 5.0 * st["crp_cells"]
     crp_tflops = crp_flop / (ms_crp * 1e-3) / 1e12
+    tr = measured_traffic() or {}
+    n_crp_launch = max(1, 2 * st["n_batches"])
+    dp_traffic = tr["dp_dram_bytes_per_crp_byte"] * st["crp_bytes"] / n_dp_launch if "dp_dram_bytes_per_crp_byte" in tr else None
+    crp_traffic = tr["crp_dram_bytes_per_cell"] * st["crp_cells"] / n_crp_launch if "crp_dram_bytes_per_cell" in tr else None
     kernels = [
         {"kernel": "dp_rowpar_kernel (Qmax)", "bound": "hbm", "achieved": dp_gbs, "peak": pk["hbm"], "unit": "GB/s",
-         "frac": dp_gbs / pk["hbm"], "traffic": None, "ms_per_step": ms_dp, "launches_per_step": n_dp_launch,
+         "frac": dp_gbs / pk["hbm"], "traffic": dp_traffic, "ms_per_step": ms_dp, "launches_per_step": n_dp_launch,
          "gcups": gcups, "share_of_step": ms_dp / ms_tot},
         {"kernel": "crp_strip_gemm_kernel x2 (cross-similarity + thresholds + binarise)" if args.crp_mode in (0, 4)
                    else "crp_strip kernels (cross-similarity + thresholds + binarise)",
          "bound": "tensor", "achieved": crp_tflops,
-         "peak": pk["bf16_sus"], "unit": "TFLOP/s", "frac": crp_tflops / pk["bf16_sus"], "traffic": None,
-         "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
+         "peak": pk["bf16_sus"], "unit": "TFLOP/s", "frac": crp_tflops / pk["bf16_sus"], "traffic": crp_traffic,
+         "traffic_note": "DRAM bytes per launch (2 launches per batch): ncu dram bytes per CRP cell (profiles/traffic.json) x cells per launch; "
+                         "the CRP itself is 1 B per cell and pass, the rest is list spill written back from L2",
+         "launches_per_step": n_crp_launch, "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
          "note": "algorithmic flop = (2*108+5)*M*N per pair (SURVEY 8(d)), peak = measured dense bf16. The kernel runs the "
                  "contraction 2.5 times (column thresholds, row thresholds, binarise) as 3-product TF32 splits on tcgen05 "
                  "(41 MMAs of 128x256x8 per tile = 664 executed flop per cell and pass, dense TF32 peak is half the bf16 "
@@ -322,6 +341,7 @@ def run_ours(args, rank, world, local_rank):
     roofline = {k: dominant[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}
     roofline["kernel"] = dominant["kernel"]
     roofline["peak_source"] = pk["src"]
+    roofline["traffic_source"] = tr.get("source")
 
     if rank != 0:
         return

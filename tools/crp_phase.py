@@ -26,3 +26,4 @@ x = ctx.debug_counters_ext(48)[16:]
 names = ["stageA+ymax", "smp gather", "smp mma wait", "piv dump", "piv hist", "count pass", "sel list load", "sel binning", "sel scan",
          "sel collect", "sel bisect rows", "sel offsets", "sel exact chains", "sel rank", "fallback rows", "bin stream", "bin exact"]
 print("sub-phases (kclk per strip): " + "; ".join("%s %.1f" % (nm, v / tasks / 1e3) for nm, v in zip(names, x)))
+print("stats: crp_cells %d crp_bytes %d dp_cells %d ms_dp %.3f n_exact %d" % (st["crp_cells"], st["crp_bytes"], st["dp_cells"], st["ms_dp"], st["n_exact_cells"]))
