@@ -53,6 +53,8 @@ struct acoss_ctx {
     std::vector<int32_t> h_emb;       // embedded rows per track
     std::vector<int64_t> h_sd_off;    // self-dot table offsets
     DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma, d_fnorm;
+    DevBuf d_smpop;                   // per-track sample operands of the tensor-core CRP kernel (m = 9, tau = 1 only)
+    bool have_smpop = false;
     // SiMPle feature store (frame-major float64) + per-track chroma profiles
     int sp_tracks = 0;
     std::vector<int64_t> sp_offs;
@@ -119,7 +121,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
-                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
+                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
                       &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
@@ -218,6 +220,16 @@ extern "C" int acoss_upload_tracks(acoss_ctx* ctx, const float* frames_host, con
                                              ctx->d_emb.as<int32_t>(), ctx->d_sd_off.as<int64_t>(), m, tau,
                                              ctx->d_selfdot.as<float>());
         CK_LAUNCH();
+    }
+    // sample operands of the tensor-core CRP kernel: 225 KB per track, built only when they fit a 6 GiB budget (the kernel
+    // gathers the samples itself otherwise)
+    ctx->have_smpop = false;
+    if (m == 9 && tau == 1 && max_emb > 0 && (size_t)n_tracks * GM_SMP_OP_BYTES <= ((size_t)6 << 30)) {
+        RESERVE(ctx->d_smpop, (size_t)n_tracks * GM_SMP_OP_BYTES);
+        gm_sample_operand_kernel<<<n_tracks, 256, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(), ctx->d_emb.as<int32_t>(),
+                                                           ctx->d_sd_off.as<int64_t>(), ctx->d_selfdot.as<float>(), ctx->d_smpop.as<unsigned char>());
+        CK_LAUNCH();
+        ctx->have_smpop = true;
     }
     CK(cudaStreamSynchronize(st));   // host buffers may be released by the caller
     return ACOSS_OK;

@@ -58,6 +58,8 @@
 #define GM_A_BYTES (6 * GM_APLANE + GM_ROWS * 16)       // 15 104
 #define GM_B_BYTES (6 * GM_BPLANE + GM_TN * 16)         // 29 440
 #define GM_SMP_CHUNKS 28
+#define GM_SMP_PSTRIDE (GM_TN * 16 + 16)   // plane stride of the gathered sample operand: skewed by one 16-byte entry, so that a warp
+                                           // writing the 28 chunk planes of ONE sample spreads over all bank groups
 #define GM_R1_BYTES 131072                     // 131 072: sample operand / sample dump (64 rows) / 3 B buffers + edges + ambiguity list / scratch
 #define GM_EDGE_OFF (3 * GM_B_BYTES)                    // column band edges lo[4][256] (floats), slot = tile % 4
 #define GM_AMB_OFF 93184                                // ambiguity list (ints)
@@ -66,6 +68,8 @@
 #define GM_ROWV_BYTES (GM_ROWS * 4)
 #define GM_ARAW_BYTES ((GM_ROWS + 8) * ACOSS_NBINS * 4)  // strip frames in the oracle's bin order, for the exact chains
 // shared memory: A planes | R1 | per-warp scratch | per-row arrays (pa pb thA xx loq hiq: float; cnta lcnt flag: int) | 2 mbarriers | tmem holder
+#define GM_SMP_HALF_BYTES (GM_SMP_CHUNKS * GM_SMP_PSTRIDE)          // 115 136: one half (256 samples) of a track's sample operand
+#define GM_SMP_OP_BYTES (GM_SHALVES * GM_SMP_HALF_BYTES)           // per track, precomputed at upload (gm_sample_operand_kernel)
 #define GM_SMEM_BYTES (GM_A_BYTES + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4 + 12 * GM_ROWV_BYTES + GM_ARAW_BYTES + 128)
 #define GM_TMEM_COLS 512
 #define GM_POOL(r, slot) ((r) * 32 + (((slot) + (r)) & 31))   // candidate pool index: thread-per-row access is bank-conflict-free
@@ -195,12 +199,12 @@ __device__ __forceinline__ void gm_issue_sample(uint32_t d_tmem, uint32_t a0, ui
     for (int c3 = 0; c3 < 3; ++c3) {
 #pragma unroll
         for (int kp = 0; kp < 4; ++kp) {
-            gm_mma(d_tmem, GM_DLO(al, c3 * GM_APLANE + 32 * kp, 16), GM_DLO(sl, (8 * c3 + 2 * kp) * (GM_TN * 16), GM_TN * 16), acc);
+            gm_mma(d_tmem, GM_DLO(al, c3 * GM_APLANE + 32 * kp, 16), GM_DLO(sl, (8 * c3 + 2 * kp) * GM_SMP_PSTRIDE, GM_SMP_PSTRIDE), acc);
             acc = 1;
         }
     }
-    gm_mma(d_tmem, GM_DLO(al, 128, GM_APLANE), GM_DLO(sl, 24 * (GM_TN * 16), GM_TN * 16), 1);
-    gm_mma(d_tmem, GM_DLO(al, 2 * GM_APLANE + 128, 4 * GM_APLANE - 128), GM_DLO(sl, 26 * (GM_TN * 16), GM_TN * 16), 1);
+    gm_mma(d_tmem, GM_DLO(al, 128, GM_APLANE), GM_DLO(sl, 24 * GM_SMP_PSTRIDE, GM_SMP_PSTRIDE), 1);
+    gm_mma(d_tmem, GM_DLO(al, 2 * GM_APLANE + 128, 4 * GM_APLANE - 128), GM_DLO(sl, 26 * GM_SMP_PSTRIDE, GM_SMP_PSTRIDE), 1);
 }
 
 // One frame (12 terms) of the oracle's sequential chain: acc += a[c] * b[(c + OFF) % 12], c ascending, no FMA.
@@ -229,6 +233,44 @@ __device__ __forceinline__ float gm_chain12_rot(float acc, const float (&a)[12],
     }
 }
 
+// ---- per-track sample operand, built once at upload ---------------------------------------------------------------
+// The sample columns of a strip depend on side B only (positions spread over its NB embedded rows), so the gathered,
+// TF32-rounded K-major operand of every track is precomputed in its final shared-memory layout and a strip fetches it
+// with one bulk copy per half (TMA engine, no LSU requests: the per-SM LSU path from L2 sustains only ~15 B/clk here).
+// Norm entries use the unrotated self-dot table: the sample only steers the pivots, which the count pass verifies.
+__global__ void gm_sample_operand_kernel(const float* __restrict__ frames, const int64_t* __restrict__ offs,
+                                         const int32_t* __restrict__ emb_len, const int64_t* __restrict__ sd_off,
+                                         const float* __restrict__ selfdot, unsigned char* __restrict__ out)
+{
+    const int track = blockIdx.x;
+    const int NB = emb_len[track];
+    if (NB <= 0) return;
+    const float* fr = frames + offs[track] * ACOSS_NBINS;
+    const float* sd = selfdot + sd_off[track];
+    unsigned char* o = out + (size_t)track * GM_SMP_OP_BYTES;
+    for (int e = threadIdx.x; e < GM_S * GM_SMP_CHUNKS; e += blockDim.x) {
+        const int idx = e / GM_SMP_CHUNKS, q = e - idx * GM_SMP_CHUNKS;      // sample, chunk plane
+        const int half = idx / GM_TN, s = idx - half * GM_TN;
+        const int pos = (int)(((long long)idx * NB) / GM_S);
+        float4 v;
+        if (q < 27) {
+            const int c3 = q < 24 ? (q >> 3) : q - 24, k = q < 24 ? (q & 7) : 8;
+            const float4 x = *reinterpret_cast<const float4*>(fr + (int64_t)(pos + k) * ACOSS_NBINS + 4 * c3);
+            v = make_float4(tf32_rna(x.x), tf32_rna(x.y), tf32_rna(x.z), tf32_rna(x.w));
+        } else {
+            v.x = 1.0f; v.y = 1.0f;
+            tf32_split(sd[pos], v.z, v.w);
+        }
+        *reinterpret_cast<float4*>(o + (size_t)half * GM_SMP_HALF_BYTES + q * GM_SMP_PSTRIDE + s * 16) = v;
+    }
+}
+__device__ __forceinline__ void gm_bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // counters: [0] exact cells  [1] fallback rows  [2..6] cycles (thread 0): stage+sample, pivots, count pass, select, binarise
 //           [7] tasks  [11] too many candidates  [12] window not inside the list  [13] bracket miss  [15] list overflow
 //           [14] max observed |rho~ - rho_oracle| / (xx + yy) (float bits)
@@ -240,6 +282,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                       float* __restrict__ thr, uint8_t* __restrict__ crp,
                       int side_a_is_query, float qf,
                       float2* __restrict__ lists,            // [gridDim.x][4][GM_SUBCAP][GM_ROWS] (rho~, column) of the listed elements
+                      const unsigned char* __restrict__ smpop, // per-track sample operands (gm_sample_operand_kernel) or null: gather in the kernel
                       unsigned long long* __restrict__ counters, int dbg)
 {
     extern __shared__ __align__(128) unsigned char gsm[];
@@ -261,20 +304,20 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
     // mbarriers: full[2] (MMAs of a tile done, by tcgen05.commit), empty[2] (a TMEM buffer has been read; one arrival per
     // warp), built[3] (a side-B operand buffer has been written; one arrival per warp), smp (sample MMAs done)
     uint64_t* mbar = reinterpret_cast<uint64_t*>(Araw + (GM_ROWS + 8) * ACOSS_NBINS);
-    uint64_t* mb_full = mbar, *mb_empty = mbar + 2, *mb_built = mbar + 4, *mb_smp = mbar + 7;
-    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 8);
+    uint64_t* mb_full = mbar, *mb_empty = mbar + 2, *mb_built = mbar + 4, *mb_smp = mbar + 7, *mb_ld = mbar + 8;
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 9);
     float* s_red = reinterpret_cast<float*>(tmem_holder + 2);            // 8 words: ambiguity counter, strip error bound for the producer
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lq = warp & 3, cg = warp >> 2;          // TMEM lane quarter (strip rows 32 lq ..), column group (64 cg ..)
     const int myrow = 32 * lq + lane;
     unsigned long long n_exact = 0;
-    uint32_t pf0 = 0, pf1 = 0, psmp = 0;              // mbarrier phase parities: full (every thread), sample
+    uint32_t pf0 = 0, pf1 = 0, psmp = 0, pld = 0;     // mbarrier phase parities: full (every thread), sample, sample-operand bulk load
     float max_err = 0.0f;
 
     if (warp == 0) gm_tmem_alloc(tmem_holder);
     if (tid == 0) {
         mbar_init(mb_full, 1); mbar_init(mb_full + 1, 1); mbar_init(mb_empty, GM_WARPS); mbar_init(mb_empty + 1, GM_WARPS);
-        mbar_init(mb_built, GM_WARPS); mbar_init(mb_built + 1, GM_WARPS); mbar_init(mb_built + 2, GM_WARPS); mbar_init(mb_smp, 1);
+        mbar_init(mb_built, GM_WARPS); mbar_init(mb_built + 1, GM_WARPS); mbar_init(mb_built + 2, GM_WARPS); mbar_init(mb_smp, 1); mbar_init(mb_ld, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     tc_fence_before();
@@ -391,32 +434,45 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         if (!tiny) {
             // ---- sample: gather GM_S spread columns (blocks of 256) into an explicit K-major operand (hi parts only; the pivots only
             //      have to be roughly right, the count pass verifies the bracket), 14 MMAs per half into TMEM buffer 0 / 1
+            const unsigned char* smp_src = smpop ? smpop + (size_t)(side_a_is_query ? pd.r : pd.q) * GM_SMP_OP_BYTES : nullptr;
             for (int half = 0; half < GM_SHALVES; ++half) {
-                {
-                    // thread (s = tid % 256, parity = tid / 256) gathers chunks q = parity, parity + 2, ... of sample s: all
-                    // 14 loads are in flight at once (one L2 round trip per half instead of 14)
+                if (smp_src) {
+                    // precomputed operand of the side-B track: one bulk copy (R1 is free: the barrier above / the wait on the
+                    // previous half's MMAs), completion on an mbarrier
+                    if (tid == 0) gm_bulk_load(R1, smp_src + (size_t)half * GM_SMP_HALF_BYTES, GM_SMP_HALF_BYTES, mb_ld);
+                    mbar_wait(mb_ld, pld); pld ^= 1;
+                } else {
+                    // A warp gathers 16 samples of the half, one sample per load instruction: lanes 0 .. 26 read the 27
+                    // consecutive 16-byte chunks of frames pos .. pos + 8 (432 contiguous bytes = 4 or 5 L1 tag lookups; one
+                    // chunk per thread at scattered addresses cost 27, and the L1 tag stage was the bound of this phase), lane
+                    // 27 the norm.  Memory chunk m = 3 k + c3 goes to operand plane q = 8 c3 + k (k < 8) or 24 + c3 (k = 8).
                     static_assert(GM_THREADS == 2 * GM_TN && GM_SMP_CHUNKS == 28, "sample gather mapping");
-                    const int s = tid & (GM_TN - 1), qpar = tid >> 8;
-                    const int pos = (int)(((long long)(half * GM_TN + s) * NB) / GM_S);
-                    const float4* fb = reinterpret_cast<const float4*>(fr_b + (int64_t)pos * ACOSS_NBINS);
-                    float4 x[14];
+                    static_assert(GM_SMP_CHUNKS * GM_SMP_PSTRIDE <= GM_R1_BYTES, "sample operand");
+                    const int mk = lane / 3, mc3 = lane - 3 * mk;
+                    const int q = lane < 24 ? 8 * mc3 + mk : lane;          // lanes 24 .. 26: k = 8, q = 24 + c3 = lane; lane 27: norms
 #pragma unroll
-                    for (int it = 0; it < 14; ++it) {
-                        const int q = qpar + 2 * it;                  // warp-uniform
-                        if (q < 27) {
-                            const int c3 = q < 24 ? (q >> 3) : q - 24, k = q < 24 ? (q & 7) : 8;
-                            x[it] = __ldg(fb + 3 * k + c3);
-                        } else {
-                            x[it] = make_float4(1.0f, 1.0f, __ldg(sdB + pos), 0.0f);
+                    for (int i0 = 0; i0 < 16; i0 += 8) {
+                        // every lane issues the same unconditional loads (lanes 27 .. 31 re-read chunk 26, the norm is a
+                        // broadcast load), so that all 16 are in flight at once; the lane's role is resolved by selects
+                        float4 x[8];
+                        float nrm[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int s = 16 * warp + i0 + i;
+                            const int pos = (int)(((long long)(half * GM_TN + s) * NB) / GM_S);
+                            x[i] = __ldg(reinterpret_cast<const float4*>(fr_b + (int64_t)pos * ACOSS_NBINS) + min(lane, 26));
+                            nrm[i] = __ldg(sdB + pos);
                         }
-                    }
 #pragma unroll
-                    for (int it = 0; it < 14; ++it) {
-                        const int q = qpar + 2 * it;
-                        float4 o;
-                        if (q < 27) o = make_float4(tf32_rna(x[it].x), tf32_rna(x[it].y), tf32_rna(x[it].z), tf32_rna(x[it].w));
-                        else { o.x = 1.0f; o.y = 1.0f; tf32_split(x[it].z, o.z, o.w); }
-                        *reinterpret_cast<float4*>(R1 + q * (GM_TN * 16) + s * 16) = o;
+                        for (int i = 0; i < 8; ++i) {
+                            const int s = 16 * warp + i0 + i;
+                            float nh, nl;
+                            tf32_split(nrm[i], nh, nl);
+                            const bool isn = lane >= 27;
+                            const float4 o = make_float4(isn ? 1.0f : tf32_rna(x[i].x), isn ? 1.0f : tf32_rna(x[i].y),
+                                                         isn ? nh : tf32_rna(x[i].z), isn ? nl : tf32_rna(x[i].w));
+                            if (lane < 28) *reinterpret_cast<float4*>(R1 + q * GM_SMP_PSTRIDE + s * 16) = o;
+                        }
                     }
                 }
                 fence_proxy_async_smem();
