@@ -853,9 +853,17 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                                 pool_col[GM_POOL(myrow, slot)] = __float_as_int(ent.y); pool_dex[GM_POOL(myrow, slot)] = ent.x; ++slot;
                             }
                         } else {
-                            for (int q = 0; q < n; ++q) {         // rare: more candidates than staging slots, read the sub-list again
-                                const float2 ent = ml[q * GM_ROWS];
-                                if (ent.x >= c_min && ent.x <= c_max) { pool_col[GM_POOL(myrow, slot)] = __float_as_int(ent.y); pool_dex[GM_POOL(myrow, slot)] = ent.x; ++slot; }
+                            // more candidates than staging slots (plateaus of near-equal distances put them in one owner's
+                            // sub-list): read the sub-list again, 16 loads in flight
+                            for (int q0 = 0; q0 < n; q0 += 16) {
+                                float2 t[16];
+#pragma unroll
+                                for (int q = 0; q < 16; ++q) t[q] = ml[min(q0 + q, n - 1) * GM_ROWS];
+#pragma unroll
+                                for (int q = 0; q < 16; ++q)
+                                    if (q0 + q < n && t[q].x >= c_min && t[q].x <= c_max) {
+                                        pool_col[GM_POOL(myrow, slot)] = __float_as_int(t[q].y); pool_dex[GM_POOL(myrow, slot)] = t[q].x; ++slot;
+                                    }
                             }
                         }
                         if (cg == 0) { s_nc[myrow] = n_c; s_kx[myrow] = kx; }
