@@ -72,6 +72,9 @@
 #define GM_SMP_OP_BYTES (GM_SHALVES * GM_SMP_HALF_BYTES)           // per track, precomputed at upload (gm_sample_operand_kernel)
 #define GM_SMEM_BYTES (GM_A_BYTES + GM_R1_BYTES + GM_WARPS * GM_WSCR_WORDS * 4 + 12 * GM_ROWV_BYTES + GM_ARAW_BYTES + 128)
 #define GM_TMEM_COLS 512
+// list entry (value, column) of slot s of a sub-list, relative to the owner's base (region + 2 * row): slots are stored in pairs,
+// [slot / 2][row][slot % 2], so that a thread reads two consecutive slots with one 16-byte load and a warp 512 contiguous bytes
+#define GM_LIDX(s) ((((s) >> 1) * (2 * GM_ROWS)) + ((s) & 1))
 #define GM_POOL(r, slot) ((r) * 32 + (((slot) + (r)) & 31))   // candidate pool index: thread-per-row access is bank-conflict-free
 #define GM_BIG 1.0e30f                 // norm entry of padding columns: rho~ = huge, never below a pivot or an edge
 #define GM_PMAX 1.0e29f                // "unbounded" pivots
@@ -674,7 +677,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
         if (!tiny) {
             // ---- count pass: c_a = #(rho~ < pa); elements of [pa, pb) go to the row's list
             const float pa = s_pa[myrow], pb = s_pb[myrow];
-            float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;        // slot s at ml[s * GM_ROWS]: private to this thread, no atomics;
+            float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + 2 * myrow;    // slot s at ml[GM_LIDX(s)]: private to this thread, no atomics;
                                                                               // rows are adjacent, so reading a slot is coalesced across a warp
             // d = rho~ - pa: "below" is the sign bit of d, "inside [pa, pb)" is one unsigned compare of d's bit pattern against
             // that of pb - pa (a negative d has the top bit set).  Elements within a rounding error of pb may be left out;
@@ -687,7 +690,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     const uint32_t u = __float_as_uint(v[q] - pa);
                     ca += u >> 31;
                     if (u < wbits) {
-                        if (!(dbg & 8)) ml[min(ln, GM_SUBCAP - 1) * GM_ROWS] = make_float2(v[q], __int_as_float(jbase + q));     // overflow is detected from ln
+                        if (!(dbg & 8)) ml[GM_LIDX(min(ln, GM_SUBCAP - 1))] = make_float2(v[q], __int_as_float(jbase + q));     // overflow is detected from ln
                         ++ln;
                     }
                 }
@@ -725,7 +728,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
             const bool ovf = max(max(c4.x, c4.y), max(c4.z, c4.w)) > GM_SUBCAP;
             bool ok = rowvalid && (c_a <= pr.lo) && (c_a + c_ab >= pr.hi + 1) && !ovf;
             if (rowvalid && !ok && cg == 0 && ovf) atomicAdd(&counters[15], 1ull);
-            const float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + myrow;
+            const float2* ml = my_lists + cg * GM_SUBCAP * GM_ROWS + 2 * myrow;
             const int n = ok ? ln : 0;
             const float pa = s_pa[myrow], pb = s_pb[myrow];
 #pragma unroll
@@ -741,7 +744,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 float lmin = INFINITY, lmax = -INFINITY;
                 const bool need = ok && (pa == plow || pb == GM_PMAX);
                 if (need)
-                    for (int q = 0; q < n; ++q) { const float x = ml[q * GM_ROWS].x; lmin = fminf(lmin, x); lmax = fmaxf(lmax, x); }
+                    for (int q = 0; q < n; ++q) { const float x = ml[GM_LIDX(q)].x; lmin = fminf(lmin, x); lmax = fmaxf(lmax, x); }
                 xf[xi + cg] = lmin; xf[GM_THREADS + xi + cg] = lmax;
                 gm_csync();
                 if (need) {
@@ -760,7 +763,10 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 // increment carries the predicate
                 float t[32];
 #pragma unroll
-                for (int q = 0; q < 32; ++q) t[q] = ml[min(q0 + q, n - 1) * GM_ROWS].x;
+                for (int q = 0; q < 32; q += 2) {
+                    const float4 e2 = *reinterpret_cast<const float4*>(ml + GM_LIDX(min(q0 + q, (n - 1) & ~1)));
+                    t[q] = e2.x; t[q + 1] = e2.z;
+                }
 #pragma unroll
                 for (int q = 0; q < 32; ++q) {
                     const int b = min(127, max(0, (int)((t[q] - vmin) * bscale)));
@@ -824,7 +830,10 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                     for (int q0 = 0; q0 < n; q0 += 16) {
                         float2 t[16];
 #pragma unroll
-                        for (int q = 0; q < 16; ++q) t[q] = ml[min(q0 + q, n - 1) * GM_ROWS];
+                        for (int q = 0; q < 16; q += 2) {
+                            const float4 e2 = *reinterpret_cast<const float4*>(ml + GM_LIDX(min(q0 + q, (n - 1) & ~1)));
+                            t[q] = make_float2(e2.x, e2.y); t[q + 1] = make_float2(e2.z, e2.w);
+                        }
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {           // branch-free: predicated store into the staging slot
                             const bool live = q0 + q < n;
@@ -858,7 +867,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                             for (int q0 = 0; q0 < n; q0 += 16) {
                                 float2 t[16];
 #pragma unroll
-                                for (int q = 0; q < 16; ++q) t[q] = ml[min(q0 + q, n - 1) * GM_ROWS];
+                                for (int q = 0; q < 16; ++q) t[q] = ml[GM_LIDX(min(q0 + q, n - 1))];
 #pragma unroll
                                 for (int q = 0; q < 16; ++q)
                                     if (q0 + q < n && t[q].x >= c_min && t[q].x <= c_max) {
@@ -881,14 +890,14 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                 const int cseg[4] = {c4r.x, c4r.y, c4r.z, c4r.w};
                 const int c_ar = s_cnta[r], c_abr = c4r.x + c4r.y + c4r.z + c4r.w;
                 const float par = s_pa[r], pbr = s_pb[r];
-                const float2* lst = my_lists + r;
+                const float2* lst = my_lists + 2 * r;
                 float l2[GM_LPL];
                 float vmn = INFINITY, vmx = -INFINITY;
 #pragma unroll
                 for (int q = 0; q < GM_LPL; ++q) {              // slot (q % 4) * 32 + lane of segment q / 4
                     const int sl = (q & 3) * 32 + lane;
                     l2[q] = INFINITY;
-                    if (sl < cseg[q >> 2]) { l2[q] = lst[((q >> 2) * GM_SUBCAP + sl) * GM_ROWS].x; vmn = fminf(vmn, l2[q]); vmx = fmaxf(vmx, l2[q]); }
+                    if (sl < cseg[q >> 2]) { l2[q] = lst[(q >> 2) * GM_SUBCAP * GM_ROWS + GM_LIDX(sl)].x; vmn = fminf(vmn, l2[q]); vmx = fmaxf(vmx, l2[q]); }
                 }
                 for (int o = 16; o > 0; o >>= 1) {
                     vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
@@ -931,7 +940,7 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                         if (cand) {
                             const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
                             if (slot < 32) {
-                                pool_col[GM_POOL(r, slot)] = __float_as_int(lst[((q >> 2) * GM_SUBCAP + (q & 3) * 32 + lane) * GM_ROWS].y);
+                                pool_col[GM_POOL(r, slot)] = __float_as_int(lst[(q >> 2) * GM_SUBCAP * GM_ROWS + GM_LIDX((q & 3) * 32 + lane)].y);
                                 pool_dex[GM_POOL(r, slot)] = l2[q];
                             }
                         }
