@@ -66,6 +66,8 @@ SYMBOLS = {
     "acoss_snf": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                  ctypes.c_double, c_f64p, c_vp]),
     "acoss_simple_upload": (ctypes.c_int, [c_vp, c_f64p, c_i64p, ctypes.c_int32]),
+    "acoss_simple_preprocess": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                               ctypes.POINTER(ctypes.c_double), ctypes.c_int32, ctypes.POINTER(ctypes.c_double), c_i64p]),
     "acoss_simple_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_int32, c_f64p]),
     "acoss_ftm2d_allpairs": (ctypes.c_int, [c_vp, c_f64p, ctypes.c_int32, ctypes.c_int32, c_f64p]),
     "acoss_earlyfusion_upload": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32,
@@ -282,6 +284,23 @@ class Context(object):
         return ([Ws[k] for k in range(nm)] if want_Ws else None), fused
 
     # ---- SiMPle / FTM2D ---------------------------------------------------------------
+    def simple_preprocess(self, raw, win=200, skip=100, win_len_smooth=4):
+        """Simple.load_features + Simple.smooth for a list of raw (T_t, 12) float32 chroma arrays, on the device
+        (simple_silva.py:34-43, 56-66).  Returns a list of (12, int(T_t / skip)) float64 arrays."""
+        raw = [_np(r, np.float32).reshape(-1, 12) for r in raw]
+        offs = np.zeros(len(raw) + 1, np.int64)
+        offs[1:] = np.cumsum([r.shape[0] for r in raw])
+        flat = _np(np.concatenate(raw, 0) if raw else np.zeros((0, 12)), np.float32)
+        k = np.arange(win_len_smooth + 2)
+        taps = 0.5 - 0.5 * np.cos(2.0 * np.pi * k / (win_len_smooth + 1))          # symmetric Hann (fftbins=False)
+        taps = _np(taps / np.sum(taps), np.float64)
+        cols = np.array([r.shape[0] // skip for r in raw], np.int64)
+        out = np.zeros(12 * max(int(cols.sum()), 1), np.float64)
+        co = np.zeros(len(raw) + 1, np.int64)
+        self._ck(self.lib.acoss_simple_preprocess(self.h, _ptr(flat, ctypes.c_float), _ptr(offs, ctypes.c_int64), len(raw), int(win), int(skip),
+                                                  _ptr(taps, ctypes.c_double), len(taps), _ptr(out, ctypes.c_double), _ptr(co, ctypes.c_int64)))
+        return [out[12 * co[t]:12 * co[t + 1]].reshape(12, -1).copy() for t in range(len(raw))]
+
     def simple_upload(self, feats):
         """feats: list of (12, L_t) float64 arrays (Simple.load_features output)."""
         feats = [_np(f, np.float64) for f in feats]

@@ -207,3 +207,50 @@ ftm2d_allpairs_kernel(const double* __restrict__ S, int n, int d, double* __rest
             if (i < n && j < n) D[(int64_t)i * n + j] = exp(-acc[a][b]);
         }
 }
+
+// ---- SiMPle per-track preprocessing (Simple.load_features + Simple.smooth, acoss/algorithms/simple_silva.py:34-43, 56-66) ----
+// Block per track.  (1) column k of the reduced feature = mean over raw frames k SKIP .. k SKIP + WIN - 1 (clipped at the end
+// of the track) of every chroma bin: numpy reduces the transposed float32 view sequentially over time in float32 and divides
+// in float32 (checked against numpy in tests/); (2) 'same'-aligned convolution with the normalised Hann window (float64, taps
+// computed on the host); (3) every column divided by its L2 norm over the 12 bins (summed bin-ascending), norms below the
+// smallest normal double left alone.  `stage` holds the (12, L) float64 output of step (1).
+__global__ void simple_preprocess_kernel(const float* __restrict__ raw, const int64_t* __restrict__ raw_offs,
+                                         const int64_t* __restrict__ col_offs, int win, int skip,
+                                         const double* __restrict__ taps, int n_taps,
+                                         double* __restrict__ stage, double* __restrict__ out)
+{
+    const int t = blockIdx.x;
+    const int64_t T = raw_offs[t + 1] - raw_offs[t];
+    const int L = (int)(col_offs[t + 1] - col_offs[t]);
+    const float* x = raw + raw_offs[t] * ACOSS_NBINS;
+    double* st = stage + col_offs[t] * ACOSS_NBINS;
+    double* o = out + col_offs[t] * ACOSS_NBINS;
+    for (int e = threadIdx.x; e < L * ACOSS_NBINS; e += blockDim.x) {
+        const int k = e / ACOSS_NBINS, c = e - k * ACOSS_NBINS;        // consecutive threads: consecutive bins of one frame
+        const int64_t j0 = (int64_t)k * skip;
+        const int cnt = (int)min((int64_t)win, T - j0);
+        float acc = 0.0f;
+        for (int j = 0; j < cnt; ++j) acc = __fadd_rn(acc, x[(j0 + j) * ACOSS_NBINS + c]);
+        st[(int64_t)c * L + k] = (double)__fdiv_rn(acc, (float)cnt);
+    }
+    __syncthreads();
+    const int start = (n_taps - 1) / 2;
+    for (int e = threadIdx.x; e < L * ACOSS_NBINS; e += blockDim.x) {
+        const int c = e / L, i = e - c * L;
+        const int nfull = i + start;                                   // index into the 'full' convolution
+        double acc = 0.0;
+        for (int k = 0; k < n_taps; ++k) {
+            const int j = nfull - k;
+            if (j >= 0 && j < L) acc = __dadd_rn(acc, __dmul_rn(st[(int64_t)c * L + j], taps[k]));
+        }
+        o[(int64_t)c * L + i] = acc;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < L; i += blockDim.x) {
+        double ss = 0.0;
+        for (int c = 0; c < ACOSS_NBINS; ++c) { const double v = fabs(o[(int64_t)c * L + i]); ss = __dadd_rn(ss, __dmul_rn(v, v)); }
+        double len = sqrt(ss);
+        if (len < 2.2250738585072014e-308) len = 1.0;
+        for (int c = 0; c < ACOSS_NBINS; ++c) o[(int64_t)c * L + i] = o[(int64_t)c * L + i] / len;
+    }
+}

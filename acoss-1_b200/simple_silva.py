@@ -6,7 +6,8 @@ Profile for Music Analysis and Exploration. IEEE Transactions on Multimedia.
 Host-side mirror of the reference's `Simple` (acoss/algorithms/simple_silva.py:26-126): same
 constructor keywords, `load_features`, `oti`, `smooth`, `similarity(idxs)`.  The per-pair OTI +
 matrix-profile join + median (:45-54, :68-118) run on the GPU (acoss_simple_pairs), all ordered
-pairs of a `similarity` call in one batch.  Features are cached (the reference re-reads both
+pairs of a `similarity` call in one batch; so does the per-track preprocessing of `load_features` /
+`smooth` (:34-43, :56-66) when the tracks are loaded in bulk (`preload`, acoss_simple_preprocess).  Features are cached (the reference re-reads both
 files for every pair; results are unaffected).
 """
 import numpy as np
@@ -77,10 +78,18 @@ class Simple(CoverAlgorithm):
         return np.roll(seq_b, sorted_index[-1], axis=0), sorted_index
 
     def preload(self):
+        """All tracks at once: WIN/SKIP means, Hann smoothing and column normalisation run on the device
+        (acoss_simple_preprocess) for every track `load_features` has not produced yet, then the features are
+        uploaded for the pair kernel."""
         if self._uploaded:
             return
-        feats = [self.load_features(i) for i in range(self.N)]
-        self.context().simple_upload(feats)
+        missing = [i for i in range(self.N) if i not in self.all_feats]
+        if missing:
+            raw = [np.asarray(CoverAlgorithm.load_features(self, i)[self.chroma_type], np.float32) for i in missing]
+            feats = self.context().simple_preprocess(raw, win=self.WIN, skip=self.SKIP)
+            for i, f in zip(missing, feats):
+                self.all_feats[i] = f
+        self.context().simple_upload([self.all_feats[i] for i in range(self.N)])
         self._uploaded = True
 
     def pair_cost(self, idxs):

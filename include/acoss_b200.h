@@ -220,6 +220,16 @@ int acoss_snf(acoss_ctx *ctx, const void *mats_host, int32_t dtype, int32_t n_ma
 int acoss_simple_upload(acoss_ctx *ctx, const double *feats_host, const int64_t *col_offsets_host,
                         int32_t n_tracks);
 
+/* Per-track SiMPle preprocessing on the device (replaces the Python loops of
+ * Simple.load_features and Simple.smooth, acoss/algorithms/simple_silva.py:34-43, 56-66): raw (T_t, 12)
+ * float32 chroma -> (12, int(T_t / SKIP)) float64: mean over WIN-frame windows every SKIP frames, 'same'
+ * convolution with the taps (the normalised Hann window of length win_len_smooth + 2, computed by the
+ * caller), columns L2-normalised.  out_col_offsets_host[n_tracks + 1] receives the column offsets;
+ * out_feats_host must hold 12 * sum_t int(T_t / SKIP) doubles (track t at 12 * offset, row-major (12, L_t)). */
+int acoss_simple_preprocess(acoss_ctx *ctx, const float *raw_frames_host, const int64_t *raw_offsets_host,
+                            int32_t n_tracks, int32_t win, int32_t skip, const double *taps_host,
+                            int32_t n_taps, double *out_feats_host, int64_t *out_col_offsets_host);
+
 /* For every ORDERED pair (i, j): Sj = Simple.oti(Si, Sj)[0]; out = -Simple.simple_sim(Si, Sj)
  * (simple_silva.py:45-54, 68-118, 120-126); sslen = SSLEN (default 10).  float64 scores. */
 int acoss_simple_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pairs, int32_t sslen,

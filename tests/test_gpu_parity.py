@@ -470,6 +470,36 @@ def test_simple_pairs_vs_reference_golden(ctx, golden):
     np.testing.assert_allclose(D, g["simple_D"], rtol=1e-6, atol=1e-9)
 
 
+def test_simple_preprocess_vs_reference_golden(ctx, golden):
+    """Device WIN/SKIP mean + Hann smoothing + column normalisation vs the reference's Simple.load_features run
+    verbatim (simple_silva.py:34-43, 56-66; golden made by oracle/make_golden.py).  float64: tolerance 1e-12 (the
+    summation order inside numpy.convolve is not specified); plus ragged / short inputs against the host mirror."""
+    from oracle.make_golden import simple_ftm_dataset
+    import acoss_b200
+    g = golden("simple_ftm2d_reference.npz")
+    ds, _ = simple_ftm_dataset()
+    got = ctx.simple_preprocess(ds["hpcp"])
+    assert len(got) == 10
+    for i, f in enumerate(got):
+        ref = g["simple_feat%d" % i]
+        assert f.shape == ref.shape
+        np.testing.assert_allclose(f, ref, rtol=1e-12, atol=1e-15)
+    # ragged: T not a multiple of SKIP, last window clipped, a track shorter than SKIP (no columns), other WIN / SKIP
+    rng = np.random.default_rng(5)
+    raw = [rng.random((n, 12)).astype(np.float32) for n in (1234, 99, 100, 777, 2001)]
+    mirror = acoss_b200.Simple.__new__(acoss_b200.Simple)
+    for win, skip in ((200, 100), (64, 50), (30, 70)):
+        got = ctx.simple_preprocess(raw, win=win, skip=skip)
+        for r, f in zip(raw, got):
+            fo = r.T
+            nf = np.zeros((12, int(fo.shape[1] / skip)))
+            for k in range(nf.shape[1]):
+                nf[:, k] = np.mean(fo[:, k * skip:k * skip + win], axis=1)
+            assert f.shape == nf.shape
+            if nf.shape[1]:
+                np.testing.assert_allclose(f, mirror.smooth(nf), rtol=1e-12, atol=1e-15)
+
+
 def test_simple_generic_sslen_and_errors(ctx):
     import acoss_b200
     rng = np.random.default_rng(5)
