@@ -8,8 +8,11 @@ same constructor keywords, `load_features`, `similarity(idxs)`, `normalize_by_le
 The per-pair essentia calls (ChromaCrossSimilarity + CoverSongSimilarity, :60-67) are
 replaced by one batched GPU call through the C-ABI (acoss_serra09_pairs).
 """
+import os
+
 import numpy as np
 
+from . import featio
 from .algorithm_template import CoverAlgorithm, _torch
 
 __all__ = ['Serra09']
@@ -44,10 +47,37 @@ class ChromaPairAlgorithm(CoverAlgorithm):
             self.all_feats[i] = self._downsample([chroma])[0]
         return self.all_feats[i]
 
-    def preload(self):
-        """Load + downsample every track in one device batch and upload the track store."""
+    def packed_store_path(self):
+        """`<cacheprefix>_<chroma_type>.acosspk`: the packed feature store of this dataset (featio.save_packed)."""
+        return "%s_%s.acosspk" % (self.get_cacheprefix(), self.chroma_type)
+
+    def build_packed_store(self, path=None):
+        """Write every track's raw chroma (and clique labels) into one memory-mappable file; later runs load the
+        whole dataset with one mmap instead of one per-track file each."""
+        path = path or self.packed_store_path()
+        feats = [CoverAlgorithm.load_features(self, i) for i in range(self.N)]
+        featio.save_packed(path, [f[self.chroma_type] for f in feats], [f['label'] for f in feats])
+        return path
+
+    def _load_packed(self, path):
+        frames, offs, labels = featio.load_packed(path)
+        if len(labels) != self.N or frames.shape[1] != 12:
+            raise IOError("%s does not match this dataset (%d tracks)" % (path, self.N))
+        for i, l in enumerate(labels):
+            self.cliques.setdefault(l, set([])).add(i)
+        return [frames[offs[i]:offs[i + 1]] for i in range(self.N)]
+
+    def preload(self, packed_store=None):
+        """Load + downsample every track in one device batch and upload the track store.  `packed_store`: path of
+        a featio packed store (default: `packed_store_path()` when that file exists)."""
         if self._uploaded:
             return
+        if packed_store is None and os.path.exists(self.packed_store_path()):
+            packed_store = self.packed_store_path()
+        if packed_store is not None and len(self.all_feats) < self.N:
+            raw = self._load_packed(packed_store)
+            for i, x in enumerate(self._downsample(raw)):
+                self.all_feats.setdefault(i, x)
         missing = [i for i in range(self.N) if i not in self.all_feats]
         if missing:
             raw = [CoverAlgorithm.load_features(self, i)[self.chroma_type] for i in missing]

@@ -2,6 +2,8 @@
 same seeded inputs, against the committed golden fixtures, and -- at large sizes -- through
 size-independent properties.  Bar: bit-exact for the CRP / thresholds / integer scores and ranks;
 normalised float32 matrices bit-equal (same float64 arithmetic); eval tuples identical."""
+import os
+
 import numpy as np
 import pytest
 
@@ -452,6 +454,33 @@ def _simple_ftm_dataset(workdir):
     ds, extra = simple_ftm_dataset()
     fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"), extra=extra)
     return str(workdir / "ds.csv"), fdir
+
+
+def test_serra09_class_from_packed_store_identical(workdir):
+    """Serra09 through the packed feature store (one mmap for the whole dataset, featio.save_packed) gives the same
+    matrix, bit for bit, as through the per-track files, including the clique bookkeeping and the eval tuple."""
+    import acoss_b200
+    from acoss_b200 import synth
+    ds = synth.make_named("covers80", "S", seed=11, scale=0.1)
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"))
+    a = acoss_b200.Serra09(str(workdir / "ds.csv"), fdir, shortname="pk_a", downsample_fac=ds["fac"])
+    a.all_pairwise(1, symmetric=True)
+    a.normalize_by_length()
+    ra = a.getEvalStatistics("main")
+    b = acoss_b200.Serra09(str(workdir / "ds.csv"), fdir, shortname="pk_b", downsample_fac=ds["fac"])
+    path = b.build_packed_store()
+    assert os.path.exists(path) and path == b.packed_store_path()
+    c = acoss_b200.Serra09(str(workdir / "ds.csv"), fdir, shortname="pk_b", downsample_fac=ds["fac"])
+    c.filepaths = ["/nonexistent/%d.h5" % k for k in range(c.N)]        # the per-track files must not be touched
+    c.all_pairwise(1, symmetric=True)
+    c.normalize_by_length()
+    rc = c.getEvalStatistics("main")
+    assert np.array_equal(np.array(a.Ds["main"]), np.array(c.Ds["main"]))
+    assert {k: sorted(v) for k, v in a.cliques.items()} == {k: sorted(v) for k, v in c.cliques.items()}
+    assert list(ra[:4]) == list(rc[:4])
+    for o in (a, b, c):
+        o.cleanup_memmap()
+
 
 
 def test_simple_pairs_vs_reference_golden(ctx, golden):

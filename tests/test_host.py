@@ -163,3 +163,38 @@ def test_simple_and_ftm2d_load_features_match_reference(golden, workdir):
     a, b = g["simple_feat0"], g["simple_feat1"]
     rolled, idx = s.oti(a, b)
     assert rolled.shape == b.shape and len(idx) == 12
+
+
+def test_packed_feature_store_roundtrip_and_errors(tmp_path):
+    """featio.save_packed / load_packed: ragged tracks incl. an empty one, labels, mmap view,
+    and loud failures on foreign / truncated / inconsistent files."""
+    from acoss_b200 import featio
+    rng = np.random.default_rng(3)
+    tracks = [rng.random((n, 12)).astype(np.float32) for n in (17, 0, 1, 2049, 300)]
+    labels = ["w0", "w0", "wörk 2", "w3", "w3"]
+    p = str(tmp_path / "x.acosspk")
+    featio.save_packed(p, tracks, labels)
+    frames, offs, lab = featio.load_packed(p)
+    assert isinstance(frames, np.memmap) and frames.dtype == np.float32 and frames.shape == (sum(t.shape[0] for t in tracks), 12)
+    assert lab == labels and offs.tolist() == [0, 17, 17, 18, 2067, 2367]
+    for k, t in enumerate(tracks):
+        assert np.array_equal(np.asarray(frames[offs[k]:offs[k + 1]]), t)
+    assert frames.offset % 64 == 0                              # data section is 64-byte aligned
+    with pytest.raises(ValueError):
+        featio.save_packed(p + "2", tracks, labels[:-1])
+    with pytest.raises(ValueError):
+        featio.save_packed(p + "2", [tracks[0], tracks[0][:, :5]], ["a", "b"])
+    with pytest.raises(ValueError):
+        featio.save_packed(p + "2", tracks[:1], ["bad\nlabel"])
+    bad = str(tmp_path / "bad.acosspk")
+    open(bad, "wb").write(b"not a store" * 20)
+    with pytest.raises(IOError):
+        featio.load_packed(bad)
+    raw = bytearray(open(p, "rb").read())
+    raw[64 + 8:64 + 16] = np.array([-5], np.int64).tobytes()    # offsets no longer monotone
+    open(bad, "wb").write(bytes(raw))
+    with pytest.raises(IOError):
+        featio.load_packed(bad)
+    open(bad, "wb").write(bytes(open(p, "rb").read()[:40]))     # truncated header
+    with pytest.raises(IOError):
+        featio.load_packed(bad)
