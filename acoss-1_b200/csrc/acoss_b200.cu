@@ -53,6 +53,7 @@ struct acoss_ctx {
     std::vector<int32_t> h_emb;       // embedded rows per track
     std::vector<int64_t> h_sd_off;    // self-dot table offsets
     DevBuf d_frames, d_offs, d_emb, d_sd_off, d_selfdot, d_gchroma, d_fnorm;
+    DevBuf d_dp_order;                // per batch: DP hand-out order (largest pair first) + two launch counters
     DevBuf d_smpop;                   // per-track sample operands of the tensor-core CRP kernel (m = 9, tau = 1 only)
     bool have_smpop = false;
     // SiMPle feature store (frame-major float64) + per-track chroma profiles
@@ -107,6 +108,12 @@ extern "C" int acoss_ctx_create(int device, acoss_ctx** out)
     for (auto& ev : ctx->ev) cudaEventCreate(&ev);
     cudaDeviceGetAttribute(&ctx->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
+    {   // CRP working set per batch: a quarter of the free HBM, at most 32 GiB (several DP waves per batch: with the
+        // largest-first hand-out the tail of a batch is short), at least the old 8 GiB default when that much is free
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && free_b > 0)
+            ctx->crp_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)32 << 30, free_b / 4));
+    }
     if (const char* s = getenv("ACOSS_CRP_BUDGET_MB")) {
         long mb = atol(s);
         if (mb > 0) ctx->crp_budget = (size_t)mb << 20;
@@ -121,7 +128,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
-                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
+                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_dp_order, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
                       &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],

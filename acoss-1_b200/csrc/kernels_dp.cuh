@@ -132,8 +132,11 @@ __device__ __forceinline__ void dp_row_step(uint32_t (&Aprev)[NCH][G], uint32_t 
 template <int G, int NCH, int ALIGN>
 __global__ void __launch_bounds__(128)
 dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
-                 const uint8_t* __restrict__ crp, float* __restrict__ out)
+                 const uint8_t* __restrict__ crp, float* __restrict__ out,
+                 const int32_t* __restrict__ order, unsigned* __restrict__ counter)
 {
+    // order / counter (both or neither): pairs are handed out dynamically, largest M x N first (the host sorts `order`),
+    // so that a batch of several waves of unequal pairs ends with a short tail; null: static round-robin.
     constexpr int CHUNK = 64 * G;       // cells (= bytes) per chunk
     constexpr int LB = 2 * G;           // bytes per lane and chunk
     const int lane = threadIdx.x & 31;
@@ -141,8 +144,15 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const uint32_t zmask = (lane == 0) ? 0xFFFF0000u : 0xFFFFFFFFu;   // clears cells j = 0, 1
 
-    for (int64_t pidx = warp0; pidx < n_pairs; pidx += nwarps) {
-        const PairDesc pd = descs[pidx];
+    for (int64_t it = warp0;; it += nwarps) {
+        int64_t k = it;
+        if (counter) {
+            unsigned kk = 0;
+            if (lane == 0) kk = atomicAdd(counter, 1u);
+            k = __shfl_sync(0xffffffffu, kk, 0);
+        }
+        if (k >= n_pairs) break;
+        const PairDesc pd = descs[order ? order[k] : k];
         const int M = pd.M, N = pd.N, pitch = pd.pitch;
         const int nch = (N + CHUNK - 1) / CHUNK;
         const uint8_t* base = crp + pd.crp_off + (int64_t)lane * LB;

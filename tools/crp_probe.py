@@ -9,7 +9,7 @@ from acoss_b200 import synth
 def main():
     lens = [int(x) for x in sys.argv[1].split(",")]
     mode = int(sys.argv[2]) if len(sys.argv) > 2 else 2
-    n = 64
+    n = int(os.environ.get("ACOSS_PROBE_N", "64"))
     ctx = acoss_b200.Context(0)
     for L in lens:
         labels, works, tids, hp = synth.make_tracks(n // 2, 2, 0, 5, L, L)
