@@ -332,6 +332,11 @@ def run_ours(args, rank, world, local_rank):
          "traffic_note": "DRAM bytes per launch (2 launches per batch): ncu dram bytes per CRP cell (profiles/traffic.json) x cells per launch; "
                          "the CRP itself is 1 B per cell and pass, the rest is list spill written back from L2",
          "launches_per_step": n_crp_launch, "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
+         # what the tensor pipe actually executes: three streaming passes (column count, row count, binarise) of 41 TF32 MMAs
+         # of 128x256x8 per 128x256 tile = 656 flop per cell and pass (tile padding and the sample MMAs not counted), against
+         # the dense TF32 peak = half the measured bf16 figure
+         "executed_tflops": 3.0 * 656.0 * st["crp_cells"] / (ms_crp * 1e-3) / 1e12,
+         "executed_frac_of_tf32_peak": 3.0 * 656.0 * st["crp_cells"] / (ms_crp * 1e-3) / 1e12 / (0.5 * pk["bf16_sus"]),
          "note": "algorithmic flop = (2*108+5)*M*N per pair (SURVEY 8(d)), peak = measured dense bf16. The kernel runs the "
                  "contraction 2.5 times (column thresholds, row thresholds, binarise) as 3-product TF32 splits on tcgen05 "
                  "(41 MMAs of 128x256x8 per tile = 664 executed flop per cell and pass, dense TF32 peak is half the bf16 "
