@@ -94,6 +94,7 @@ simple_pair_kernel(const int32_t* __restrict__ pairs, int64_t n_pairs, const dou
     double* As = reinterpret_cast<double*>(simple_smem);
     double* Bs = As + (size_t)maxL * ACOSS_NBINS;
     unsigned long long* mp = reinterpret_cast<unsigned long long*>(Bs + (size_t)maxL * ACOSS_NBINS);
+    int* segpre = reinterpret_cast<int*>(mp + maxL);            // [2 maxL + 2] segments in the diagonals before d
     __shared__ double otiv[ACOSS_NBINS];
     __shared__ int s_oti;
     __shared__ double s_med[2];
@@ -124,14 +125,40 @@ simple_pair_kernel(const int32_t* __restrict__ pairs, int64_t n_pairs, const dou
         const int n_mp = La - sslen + 1, n_q = Lb - sslen + 1;
         for (int e = tid; e < n_mp; e += SIMPLE_THREADS) mp[e] = 0x7FF0000000000000ull;     // +inf
         __syncthreads();
-        // work items: (diagonal delta = q - p, segment of SIMPLE_SEG profile rows), dealt round-robin
-        int item = 0;
-        for (int delta = -(n_mp - 1); delta <= n_q - 1; ++delta) {
+        // work items: (diagonal delta = q - p, segment of SIMPLE_SEG profile rows).  The item -> (diagonal, segment) map goes
+        // through a prefix table of segments per diagonal, so that thread t takes items t, t + 256, ... and ALL lanes of a
+        // warp walk their segments at the same time.  (Dealing the items out inside the enumeration loop left ONE lane of a
+        // warp active at a time: ncu showed ~30x the warp-level instructions the cells need.)
+        const int nd = n_mp + n_q - 1;                         // diagonals, index d = delta + n_mp - 1
+        for (int d = tid; d < nd; d += SIMPLE_THREADS) {
+            const int delta = d - (n_mp - 1);
+            const int p_lo = delta < 0 ? -delta : 0, p_hi = min(n_mp - 1, n_q - 1 - delta);
+            segpre[d + 1] = (p_hi - p_lo + SIMPLE_SEG) / SIMPLE_SEG;
+        }
+        if (tid == 0) segpre[0] = 0;
+        __syncthreads();
+        if (tid < 32) {                                        // inclusive scan of segpre[1 .. nd] by warp 0
+            const int per = (nd + 31) / 32;
+            const int lo = 1 + tid * per, hi = min(nd + 1, lo + per);
+            int sum = 0;
+            for (int i = lo; i < hi; ++i) sum += segpre[i];
+            int incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += t_; }
+            int run = incl - sum;
+            for (int i = lo; i < hi; ++i) { run += segpre[i]; segpre[i] = run; }
+        }
+        __syncthreads();
+        const int n_items = segpre[nd];
+        for (int item = tid; item < n_items; item += SIMPLE_THREADS) {
+            int lo = 0, hi = nd;                               // segpre[lo] <= item < segpre[hi]
+            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (segpre[mid] <= item) lo = mid; else hi = mid; }
+            const int delta = lo - (n_mp - 1);
             const int p_lo = delta < 0 ? -delta : 0;                  // first profile row on this diagonal
             const int p_hi = min(n_mp - 1, n_q - 1 - delta);          // last
             const int n_rows = p_hi - p_lo + 1;
-            for (int r0 = 0; r0 < n_rows; r0 += SIMPLE_SEG, ++item) {
-                if ((item & (SIMPLE_THREADS - 1)) != tid) continue;
+            const int r0 = (item - segpre[lo]) * SIMPLE_SEG;
+            {
                 const int n_out = min(SIMPLE_SEG, n_rows - r0);
                 const int p0 = p_lo + r0, q0 = p0 + delta;
                 if (SSLEN_T > 0) simple_walk<(SSLEN_T > 0 ? SSLEN_T : 1)>(As, Bs, p0, q0, n_out, mp);
