@@ -17,7 +17,11 @@
 #include "common.cuh"
 
 #define SIMPLE_THREADS 256
-#define SIMPLE_SEG 48            // profile rows per work item (plus SSLEN-1 warm-up cells)
+#define SIMPLE_SEG 49            // profile rows per work item (plus SSLEN-1 warm-up cells); ODD, see SIMPLE_FS
+#define SIMPLE_FS 14             // doubles per frame in shared memory (12 bins + 2 pad).  The lanes of a warp walk segments whose
+                                 // first rows are SIMPLE_SEG apart: with 12-double frames and 48-row segments every lane hit the
+                                 // same bank (48 x 24 words = 0 mod 32: ncu showed the shared-memory pipe 97 % busy on conflicts);
+                                 // 49 x 28 words = 28 mod 32 puts the eight lanes of a 16-byte-load phase on eight different bank quads
 
 // feats: frame-major (L_t, 12) float64 per track; prof: (n_tracks, 12) sums over time
 __global__ void simple_prepare_kernel(const double* __restrict__ rowmajor /* (12, L) per track */,
@@ -56,8 +60,8 @@ __device__ __forceinline__ void simple_walk(const double* __restrict__ As, const
         for (int k = 0; k < SSLEN; ++k) {
             const int t = base + k;
             if (t < total) {
-                const double* a = As + (p0 + t) * ACOSS_NBINS;
-                const double* b = Bs + (q0 + t) * ACOSS_NBINS;
+                const double* a = As + (p0 + t) * SIMPLE_FS;
+                const double* b = Bs + (q0 + t) * SIMPLE_FS;
                 double g = 0.0;
 #pragma unroll
                 for (int c = 0; c < ACOSS_NBINS; ++c) { const double d = a[c] - b[c]; g = fma(d, d, g); }
@@ -92,8 +96,8 @@ simple_pair_kernel(const int32_t* __restrict__ pairs, int64_t n_pairs, const dou
 {
     extern __shared__ __align__(16) unsigned char simple_smem[];
     double* As = reinterpret_cast<double*>(simple_smem);
-    double* Bs = As + (size_t)maxL * ACOSS_NBINS;
-    unsigned long long* mp = reinterpret_cast<unsigned long long*>(Bs + (size_t)maxL * ACOSS_NBINS);
+    double* Bs = As + (size_t)maxL * SIMPLE_FS;
+    unsigned long long* mp = reinterpret_cast<unsigned long long*>(Bs + (size_t)maxL * SIMPLE_FS);
     int* segpre = reinterpret_cast<int*>(mp + maxL);            // [2 maxL + 2] segments in the diagonals before d
     __shared__ double otiv[ACOSS_NBINS];
     __shared__ int s_oti;
@@ -117,10 +121,13 @@ simple_pair_kernel(const int32_t* __restrict__ pairs, int64_t n_pairs, const dou
         }
         __syncthreads();
         const int rot = s_oti;
-        for (int e = tid; e < La * ACOSS_NBINS; e += SIMPLE_THREADS) As[e] = feats[oa * ACOSS_NBINS + e];
+        for (int e = tid; e < La * ACOSS_NBINS; e += SIMPLE_THREADS) {
+            const int p = e / ACOSS_NBINS, c = e - p * ACOSS_NBINS;
+            As[p * SIMPLE_FS + c] = feats[oa * ACOSS_NBINS + e];
+        }
         for (int e = tid; e < Lb * ACOSS_NBINS; e += SIMPLE_THREADS) {
             const int q = e / ACOSS_NBINS, c = e - q * ACOSS_NBINS;
-            Bs[e] = feats[(ob + q) * ACOSS_NBINS + rot_src(c, rot)];
+            Bs[q * SIMPLE_FS + c] = feats[(ob + q) * ACOSS_NBINS + rot_src(c, rot)];
         }
         const int n_mp = La - sslen + 1, n_q = Lb - sslen + 1;
         for (int e = tid; e < n_mp; e += SIMPLE_THREADS) mp[e] = 0x7FF0000000000000ull;     // +inf
@@ -165,8 +172,8 @@ simple_pair_kernel(const int32_t* __restrict__ pairs, int64_t n_pairs, const dou
                 else {
                     double s = 0.0;
                     for (int t = 0; t < n_out + sslen - 1; ++t) {
-                        s += simple_cell(As + (p0 + t) * ACOSS_NBINS, Bs + (q0 + t) * ACOSS_NBINS);
-                        if (t >= sslen) s -= simple_cell(As + (p0 + t - sslen) * ACOSS_NBINS, Bs + (q0 + t - sslen) * ACOSS_NBINS);
+                        s += simple_cell(As + (p0 + t) * SIMPLE_FS, Bs + (q0 + t) * SIMPLE_FS);
+                        if (t >= sslen) s -= simple_cell(As + (p0 + t - sslen) * SIMPLE_FS, Bs + (q0 + t - sslen) * SIMPLE_FS);
                         if (t >= sslen - 1) {
                             const double v = s < 0.0 ? 0.0 : s;
                             const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
