@@ -32,10 +32,17 @@ class PairStats(ctypes.Structure):
     _fields_ = [("ms_total", ctypes.c_double), ("ms_prep", ctypes.c_double), ("ms_crp", ctypes.c_double),
                 ("ms_dp", ctypes.c_double), ("dp_cells", ctypes.c_int64), ("crp_cells", ctypes.c_int64),
                 ("crp_bytes", ctypes.c_int64), ("n_launches", ctypes.c_int64), ("n_dp_launches", ctypes.c_int64),
-                ("n_batches", ctypes.c_int64), ("n_exact_cells", ctypes.c_int64), ("n_fallback_rows", ctypes.c_int64)]
+                ("n_batches", ctypes.c_int64), ("n_exact_cells", ctypes.c_int64), ("n_fallback_rows", ctypes.c_int64),
+                ("crp_kernel_mask", ctypes.c_int64), ("dp_kernel_mask", ctypes.c_int64)]
+
+    CRP_KERNELS = {1: "exact", 2: "band", 4: "band_tc", 8: "gemm", 16: "split"}
+    DP_KERNELS = {1: "rowpar", 2: "generic"}
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        d = {k: getattr(self, k) for k, _ in self._fields_}
+        d["crp_kernels"] = [n for b, n in self.CRP_KERNELS.items() if d["crp_kernel_mask"] & b]
+        d["dp_kernels"] = [n for b, n in self.DP_KERNELS.items() if d["dp_kernel_mask"] & b]
+        return d
 
 
 # every symbol include/acoss_b200.h declares: (restype, argtypes)
@@ -46,6 +53,7 @@ SYMBOLS = {
     "acoss_version": (ctypes.c_char_p, []),
     "acoss_ctx_stream": (c_vp, [c_vp]),
     "acoss_ctx_synchronize": (ctypes.c_int, [c_vp]),
+    "acoss_ctx_set_option": (ctypes.c_int, [c_vp, ctypes.c_char_p, ctypes.c_int64]),
     "acoss_upload_tracks": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
     "acoss_median_downsample": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, c_f32p, c_i64p]),
     "acoss_serra09_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_f32p, c_f32p]),
@@ -147,6 +155,10 @@ class Context(object):
 
     def synchronize(self):
         self._ck(self.lib.acoss_ctx_synchronize(self.h))
+
+    def set_option(self, key, value):
+        """acoss_ctx_set_option: "crp_budget_bytes", "inject_alloc_failures" (include/acoss_b200.h)."""
+        self._ck(self.lib.acoss_ctx_set_option(self.h, key.encode(), int(value)))
 
     # ---- tracks ---------------------------------------------------------------
     @staticmethod

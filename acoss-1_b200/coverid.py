@@ -81,8 +81,6 @@ def benchmark(dataset_csv, feature_dir, feature_type="hpcp", algorithm="Serra09"
             algo.load_features(i)
         _logger().info('Feature loading done...')
         algo.all_pairwise(parallel, n_cores=n_workers, symmetric=False)
-    else:
-        raise NotImplementedError("acoss_b200: '%s' is not built yet in this round (see DESIGN.md)" % algorithm)
     _logger().info('Running benchmark evaluations on the given dataset - %s' % dataset_csv)
     for similarity_type in list(algo.Ds.keys()):
         results[similarity_type] = algo.getEvalStatistics(similarity_type)

@@ -72,6 +72,7 @@ struct acoss_ctx {
     acoss_pair_stats stats = {};
     unsigned long long h_counters[ACOSS_N_COUNTERS] = {};
     size_t crp_budget = (size_t)8 << 30;
+    int inject_alloc_failures = 0;    // test hook (acoss_ctx_set_option)
     int max_smem = 0;
     int num_sms = ACOSS_NUM_SMS;
 
@@ -129,7 +130,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
                       &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_dp_order, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
-                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters,
+                      &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters, &ctx->d_lists,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
                       &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin};
@@ -137,6 +138,23 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t value)
+{
+    if (!ctx || !key) return ACOSS_ERR_ARG;
+    const std::string k(key);
+    if (k == "crp_budget_bytes") {
+        if (value <= 0) { ctx->set_error("crp_budget_bytes must be positive"); return ACOSS_ERR_ARG; }
+        ctx->crp_budget = (size_t)value;
+        return ACOSS_OK;
+    }
+    if (k == "inject_alloc_failures") {
+        ctx->inject_alloc_failures = (int)std::max<int64_t>(0, value);
+        return ACOSS_OK;
+    }
+    ctx->set_error("acoss_ctx_set_option: unknown key " + k);
+    return ACOSS_ERR_ARG;
 }
 
 extern "C" void* acoss_ctx_stream(acoss_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
@@ -222,11 +240,14 @@ extern "C" int acoss_upload_tracks(acoss_ctx* ctx, const float* frames_host, con
         CK_LAUNCH();
     }
     if (max_emb > 0) {
-        dim3 grid((max_emb * ACOSS_NBINS + 127) / 128, n_tracks);
-        selfdot_kernel<<<grid, 128, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(),
-                                             ctx->d_emb.as<int32_t>(), ctx->d_sd_off.as<int64_t>(), m, tau,
-                                             ctx->d_selfdot.as<float>());
-        CK_LAUNCH();
+        // grid.y is limited to 65535: tracks go in y-chunks
+        for (int t0 = 0; t0 < n_tracks; t0 += 65535) {
+            dim3 grid((max_emb * ACOSS_NBINS + 127) / 128, std::min(65535, n_tracks - t0));
+            selfdot_kernel<<<grid, 128, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(),
+                                                 ctx->d_emb.as<int32_t>(), ctx->d_sd_off.as<int64_t>(), m, tau,
+                                                 ctx->d_selfdot.as<float>(), t0);
+            CK_LAUNCH();
+        }
     }
     // sample operands of the tensor-core CRP kernel: 225 KB per track, built only when they fit a 6 GiB budget (the kernel
     // gathers the samples itself otherwise)
@@ -247,7 +268,7 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 {
     if (!ctx) return ACOSS_ERR_ARG;
     if (!raw_frames_host || !raw_offsets_host || !out_frames_host || !out_offsets_host || n_tracks <= 0 || fac < 1 || fac > 256) {
-        ctx->set_error("acoss_median_downsample: bad argument (1 <= fac <= 256)");
+        ctx->set_error("acoss_median_downsample: bad argument (need non-null buffers, n_tracks > 0 and 1 <= fac <= 256: a segment is sorted in a 256-entry per-thread array)");
         return ACOSS_ERR_ARG;
     }
     CK(cudaSetDevice(ctx->device));
@@ -271,16 +292,17 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
         return ACOSS_ERR_NOMEM;
     }
     cudaStream_t st = ctx->stream;
-    cudaMemcpyAsync(raw.p, raw_frames_host, sizeof(float) * ACOSS_NBINS * (size_t)total_raw, cudaMemcpyHostToDevice, st);
-    cudaMemcpyAsync(roff.p, raw_offsets_host, sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st);
-    cudaMemcpyAsync(ooff.p, oo.data(), sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st);
-    if (max_out > 0) {
-        dim3 grid((unsigned)((max_out * ACOSS_NBINS + 127) / 128), n_tracks);
+    cudaError_t e = cudaMemcpyAsync(raw.p, raw_frames_host, sizeof(float) * ACOSS_NBINS * (size_t)total_raw, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(roff.p, raw_offsets_host, sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ooff.p, oo.data(), sizeof(int64_t) * (n_tracks + 1), cudaMemcpyHostToDevice, st);
+    for (int t0 = 0; e == cudaSuccess && max_out > 0 && t0 < n_tracks; t0 += 65535) {      // grid.y <= 65535
+        dim3 grid((unsigned)((max_out * ACOSS_NBINS + 127) / 128), std::min(65535, n_tracks - t0));
         median_downsample_kernel<256><<<grid, 128, 0, st>>>(raw.as<float>(), roff.as<int64_t>(), ooff.as<int64_t>(),
-                                                            n_tracks, fac, outb.as<float>());
+                                                            n_tracks, fac, outb.as<float>(), t0);
+        e = cudaGetLastError();
     }
-    cudaMemcpyAsync(out_frames_host, outb.p, sizeof(float) * ACOSS_NBINS * (size_t)total_out, cudaMemcpyDeviceToHost, st);
-    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_frames_host, outb.p, sizeof(float) * ACOSS_NBINS * (size_t)total_out, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e == cudaSuccess) e = cudaGetLastError();
     cleanup();
     if (e != cudaSuccess) { ctx->set_error(std::string("acoss_median_downsample: ") + cudaGetErrorString(e)); return ACOSS_ERR_CUDA; }

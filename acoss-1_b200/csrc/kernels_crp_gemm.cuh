@@ -286,8 +286,15 @@ crp_strip_gemm_kernel(const PairDesc* __restrict__ descs,
                       int side_a_is_query, float qf,
                       float2* __restrict__ lists,            // [gridDim.x][4][GM_SUBCAP][GM_ROWS] (rho~, column) of the listed elements
                       const unsigned char* __restrict__ smpop, // per-track sample operands (gm_sample_operand_kernel) or null: gather in the kernel
-                      unsigned long long* __restrict__ counters, int dbg)
+                      unsigned long long* __restrict__ counters, int dbg_arg)
 {
+#ifdef ACOSS_PROFILE_BUILD
+    const int dbg = dbg_arg;            // kernel-timing experiments (skip phases; results are wrong): profile builds only
+#else
+    (void)dbg_arg;
+    constexpr int dbg = 0;              // release: every `dbg &` branch folds away
+#endif
+
     extern __shared__ __align__(128) unsigned char gsm[];
     unsigned char* Apl = gsm;
     unsigned char* R1 = gsm + GM_A_BYTES;

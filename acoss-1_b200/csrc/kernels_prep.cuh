@@ -42,9 +42,9 @@ __global__ void selfdot_kernel(const float* __restrict__ frames,
                                const int64_t* __restrict__ offs,
                                const int32_t* __restrict__ emb_len,
                                const int64_t* __restrict__ sd_off,
-                               int m, int tau, float* __restrict__ sd)
+                               int m, int tau, float* __restrict__ sd, int track0)
 {
-    int track = blockIdx.y;
+    int track = track0 + blockIdx.y;
     int M = emb_len[track];
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= M * ACOSS_NBINS) return;
@@ -98,9 +98,9 @@ template <int MAXFAC>
 __global__ void median_downsample_kernel(const float* __restrict__ raw,
                                          const int64_t* __restrict__ raw_offs,
                                          const int64_t* __restrict__ out_offs,
-                                         int n_tracks, int fac, float* __restrict__ out)
+                                         int n_tracks, int fac, float* __restrict__ out, int track0)
 {
-    int track = blockIdx.y;
+    int track = track0 + blockIdx.y;
     int64_t T = raw_offs[track + 1] - raw_offs[track];
     int64_t nout = out_offs[track + 1] - out_offs[track];
     int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

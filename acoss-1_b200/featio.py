@@ -1,13 +1,17 @@
 # -*- coding: utf-8 -*-
 """
-Per-track feature files.  The reference stores one deepdish-HDF5 dict per track
+Per-track feature files and result files.  The reference stores deepdish-HDF5 dicts
 (`dd.io.load(path)` / `dd.io.save`, acoss/algorithms/algorithm_template.py:90,193;
-schema README.md:94-114).  deepdish / h5py / pytables are not installed in this
-image, so `load`/`save` use deepdish when importable and otherwise a pickled dict
-with the same keys under the same `.h5` path (the synthetic generator writes that).
-"""
-import pickle
+schema README.md:94-114).
 
+* With deepdish importable, `save` writes real deepdish HDF5 and `load` reads it: the files
+  are then interchangeable with the reference's.
+* deepdish / h5py / pytables are NOT installed in this image, so here `save` writes the same
+  (nested) dict under the same `.h5` path as a numpy `.npz` archive with '/'-joined keys --
+  a plain data container, loaded with `allow_pickle=False`.  A real Da-TACOS `.h5` directory
+  therefore cannot be read on this box; `load` says so instead of guessing.
+* Nothing is ever unpickled: a feature directory is untrusted input.
+"""
 import numpy as np
 
 try:  # pragma: no cover - not available in this image
@@ -18,6 +22,42 @@ except Exception:  # ImportError and friends
     _dd = None
 
 _HDF5_MAGIC = b"\x89HDF\r\n\x1a\n"
+_ZIP_MAGIC = b"PK\x03\x04"
+_NPZ_MARK = "__acoss_npz__"
+
+
+def _flatten(obj, prefix, out):
+    if isinstance(obj, dict):
+        if not obj:
+            out[prefix + "/__empty__" if prefix else "__empty__"] = np.zeros(0, np.uint8)
+        for k, v in obj.items():
+            k = str(k)
+            if "/" in k or k.startswith("__"):
+                raise ValueError("featio.save: key %r cannot be stored" % k)
+            _flatten(v, prefix + "/" + k if prefix else k, out)
+        return
+    a = np.array(obj) if isinstance(obj, np.memmap) else np.asarray(obj)
+    if a.dtype == object:
+        raise ValueError("featio.save: value under %r is not plain numeric / string data" % prefix)
+    out[prefix] = a
+
+
+def _unflatten(npz):
+    root = {}
+    for key in npz.files:
+        if key == _NPZ_MARK:
+            continue
+        parts = key.split("/")
+        d = root
+        for p in parts[:-1]:
+            d = d.setdefault(p, {})
+        if parts[-1] == "__empty__":
+            continue
+        a = npz[key]
+        if a.ndim == 0:
+            a = a.item()            # str / int / float leaves come back as Python scalars, like deepdish
+        d[parts[-1]] = a
+    return root
 
 
 def load(path):
@@ -25,17 +65,30 @@ def load(path):
         head = f.read(8)
     if head == _HDF5_MAGIC:
         if _dd is None:
-            raise IOError("%s is an HDF5 file but deepdish is not installed" % path)
+            raise IOError("%s is an HDF5 file but deepdish is not installed in this environment" % path)
         return _dd.io.load(path)
-    with open(path, "rb") as f:
-        return pickle.load(f)
+    if head[:4] == _ZIP_MAGIC:
+        with np.load(path, allow_pickle=False) as z:
+            if _NPZ_MARK not in z.files:
+                raise IOError("%s is a zip archive but not an acoss_b200 feature file" % path)
+            return _unflatten(z)
+    raise IOError("%s is neither deepdish HDF5 nor an acoss_b200 npz container (pickled files are refused: "
+                  "feature directories are untrusted input)" % path)
 
 
 def save(path, obj):
     if isinstance(obj, dict):
         obj = {k: (np.array(v) if isinstance(v, np.memmap) else v) for k, v in obj.items()}
-    with open(path, "wb") as f:
-        pickle.dump(obj, f, protocol=4)
+    if _dd is not None:  # pragma: no cover - not available in this image
+        _dd.io.save(path, obj)
+        return
+    if not isinstance(obj, dict):
+        raise ValueError("featio.save: only dicts are stored")
+    flat = {}
+    _flatten(obj, "", flat)
+    flat[_NPZ_MARK] = np.array(1, np.uint8)
+    with open(path, "wb") as f:      # a file object keeps the `.h5` name (np.savez would append .npz to a str)
+        np.savez(f, **flat)
 
 
 # ---- packed store ---------------------------------------------------

@@ -52,8 +52,14 @@ def _latent(rng, length):
     return out
 
 
-def _render(rng, latent, length, noise):
-    """warp latent to `length` frames, key shift, optional deletion, noise, max-normalise"""
+# the "hard" cover model (bench.py C1/C2, tests/golden/serra09_L48.npz): heavier noise and a fraction of every cover's chord
+# segments replaced by unrelated chords, so that retrieval is NOT saturated (MAP < 1, mean rank > 1) and an evaluation
+# tuple that differs from the oracle's can actually be seen
+HARD = dict(noise=0.25, p_sub=0.25)
+
+
+def _render(rng, latent, length, noise, p_sub=0.0):
+    """warp latent to `length` frames, key shift, optional deletion, chord substitutions, noise, max-normalise"""
     L0 = latent.shape[0]
     # piecewise tempo: 8 segments with speeds in [0.8, 1.2]
     speeds = rng.uniform(0.8, 1.2, size=8)
@@ -64,13 +70,21 @@ def _render(rng, latent, length, noise):
         a = int(rng.integers(0, length // 2))
         b = a + int(rng.integers(length // 20, length // 7))
         x = np.concatenate([x[:a], x[b:], x[a:b][::-1][: b - a]], axis=0)[:length]
+    if p_sub > 0.0:                               # replace a fraction of the chord segments by unrelated chords
+        x = np.array(x)
+        t = 0
+        while t < length:
+            dur = int(rng.integers(8, 41))
+            if rng.random() < p_sub:
+                x[t:t + dur] = _latent(rng, dur)[:len(x[t:t + dur])]
+            t += dur
     x = np.roll(x, int(rng.integers(0, 12)), axis=1)
     x = x + np.abs(rng.normal(0.0, noise, size=x.shape)).astype(np.float32)
     x = x / np.maximum(x.max(axis=1, keepdims=True), 1e-9)
     return np.ascontiguousarray(x, dtype=np.float32)
 
 
-def make_tracks(n_works, per_work, n_singletons, seed, len_lo, len_hi, noise=0.12):
+def make_tracks(n_works, per_work, n_singletons, seed, len_lo, len_hi, noise=0.12, p_sub=0.0):
     """Returns (labels: list[str], work_ids: list[str], track_ids: list[str], hpcps: list[(T,12) f32])."""
     rng = np.random.default_rng(seed)
     n = n_works * per_work + n_singletons
@@ -88,20 +102,23 @@ def make_tracks(n_works, per_work, n_singletons, seed, len_lo, len_hi, noise=0.1
             labels.append("W_%d" % w)
             works.append("W_%d" % w)
             tids.append("P_%d_%d" % (w, c))
-            hp.append(_render(rng, lat, int(lengths[k]), noise))
+            hp.append(_render(rng, lat, int(lengths[k]), noise, p_sub))
             k += 1
     return labels, works, tids, hp
 
 
-def make_named(shape="covers80", regime="S", seed=None, scale=1.0):
-    """Tracks of one of SHAPES x REGIMES.  `scale` < 1 shrinks the number of works (tests)."""
+def make_named(shape="covers80", regime="S", seed=None, scale=1.0, hard=False, **model):
+    """Tracks of one of SHAPES x REGIMES.  `scale` < 1 shrinks the number of works (tests); `hard` selects the HARD
+    cover model; other keywords (noise, p_sub) override the cover model."""
     nw, pw, ns = SHAPES[shape]
     if scale != 1.0:
         nw, ns = max(1, int(round(nw * scale))), int(round(ns * scale))
     rg = REGIMES[regime]
     if seed is None:
         seed = {"covers80": 80, "datacos1000": 1000, "datacos15000": 15000}[shape]
-    labels, works, tids, hp = make_tracks(nw, pw, ns, seed, rg["len_lo"], rg["len_hi"])
+    kw = dict(HARD) if hard else {}
+    kw.update(model)
+    labels, works, tids, hp = make_tracks(nw, pw, ns, seed, rg["len_lo"], rg["len_hi"], **kw)
     return dict(labels=labels, work_ids=works, track_ids=tids, hpcp=hp, fac=rg["fac"])
 
 

@@ -43,6 +43,8 @@ def parse_args():
                     help="track-length regime (SURVEY 8(d)); L = n~U[1600,2400] frames at the DP stage")
     ap.add_argument("--scale", type=float, default=1.0, help="DEBUG ONLY: shrink the number of works")
     ap.add_argument("--crp-mode", type=int, default=0)
+    ap.add_argument("--easy", action="store_true", help="the round-1 cover model (retrieval saturates: MAP = 1); default is synth.HARD")
+    ap.add_argument("--parity-pairs", type=int, default=64, help="random pairs of the grid re-computed by the oracle outside the timed region")
     ap.add_argument("--no-e2e", action="store_true", help="DEBUG ONLY: skip the end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true", help="DEBUG ONLY: skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work of the cpu_baseline sample")
@@ -74,7 +76,7 @@ def measured_traffic():
 def make_workload(args):
     """Downsampled chroma of every track (what Serra09.load_features returns) + labels."""
     from acoss_b200 import synth
-    ds = synth.make_named(args.shape, args.regime, scale=args.scale)
+    ds = synth.make_named(args.shape, args.regime, scale=args.scale, hard=not args.easy)
     fac = ds["fac"]
     return ds, fac
 
@@ -312,8 +314,9 @@ def run_ours(args, rank, world, local_rank):
     ms_tot = float(np.mean([s["ms_total"] for s in stats_acc]))
     st = stats_acc[-1]
     n_dp_launch = max(1, st["n_dp_launches"])
-    dp_bytes = st["crp_bytes"] + 4 * len(mine)              # algorithmic: M*pitch CRP bytes read once + 4 B score
+    dp_bytes = st["crp_cells"] + 4 * len(mine)              # ALGORITHMIC: M*N CRP bytes read once + 4 B score per pair
     dp_gbs = dp_bytes / (ms_dp * 1e-3) / 1e9
+    dp_streamed = st["crp_bytes"] + 4 * len(mine)           # what the kernel streams: M*pitch (row pitch padded to the DP chunk)
     gcups = st["dp_cells"] / (ms_dp * 1e-3) / 1e9
     crp_flop = 2.0 * 108 * st["crp_cells"] + 5.0 * st["crp_cells"]
     crp_tflops = crp_flop / (ms_crp * 1e-3) / 1e12
@@ -324,6 +327,7 @@ def run_ours(args, rank, world, local_rank):
     kernels = [
         {"kernel": "dp_rowpar_kernel (Qmax)", "bound": "hbm", "achieved": dp_gbs, "peak": pk["hbm"], "unit": "GB/s",
          "frac": dp_gbs / pk["hbm"], "traffic": dp_traffic, "ms_per_step": ms_dp, "launches_per_step": n_dp_launch,
+         "streamed_bytes_per_launch": dp_streamed / n_dp_launch, "streamed_over_algorithmic": dp_streamed / dp_bytes,
          "gcups": gcups, "share_of_step": ms_dp / ms_tot},
         {"kernel": "crp_strip_gemm_kernel x2 (cross-similarity + thresholds + binarise)" if args.crp_mode in (0, 4)
                    else "crp_strip kernels (cross-similarity + thresholds + binarise)",
@@ -348,6 +352,22 @@ def run_ours(args, rank, world, local_rank):
     roofline["peak_source"] = pk["src"]
     roofline["traffic_source"] = tr.get("source")
 
+    # ---- parity sample (outside the timed region): random pairs of THIS rank's shard, CUDA scores vs the oracle
+    parity = None
+    if args.parity_pairs > 0:
+        from oracle import oracle as O
+        O.build()
+        rng = np.random.default_rng(20261105 + rank)
+        pick = np.sort(rng.choice(len(mine), size=min(args.parity_pairs, len(mine)), replace=False))
+        got = d_scores_local[torch.from_numpy(pick).to(dev)].cpu().numpy()
+        exp, _, _ = O.serra09_pairs(tracks, my_pairs[pick], n_threads=os.cpu_count() or 1)
+        parity = {"pairs": int(len(pick)), "mismatches": int(np.sum(got != exp)),
+                  "checker": "oracle/acoss_oracle.c (C restatement; essentia itself is not installable: parity unpinned)"}
+        if world > 1:
+            tt = torch.tensor([parity["pairs"], parity["mismatches"]], dtype=torch.int64, device=dev)
+            dist.all_reduce(tt)
+            parity["pairs"], parity["mismatches"] = int(tt[0]), int(tt[1])
+
     if rank != 0:
         return
     cpu = None
@@ -362,6 +382,7 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roofline, "roofline_kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(n_launch), "clocks": clocks,
             "eval": {"MR": ev[0], "MRR": ev[1], "MDR": ev[2], "MAP": ev[3], "Top-1": ev[4]},
+            "parity_sample": parity,
             "batches_per_step": int(st["n_batches"]), "crp_mode": args.crp_mode,
             "debug_counters": ctx.debug_counters(),
             "exact_cell_fraction": st["n_exact_cells"] / max(1, 2 * st["crp_cells"]), "fallback_rows": int(st["n_fallback_rows"])}

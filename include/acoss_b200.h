@@ -72,7 +72,20 @@ typedef struct acoss_pair_stats {
     int64_t n_batches;
     int64_t n_exact_cells;   /* cells computed with the oracle's exact op order */
     int64_t n_fallback_rows; /* band mode: rows that fell back to the exact-row path */
+    int64_t crp_kernel_mask; /* which CRP kernels ran (one bit per batch decision), ACOSS_CRP_KERNEL_*:
+                                auto mode picks per batch from the track lengths, so a downgrade is visible here */
+    int64_t dp_kernel_mask;  /* which alignment kernels ran, ACOSS_DP_KERNEL_*              */
 } acoss_pair_stats;
+
+enum {
+    ACOSS_CRP_KERNEL_EXACT = 1,    /* crp_strip_exact_kernel: every cell in the oracle's op order      */
+    ACOSS_CRP_KERNEL_BAND = 2,     /* crp_strip_band_kernel<0>: sliding Gram on the fp32 pipes + band  */
+    ACOSS_CRP_KERNEL_BAND_TC = 4,  /* crp_strip_band_kernel<1>: tcgen05 G2 tiles                       */
+    ACOSS_CRP_KERNEL_GEMM = 8,     /* crp_strip_gemm_kernel: tcgen05 cross-similarity GEMM, one kernel */
+    ACOSS_CRP_KERNEL_SPLIT = 16,   /* crp_sample/count/select/binarise kernels (phase-split pipeline)  */
+    ACOSS_DP_KERNEL_ROWPAR = 1,    /* dp_rowpar_kernel (DPX int16x2, HBM-bound)                        */
+    ACOSS_DP_KERNEL_GENERIC = 2    /* dp_generic_kernel (fp32, any gammas / very long rows)            */
+};
 
 /* ---- context ------------------------------------------------------------- */
 
@@ -87,6 +100,14 @@ const char *acoss_version(void);
 void *acoss_ctx_stream(acoss_ctx *ctx);
 /* Blocks until all work queued on the context's stream has finished. */
 int acoss_ctx_synchronize(acoss_ctx *ctx);
+
+/* Tuning / test knobs of a context.  Keys:
+ *   "crp_budget_bytes"       per-batch CRP working set of acoss_serra09_pairs* (default: a quarter of the free HBM,
+ *                            at most 32 GiB; also settable by the environment variable ACOSS_CRP_BUDGET_MB at creation)
+ *   "inject_alloc_failures"  test hook: the next `value` device allocations of the pair pipeline's batch buffers
+ *                            report ACOSS_ERR_NOMEM (exercises the halve-the-budget retry)
+ * Returns ACOSS_ERR_ARG for an unknown key or a non-positive budget. */
+int acoss_ctx_set_option(acoss_ctx *ctx, const char *key, int64_t value);
 
 /* ---- track store --------------------------------------------------------- */
 

@@ -15,6 +15,13 @@ Files written (all small .npz):
                          verbatim on top of the C restatement of essentia (parity UNPINNED for
                          that part) -> Ds before/after normalisation, eval tuples, a few CRPs
   percentile_kat.npz     oracle percentile vs np.percentile(method='linear') in float32
+  earlyfusion_large.npz  EarlyFusion pairs at BASELINE C3 size (300-600 blocks, n_mfcc = 20): the reference's free
+                         functions + class run verbatim; bit-packed binary matrices, sub-sampled CSM rows, the
+                         k-th / (k+1)-th neighbour gaps of every row (near-tie diagnostics), all scores
+  simple_large.npz       SiMPle at BASELINE C5 size (150-250 columns): 56 ordered pairs, float64 scores
+  serra09_L48.npz        48 tracks at the L length regime (1128 pairs, M, N ~ 1600-2400): oracle scores
+                         (threaded C restatement), then the reference class's normalize_by_length +
+                         getEvalStatistics verbatim on that matrix; harder synthetic covers (MAP < 1)
 """
 import contextlib
 import io
@@ -286,6 +293,138 @@ def gen_early(ns):
     np.savez_compressed(os.path.join(GOLD, "earlyfusion_reference.npz"), **out)
     print("earlyfusion_reference: MAP", {s_: float(out["eval_" + s_][3]) for s_ in ("mfccs", "ssms", "chromas", "early", "late", "early+late")})
 
+def early_large_dataset():
+    """Block features at BASELINE C3 size: 2 works x 2 covers + 1 singleton, 300-600 blocks, d = 1000 / 1225 / 480.
+    Regenerated from the seed on the GPU box (5 MB per track is too much to commit); `checksum` guards it."""
+    from acoss_b200 import synth
+    ds = synth.make_block_features(2, 2, 1, 3301, 300, 600, noise=2.0)
+    ds["hpcp"] = [np.zeros((4, 12), np.float32) for _ in ds["labels"]]
+    ds["fac"] = 1
+    return ds
+
+
+EARLY_LARGE_PAIRS = [(0, 1), (2, 3), (1, 4), (0, 3)]
+
+
+def gen_early_large(ns):
+    from acoss_b200 import synth
+    ds = early_large_dataset()
+    bf = ds["block_feats"]
+    out = {"checksum": np.array([float(np.sum(f["mfccs"], dtype=np.float64) + np.sum(f["ssms"], dtype=np.float64) +
+                                       np.sum(f["chromas"], dtype=np.float64)) for f in bf]),
+           "n_blocks": np.array([f["mfccs"].shape[0] for f in bf], np.int32),
+           "mat_pairs": np.array(EARLY_LARGE_PAIRS, np.int32)}
+    with tempfile.TemporaryDirectory() as tmp:
+        fdir = synth.write_dataset(os.path.join(tmp, "feat"), ds, os.path.join(tmp, "ds.csv"))
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            e = quiet(ns.early.EarlyFusion, os.path.join(tmp, "ds.csv"), fdir, shortname="gl")
+            for i, f in enumerate(bf):
+                e.all_block_feats[i] = f
+            quiet(e.all_pairwise, 0, 1, True)
+            for s_ in ("mfccs", "ssms", "chromas", "early"):
+                out["D_" + s_] = np.array(e.Ds[s_])
+            for k, (a, b) in enumerate(EARLY_LARGE_PAIRS):
+                f1, f2 = bf[a], bf[b]
+                C = [ns.xrec.get_csm(f1["mfccs"], f2["mfccs"]), ns.xrec.get_csm(f1["ssms"], f2["ssms"]),
+                     ns.xrec.get_csm_blocked_oti(f1["chromas"], f2["chromas"], f1["chroma_med"], f2["chroma_med"], ns.xrec.get_csm_cosine)]
+                Ws = [ns.snf.getWCSM(c, e.K, e.K) for c in C]
+                Wsum = np.zeros_like(C[0])
+                for w in Ws:
+                    Wsum += w
+                C.append(np.exp(-Wsum))
+                C = [np.asarray(c, np.float32) for c in C]
+                M, N = C[0].shape
+                kk = int(np.round(e.kappa * N))
+                bins, gaps = [], []
+                for c in C:
+                    B = ns.xrec.csm_to_binary(c, e.kappa)
+                    B = np.asarray(B.toarray() if hasattr(B, "toarray") else B).astype(np.uint8)
+                    bins.append(np.packbits(B, axis=1))
+                    srt = np.sort(c.astype(np.float64), axis=1)
+                    gaps.append(np.stack([srt[:, kk - 1], srt[:, kk]], 1))       # k-th and (k+1)-th smallest of every row
+                out["csm_rows%d" % k] = np.stack([c[::16] for c in C])
+                out["binpk%d" % k] = np.stack(bins)
+                out["kth%d" % k] = np.stack(gaps)
+                out["shape%d" % k] = np.array([M, N, kk], np.int32)
+                out["oti%d" % k] = np.array(ns.xrec.get_oti(f1["chroma_med"], f2["chroma_med"]))
+                out["scores%d" % k] = np.array([float(ns.align.smith_waterman_constrained(np.unpackbits(bp, axis=1)[:, :N])) for bp in bins])
+        finally:
+            os.chdir(cwd)
+    np.savez_compressed(os.path.join(GOLD, "earlyfusion_large.npz"), **out)
+    print("earlyfusion_large:", [tuple(out["shape%d" % k]) for k in range(len(EARLY_LARGE_PAIRS))],
+          [out["scores%d" % k].tolist() for k in range(len(EARLY_LARGE_PAIRS))])
+
+
+def gen_simple_large(ns):
+    """SiMPle at BASELINE C5 size: 8 tracks of 150-250 columns (raw T ~ 15-25 k at SKIP = 100), all 56 ordered pairs."""
+    from acoss_b200 import synth
+    labels, works, tids, hp = synth.make_tracks(3, 2, 2, 5150, 15000, 25000)
+    ds = dict(labels=labels, work_ids=works, track_ids=tids, hpcp=hp, fac=1)
+    out = {"hpcp_sum": np.array([float(np.sum(h, dtype=np.float64)) for h in hp])}
+    with tempfile.TemporaryDirectory() as tmp:
+        fdir = synth.write_dataset(os.path.join(tmp, "feat"), ds, os.path.join(tmp, "ds.csv"))
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            s = quiet(ns.simple.Simple, os.path.join(tmp, "ds.csv"), fdir, shortname="gl")
+            feats = [np.asarray(quiet(s.load_features, i), np.float64) for i in range(s.N)]
+            prs = [(a, b) for a in range(s.N) for b in range(s.N) if a != b]
+            out["pairs"] = np.array(prs, np.int32)
+            out["scores"] = np.array([-s.simple_sim(feats[a], s.oti(feats[a], feats[b])[0]) for a, b in prs], np.float64)
+            out["n"] = np.array(s.N)
+            for i, f in enumerate(feats):
+                out["feat%d" % i] = f
+        finally:
+            os.chdir(cwd)
+    np.savez_compressed(os.path.join(GOLD, "simple_large.npz"), **out)
+    print("simple_large:", [f.shape[1] for f in feats], "scores", out["scores"][:4])
+
+
+def serra_L48_dataset():
+    """48 tracks at the L regime (n ~ 1600-2400 frames at the DP stage, downsample_fac = 1) with the HARD cover model
+    (noise + chord substitutions, the same generator bench.py uses for C2): 12 works x 3 + 12 singletons."""
+    from acoss_b200 import synth
+    labels, works, tids, hp = synth.make_tracks(12, 3, 12, 4801, 1600, 2400, **synth.HARD)
+    return dict(labels=labels, work_ids=works, track_ids=tids, hpcp=hp, fac=1)
+
+
+def gen_serra_L48(ns):
+    from acoss_b200 import synth
+    from oracle import oracle as O
+    ds = serra_L48_dataset()
+    n = len(ds["hpcp"])
+    i, j = np.triu_indices(n, 1)
+    pairs = np.stack([i, j], 1).astype(np.int32)
+    q, d, cells = O.serra09_pairs(ds["hpcp"], pairs, want_dmax=True, n_threads=os.cpu_count())
+    out = {"checksum": np.array([float(np.sum(h, dtype=np.float64)) for h in ds["hpcp"]]), "pairs": pairs,
+           "qmax": q, "dmax": d, "labels": np.array(ds["labels"])}
+    small = dict(ds)
+    small["hpcp"] = [h[:12] for h in ds["hpcp"]]      # the class only needs labels + lengths below
+    with tempfile.TemporaryDirectory() as tmp:
+        fdir = synth.write_dataset(os.path.join(tmp, "feat"), small, os.path.join(tmp, "ds.csv"))
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            s = quiet(ns.serra09.Serra09, os.path.join(tmp, "ds.csv"), fdir, shortname="gL", downsample_fac=1)
+            for k in range(n):
+                quiet(s.load_features, k)
+                s.all_feats[k] = ds["hpcp"][k]
+            D = np.zeros((n, n), np.float32)
+            D[pairs[:, 0], pairs[:, 1]] = q
+            D += D.T
+            s.Ds["main"][:, :] = D
+            out["serra_raw"] = D
+            quiet(s.normalize_by_length)
+            out["serra_norm"] = np.array(s.Ds["main"])
+            out["serra_eval"] = np.array([x for x in quiet(s.getEvalStatistics, "main")[:4]], np.float64)
+        finally:
+            os.chdir(cwd)
+    np.savez_compressed(os.path.join(GOLD, "serra09_L48.npz"), **out)
+    print("serra09_L48: MR/MRR/MDR/MAP", out["serra_eval"])
+
+
 def gen_percentile():
     from oracle import oracle as O
     rng = np.random.default_rng(5)
@@ -305,6 +444,12 @@ def main():
     from oracle import refload
     os.makedirs(GOLD, exist_ok=True)
     ns = refload.load()
+    only = sys.argv[1:]
+    if only:                      # python -m oracle.make_golden early_large simple_large ...
+        for name in only:
+            fn = globals()["gen_" + name]
+            fn() if name == "percentile" else fn(ns)
+        return
     gen_percentile()
     gen_sw(ns)
     gen_eval(ns)
@@ -312,6 +457,9 @@ def main():
     gen_serra(ns)
     gen_simple_ftm(ns)
     gen_early(ns)
+    gen_early_large(ns)
+    gen_simple_large(ns)
+    gen_serra_L48(ns)
 
 
 if __name__ == "__main__":

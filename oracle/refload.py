@@ -32,10 +32,28 @@ def available():
 
 
 class _DeepdishIO(object):
-    """deepdish.io stand-in: pickle-backed dict files with the same load/save API."""
+    """deepdish.io stand-in with the same load/save API.  Reads the npz container the synthetic generator writes
+    (acoss_b200.featio: '/'-joined keys, no pickle); files the reference classes write THEMSELVES through this stub
+    (their private caches in the test's temporary directory) are pickles."""
 
     @staticmethod
     def load(path):
+        with open(path, "rb") as f:
+            head = f.read(4)
+        if head == b"PK\x03\x04":
+            root = {}
+            with np.load(path, allow_pickle=False) as z:
+                for key in z.files:
+                    if key.startswith("__"):
+                        continue
+                    parts = key.split("/")
+                    d = root
+                    for q in parts[:-1]:
+                        d = d.setdefault(q, {})
+                    if parts[-1] != "__empty__":
+                        a = z[key]
+                        d[parts[-1]] = a.item() if a.ndim == 0 else a
+            return root
         with open(path, "rb") as f:
             return pickle.load(f)
 

@@ -252,6 +252,41 @@ def test_pairs_scores_long_tracks_sample(ctx, oracle):
     assert np.array_equal(q, oq) and np.array_equal(d, od)
 
 
+def test_pairs_multibatch_and_alloc_retry_vs_oracle(oracle):
+    """The multi-batch path of the pair pipeline (scratch-buffer reuse and regrowth across batches, per-batch DP
+    hand-out counters, kernel choice per batch on ragged lengths straddling 512 frames) and the halve-the-budget
+    retry after an allocation failure: scores bit-equal to the single-batch run and to the oracle."""
+    import acoss_b200
+    rng = np.random.default_rng(77)
+    lens = [int(x) for x in rng.integers(60, 500, size=8)] + [int(x) for x in rng.integers(520, 760, size=6)]
+    tracks = _tracks(rng, lens)
+    n = len(tracks)
+    pairs = np.array([(i, j) for i in range(n) for j in range(n) if i != j], np.int32)
+    pairs = pairs[rng.permutation(len(pairs))[:90]]
+    oq, od, _ = oracle.serra09_pairs(tracks, pairs, want_dmax=True, n_threads=8)
+    c = acoss_b200.Context(0)
+    try:
+        c.upload_tracks(tracks)
+        q1, d1 = c.serra09_pairs(pairs, want_dmax=True)
+        assert c.pair_stats()["n_batches"] == 1
+        c.set_option("crp_budget_bytes", 1 << 20)          # ~2-20 pairs per batch
+        q2, d2 = c.serra09_pairs(pairs, want_dmax=True)
+        st = c.pair_stats()
+        assert st["n_batches"] > 5, st
+        assert set(st["crp_kernels"]) >= {"gemm", "band"}, st       # both sides of the 512-frame switch ran
+        assert np.array_equal(q1, oq) and np.array_equal(d1, od)
+        assert np.array_equal(q2, oq) and np.array_equal(d2, od)
+        c.set_option("crp_budget_bytes", 64 << 20)
+        c.set_option("inject_alloc_failures", 2)            # two failed reservations -> budget quartered, call succeeds
+        q3, d3 = c.serra09_pairs(pairs, want_dmax=True)
+        assert c.pair_stats()["n_batches"] >= 2
+        assert np.array_equal(q3, oq) and np.array_equal(d3, od)
+        with pytest.raises(acoss_b200.AcossError):
+            c.set_option("no_such_option", 1)
+    finally:
+        c.close()
+
+
 def test_median_downsample_vs_oracle(ctx, oracle):
     rng = np.random.default_rng(41)
     raws = [rng.random((n, 12)).astype(np.float32) for n in (1, 39, 40, 41, 1600, 2399, 80)]
@@ -287,6 +322,42 @@ def test_serra09_class_matches_reference_golden(golden, workdir):
     assert np.array_equal(np.array(s.Ds["main"]), g["serra_norm"])
     MR, MRR, MDR, MAP, tops = s.getEvalStatistics("main")
     assert [MR, MRR, MDR, MAP] == g["serra_eval"].tolist()
+    s.cleanup_memmap()
+
+
+def test_serra09_L48_full_run_vs_golden(golden, workdir):
+    """A full Serra09 run at the L length regime (48 tracks, 1128 pairs, M, N ~ 1600-2400, the HARD cover model so
+    that MAP < 1): raw and normalised matrices bit-equal to the oracle's / the reference class's, eval tuple
+    identical (golden: oracle/make_golden.py gen_serra_L48)."""
+    import acoss_b200
+    from acoss_b200 import synth
+    from oracle.make_golden import serra_L48_dataset
+    g = golden("serra09_L48.npz")
+    ds = serra_L48_dataset()
+    assert np.array_equal([float(np.sum(h, dtype=np.float64)) for h in ds["hpcp"]], g["checksum"])
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"))
+    s = acoss_b200.Serra09(str(workdir / "ds.csv"), fdir, shortname="gL", downsample_fac=1)
+    s.all_pairwise(1, symmetric=True)
+    assert "gemm" in s.last_stats["crp_kernels"] or "split" in s.last_stats["crp_kernels"]
+    assert np.array_equal(np.array(s.Ds["main"]), g["serra_raw"])
+    s.normalize_by_length()
+    assert np.array_equal(np.array(s.Ds["main"]), g["serra_norm"])
+    MR, MRR, MDR, MAP, tops = s.getEvalStatistics("main")
+    assert [MR, MRR, MDR, MAP] == g["serra_eval"].tolist()
+    assert MAP < 0.95 and MR > 1.0          # the check is not vacuous: retrieval is not saturated
+    # resume path: all_pairwise(precomputed=True) re-loads `<prefix>_Ds.h5` (algorithm_template.py:163-166)
+    s2 = acoss_b200.Serra09(str(workdir / "ds.csv"), fdir, shortname="gL", downsample_fac=1)
+    assert not np.any(np.array(s2.Ds["main"]))              # the constructor truncates the memmap (SURVEY Q13)
+    s2.all_pairwise(1, symmetric=True, precomputed=True)
+    assert np.array_equal(np.array(s2.Ds["main"]), g["serra_raw"])
+    assert sum(len(c) for c in s2.cliques.values()) == s2.N
+    s2.Ds["main"] = np.array(s2.Ds["main"])
+    s2.preload()
+    s2.normalize_by_length()
+    assert [float(x) for x in s2.getEvalStatistics("main")[:4]] == g["serra_eval"].tolist()
+    ctx2 = s.context()
+    q, d = ctx2.serra09_pairs(g["pairs"][:64], want_dmax=True)
+    assert np.array_equal(d, g["dmax"][:64]) and np.array_equal(q, g["qmax"][:64])
     s.cleanup_memmap()
 
 
@@ -499,6 +570,17 @@ def test_simple_pairs_vs_reference_golden(ctx, golden):
     np.testing.assert_allclose(D, g["simple_D"], rtol=1e-6, atol=1e-9)
 
 
+def test_simple_pairs_large_vs_reference_golden(ctx, golden):
+    """BASELINE C5 size: 8 tracks of 170-246 columns, all 56 ordered pairs against the reference's simple_sim run
+    verbatim (float64; tolerance as above)."""
+    g = golden("simple_large.npz")
+    feats = [g["feat%d" % i] for i in range(int(g["n"]))]
+    assert min(f.shape[1] for f in feats) >= 150 and max(f.shape[1] for f in feats) <= 250
+    ctx.simple_upload(feats)
+    got = ctx.simple_pairs(g["pairs"])
+    np.testing.assert_allclose(got, g["scores"], rtol=1e-9, atol=1e-11)
+
+
 def test_simple_preprocess_vs_reference_golden(ctx, golden):
     """Device WIN/SKIP mean + Hann smoothing + column normalisation vs the reference's Simple.load_features run
     verbatim (simple_silva.py:34-43, 56-66; golden made by oracle/make_golden.py).  float64: tolerance 1e-12 (the
@@ -611,6 +693,53 @@ def test_earlyfusion_pair_matrices_vs_reference_golden(ctx, golden):
         mism = int((bn != g["bin%d" % k]).sum())
         assert mism == 0, "binary matrices differ in %d cells" % mism
         assert sc.astype(np.float32).tolist() == [g["D_" + s][a, b] for s in ("mfccs", "ssms", "chromas", "early")]
+
+
+def test_earlyfusion_large_vs_reference_golden(ctx, golden):
+    """BASELINE C3 size (367-587 blocks, d = 1000 / 1225 / 480, k = 37-59 neighbours): CSM rows, the four binary
+    matrices and the four scores of four pairs against the reference's functions run verbatim.
+
+    The reference's CSMs come out of numpy's BLAS sgemm; no other implementation reproduces its summation order, so
+    a cell whose value is within float32-GEMM rounding of its row's k-th neighbour can legitimately fall on either
+    side.  The golden stores every row's k-th and (k+1)-th smallest value (float64 sort of the reference's matrix):
+    a differing cell is accepted only in a row whose gap is below the rounding tolerance, and then the scores are
+    not compared for that matrix.  Everything else must be identical."""
+    from oracle.make_golden import early_large_dataset
+    g = golden("earlyfusion_large.npz")
+    ds = early_large_dataset()
+    bf = ds["block_feats"]
+    assert np.array_equal([float(np.sum(f["mfccs"], dtype=np.float64) + np.sum(f["ssms"], dtype=np.float64) +
+                                 np.sum(f["chromas"], dtype=np.float64)) for f in bf], g["checksum"])
+    ctx.earlyfusion_upload(bf)
+    n_diff_total = 0
+    for k, (a, b) in enumerate(g["mat_pairs"]):
+        M, N, kk = (int(x) for x in g["shape%d" % k])
+        csm, bn, sc = ctx.earlyfusion_pair_matrices(int(a), int(b), kappa=0.1, K=10)
+        assert csm.shape == (4, M, N)
+        np.testing.assert_allclose(csm[:3, ::16], g["csm_rows%d" % k][:3], rtol=2e-5, atol=2e-6)
+        np.testing.assert_allclose(csm[3, ::16], g["csm_rows%d" % k][3], rtol=2e-4, atol=1e-6)
+        ref_bin = np.unpackbits(g["binpk%d" % k], axis=2)[:, :, :N]
+        assert np.array_equal(bn.sum(2), ref_bin.sum(2))                  # exactly k ones per row
+        for t in range(4):
+            rows = np.nonzero((bn[t] != ref_bin[t]).any(1))[0]
+            n_diff_total += len(rows)
+            kth = g["kth%d" % k][t]
+            for r in rows:          # only a near-tie at the k-th neighbour may differ
+                gap = kth[r, 1] - kth[r, 0]
+                tol = (2e-5 if t < 3 else 2e-4) * max(abs(kth[r, 1]), 1e-3)
+                assert gap <= tol, "pair %d matrix %d row %d differs with a gap of %g" % (k, t, r, gap)
+                assert int((bn[t, r] != ref_bin[t, r]).sum()) == 2
+            if len(rows) == 0:
+                assert np.float32(sc[t]) == np.float32(g["scores%d" % k][t]), (k, t, sc[t], g["scores%d" % k][t])
+                assert np.float32(sc[t]) == g[("D_mfccs", "D_ssms", "D_chromas", "D_early")[t]][a, b]
+    # whole-batch call (the production path: batched kernels instead of the test hook)
+    prs = np.array([(int(a), int(b)) for a, b in g["mat_pairs"]], np.int32)
+    got = ctx.earlyfusion_pairs(prs, kappa=0.1, K=10)
+    for k in range(len(prs)):
+        _, _, sc = ctx.earlyfusion_pair_matrices(int(prs[k, 0]), int(prs[k, 1]), kappa=0.1, K=10)
+        assert got[k].tolist() == sc.tolist()
+    print("earlyfusion_large: rows with a near-tie difference: %d" % n_diff_total)
+    assert n_diff_total <= 8
 
 
 def test_earlyfusion_class_matches_reference_golden(golden, workdir):

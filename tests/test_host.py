@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_header():
     from acoss_b200 import _lib
     assert ctypes.sizeof(_lib.CrpParams) == 28
-    assert ctypes.sizeof(_lib.PairStats) == 4 * 8 + 8 * 8
+    assert ctypes.sizeof(_lib.PairStats) == 4 * 8 + 10 * 8
 
 
 def test_no_cpu_fallback_without_gpu():
