@@ -16,6 +16,7 @@
 #include "kernels_crp.cuh"
 #include "kernels_crp_band.cuh"
 #include "kernels_crp_gemm.cuh"
+#include "kernels_crp_split.cuh"
 #include "kernels_dp.cuh"
 #include "kernels_eval.cuh"
 #include "kernels_snf.cuh"
@@ -56,6 +57,12 @@ struct acoss_ctx {
     DevBuf d_dp_order;                // per batch: DP hand-out order (largest pair first) + two launch counters
     DevBuf d_smpop;                   // per-track sample operands of the tensor-core CRP kernel (m = 9, tau = 1 only)
     bool have_smpop = false;
+    // phase-split CRP pipeline: per-track side-B operand planes + norm planes in their shared-memory layout, byte offsets
+    // (2 per track), max of the self-dot table per rotation; per-chunk scratch (pivots, counts, lists), column edges
+    DevBuf d_opb, d_opn, d_op_off, d_sdmax, d_piv, d_cnt4, d_lcnt, d_slists, d_edges, d_fb;
+    bool have_split = false;
+    int64_t split_launches = 0;
+    int auto_split = 0;               // crp_mode 0 picks the phase-split pipeline (acoss_ctx_set_option "auto_split")
     // SiMPle feature store (frame-major float64) + per-track chroma profiles
     int sp_tracks = 0;
     std::vector<int64_t> sp_offs;
@@ -131,6 +138,8 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
                       &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_dp_order, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
                       &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters, &ctx->d_lists,
+                      &ctx->d_opb, &ctx->d_opn, &ctx->d_op_off, &ctx->d_sdmax, &ctx->d_piv, &ctx->d_cnt4, &ctx->d_lcnt, &ctx->d_slists,
+                      &ctx->d_edges, &ctx->d_fb,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
                       &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin};
@@ -149,6 +158,7 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
         ctx->crp_budget = (size_t)value;
         return ACOSS_OK;
     }
+    if (k == "auto_split") { ctx->auto_split = value != 0; return ACOSS_OK; }
     if (k == "inject_alloc_failures") {
         ctx->inject_alloc_failures = (int)std::max<int64_t>(0, value);
         return ACOSS_OK;
@@ -258,6 +268,41 @@ extern "C" int acoss_upload_tracks(acoss_ctx* ctx, const float* frames_host, con
                                                            ctx->d_sd_off.as<int64_t>(), ctx->d_selfdot.as<float>(), ctx->d_smpop.as<unsigned char>());
         CK_LAUNCH();
         ctx->have_smpop = true;
+    }
+    // operand store of the phase-split CRP pipeline (kernels_crp_split.cuh): 288 B per frame, built when it fits 8 GiB
+    ctx->have_split = false;
+    if (ctx->have_smpop) {
+        std::vector<int64_t> op_off(2 * (size_t)n_tracks);
+        size_t pl_bytes = 0, nr_bytes = 0;
+        int max_tiles = 0;
+        for (int t = 0; t < n_tracks; ++t) {
+            const int nt = sp_tiles(ctx->h_emb[t]);
+            op_off[2 * t] = (int64_t)pl_bytes; op_off[2 * t + 1] = (int64_t)nr_bytes;
+            if (nt > 0) { pl_bytes += (size_t)6 * (GM_TN * nt + 8) * 16; nr_bytes += (size_t)ACOSS_NBINS * GM_TN * nt * 16; }
+            max_tiles = std::max(max_tiles, nt);
+        }
+        if (max_tiles > 0 && pl_bytes + nr_bytes <= ((size_t)8 << 30)) {
+            RESERVE(ctx->d_opb, pl_bytes + 64);
+            RESERVE(ctx->d_opn, nr_bytes + 64);
+            RESERVE(ctx->d_op_off, sizeof(int64_t) * op_off.size());
+            RESERVE(ctx->d_sdmax, sizeof(float) * ACOSS_NBINS * n_tracks);
+            CK(cudaMemcpyAsync(ctx->d_op_off.p, op_off.data(), sizeof(int64_t) * op_off.size(), cudaMemcpyHostToDevice, st));
+            const int P = GM_TN * max_tiles + 8, W = GM_TN * max_tiles;
+            for (int t0 = 0; t0 < n_tracks; t0 += 65535) {
+                const int ny = std::min(65535, n_tracks - t0);
+                sp_planes_kernel<<<dim3((P + 127) / 128, ny), 128, 0, st>>>(ctx->d_frames.as<float>(), ctx->d_offs.as<int64_t>(), ctx->d_emb.as<int32_t>(),
+                                                                            ctx->d_op_off.as<int64_t>(), ctx->d_opb.as<unsigned char>(), t0);
+                CK_LAUNCH();
+                sp_norms_kernel<<<dim3((ACOSS_NBINS * W + 127) / 128, ny), 128, 0, st>>>(ctx->d_emb.as<int32_t>(), ctx->d_sd_off.as<int64_t>(),
+                                                                                         ctx->d_selfdot.as<float>(), ctx->d_op_off.as<int64_t>(),
+                                                                                         ctx->d_opn.as<unsigned char>(), t0);
+                CK_LAUNCH();
+            }
+            sp_sdmax_kernel<<<n_tracks, 256, 0, st>>>(ctx->d_emb.as<int32_t>(), ctx->d_sd_off.as<int64_t>(), ctx->d_selfdot.as<float>(),
+                                                      ctx->d_sdmax.as<float>());
+            CK_LAUNCH();
+            ctx->have_split = true;
+        }
     }
     CK(cudaStreamSynchronize(st));   // host buffers may be released by the caller
     return ACOSS_OK;

@@ -22,6 +22,7 @@ struct PairDesc {
     int64_t thr_q_off;       // float offset of thr_q[M] / thr_r[N] in the batch threshold buffer
     int64_t thr_r_off;
     int64_t out_idx;         // index of this pair in the caller's output arrays
+    int64_t edge_off;        // float offset of this pair's column band edges (phase-split CRP pipeline, pass 2)
 };
 
 // exact fp32 arithmetic helpers: the oracle's op order, never contracted to FMA

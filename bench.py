@@ -38,7 +38,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--shape", default="datacos1000", help="synth.SHAPES key (default: 1000 tracks)")
+    ap.add_argument("--config", default="C2", choices=["C1", "C2", "C3", "C4", "C5"],
+                    help="BASELINE.json config (SURVEY 8(d)): C1 Serra09 160 tracks, C2 Serra09 1000 tracks (default, the driver line), "
+                         "C3 EarlyFusionTralie 1000 tracks, C4 LateFusionChen 1000 tracks, C5 SiMPle + FTM2D 15 000 tracks")
+    ap.add_argument("--cpu-full", action="store_true", help="cpu_baseline over the WHOLE pair grid (C1: 12 720 pairs) instead of a bounded sample")
+    ap.add_argument("--pairs-per-step", type=int, default=0, help="C3 / C5: pairs of the grid processed per step (0 = config default)")
+    ap.add_argument("--shape", default=None, help="synth.SHAPES key (default: by --config)")
     ap.add_argument("--regime", default="L", choices=["S", "R", "L"],
                     help="track-length regime (SURVEY 8(d)); L = n~U[1600,2400] frames at the DP stage")
     ap.add_argument("--scale", type=float, default=1.0, help="DEBUG ONLY: shrink the number of works")
@@ -48,7 +53,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true", help="DEBUG ONLY: skip the end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true", help="DEBUG ONLY: skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work of the cpu_baseline sample")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.shape is None:
+        args.shape = {"C1": "covers80", "C5": "datacos15000"}.get(args.config, "datacos1000")
+    return args
 
 
 def peaks():
@@ -127,27 +135,48 @@ class ClockSampler(object):
         return out
 
 
-def cpu_baseline_sample(tracks, all_pairs, target_seconds, seed=0):
+def cpu_baseline_sample(tracks, all_pairs, target_seconds, seed=0, full=False, want_dmax=False):
     """The oracle port (single-threaded per pair like essentia) fanned out over all host threads
-    on a bounded random sample of the workload's pairs."""
+    on a bounded random sample of the workload's pairs (or, with full=True, on the whole grid)."""
     from oracle import oracle as O
     O.build()
     cores = os.cpu_count() or 1
     rng = np.random.default_rng(seed)
-    probe = all_pairs[rng.choice(len(all_pairs), size=min(len(all_pairs), cores), replace=False)]
+    if full:
+        n, sample = len(all_pairs), all_pairs
+    else:
+        probe = all_pairs[rng.choice(len(all_pairs), size=min(len(all_pairs), cores), replace=False)]
+        t0 = time.perf_counter()
+        O.serra09_pairs(tracks, probe, n_threads=cores, want_dmax=want_dmax)
+        t_probe = time.perf_counter() - t0
+        per_round = max(t_probe, 1e-4)                      # seconds per `cores` pairs
+        n = int(min(len(all_pairs), max(cores, cores * round(target_seconds / per_round))))
+        sample = all_pairs[rng.choice(len(all_pairs), size=n, replace=False)]
     t0 = time.perf_counter()
-    O.serra09_pairs(tracks, probe, n_threads=cores)
-    t_probe = time.perf_counter() - t0
-    per_round = max(t_probe, 1e-4)                      # seconds per `cores` pairs
-    n = int(min(len(all_pairs), max(cores, cores * round(target_seconds / per_round))))
-    sample = all_pairs[rng.choice(len(all_pairs), size=n, replace=False)]
-    t0 = time.perf_counter()
-    q, _, cells = O.serra09_pairs(tracks, sample, n_threads=cores)
+    q, _, cells = O.serra09_pairs(tracks, sample, n_threads=cores, want_dmax=want_dmax)
     dt = time.perf_counter() - t0
     return dict(value=n / dt, unit=UNIT, cores=cores, kind="port",
-                sample="%d random pairs of the %d-pair grid (%.1f s, %d threads, oracle/acoss_oracle.c -O2 "
-                       "-ffp-contract=off); %.4f GCUPS" % (n, len(all_pairs), dt, cores, cells / dt / 1e9),
+                sample="%s of the %d-pair grid (%.1f s, %d threads, oracle/acoss_oracle.c -O2 "
+                       "-ffp-contract=off%s); %.4f GCUPS" % ("ALL pairs" if full else "%d random pairs" % n, len(all_pairs), dt, cores,
+                                                              ", Qmax + Dmax" if want_dmax else "", cells / dt / 1e9),
                 seconds=dt, gcups=cells / dt / 1e9)
+
+
+def add_cpu_snf(cpu, n_tracks, n_pairs):
+    """C4: the N x N similarity network fusion of two matrices (oracle/ports.py, numpy) timed once and added to the
+    extrapolated whole-grid CPU time."""
+    from oracle import ports as P
+    rng = np.random.default_rng(4)
+    A = rng.random((n_tracks, n_tracks)).astype(np.float32) + 0.1
+    B = rng.random((n_tracks, n_tracks)).astype(np.float32) + 0.1
+    t0 = time.perf_counter()
+    P.snf([A, B], K=20, niters=20, reg_diag=1)
+    t_snf = time.perf_counter() - t0
+    total = n_pairs / cpu["value"] + t_snf
+    cpu = dict(cpu)
+    cpu["sample"] += "; + SNF of two %d x %d matrices (numpy port) %.2f s; value = pairs / (extrapolated pair time + SNF)" % (n_tracks, n_tracks, t_snf)
+    cpu["value"] = n_pairs / total
+    return cpu
 
 
 def run_reference(args, rank, world):
@@ -164,13 +193,13 @@ def run_reference(args, rank, world):
     per_step = max(2.0, min(30.0, 150.0 / max(1, args.steps + args.warmup)))
     vals, last = [], None
     for s in range(args.warmup + args.steps):
-        last = cpu_baseline_sample(tracks, all_pairs, per_step, seed=s)
+        last = cpu_baseline_sample(tracks, all_pairs, per_step, seed=s, want_dmax=args.config == "C4")
         if s >= args.warmup:
             vals.append(last)
     tot_pairs = sum(v["value"] * v["seconds"] for v in vals)
     tot_s = sum(v["seconds"] for v in vals)
     value = tot_pairs / tot_s
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+    line = {"impl": "reference", "metric": "latefusionchen_allpairs_comparisons_per_sec" if args.config == "C4" else METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / max(1, len(vals)), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, n, len(all_pairs)),
@@ -181,13 +210,16 @@ def run_reference(args, rank, world):
 
 
 def workload_config(args, n_tracks, n_pairs):
-    return {"workload": "C2-%s: Serra09 (OTI+CRP+Qmax) all-pairs, %d synthetic Da-TACOS-benchmark-shape HPCP tracks "
+    return {"workload": "%s-%s: %s all-pairs, %d synthetic %s HPCP tracks "
                         "(%s), %d pairs, m=9 tau=1 kappa=0.095" % (
-                            args.regime, n_tracks,
+                            args.config, args.regime,
+                            "LateFusionChen (OTI+CRP+Qmax+Dmax, distance normalisation, SNF K=20 x 20 iterations)" if args.config == "C4"
+                            else "Serra09 (OTI+CRP+Qmax)", n_tracks,
+                            "covers80-shape" if args.shape == "covers80" else "Da-TACOS-benchmark-shape",
                             {"L": "n~U[1600,2400] frames at the DP stage, downsample_fac=1",
                              "R": "raw T~U[15000,25000], downsample_fac=40",
                              "S": "raw T~U[1600,2400], downsample_fac=40"}[args.regime], n_pairs),
-            "shape": args.shape, "regime": args.regime, "tracks": n_tracks, "pairs": n_pairs,
+            "shape": args.shape, "regime": args.regime, "tracks": n_tracks, "pairs": n_pairs, "cover_model": "easy" if args.easy else "hard",
             "l2_policy": "inputs larger than L2: every step re-streams the CRP working set (GBs) through HBM",
             "debug_scale": args.scale}
 
@@ -234,12 +266,17 @@ def run_ours(args, rank, world, local_rank):
     ctx.upload_tracks(frames=frames, offsets=offs)
     stream = torch.cuda.ExternalStream(ctx.lib.acoss_ctx_stream(ctx.h), device=dev)
     cap = (P + world - 1) // world + 1
+    chen = args.config == "C4"
     d_scores_local = torch.zeros(cap, dtype=torch.float32, device=dev)
+    d_dmax_local = torch.zeros(cap, dtype=torch.float32, device=dev) if chen else None
     d_idx_local = torch.full((cap,), -1, dtype=torch.int64, device=dev)
     d_idx_local[:len(mine)] = torch.from_numpy(mine).to(dev)
     d_pairs_all = torch.from_numpy(all_pairs).to(dev)
     d_scores_all = torch.zeros(P, dtype=torch.float32, device=dev)
     d_D = torch.zeros((n, n), dtype=torch.float32, device=dev)
+    d_D2 = torch.zeros((n, n), dtype=torch.float32, device=dev) if chen else None
+    d_Df = torch.zeros((n, n), dtype=torch.float32, device=dev) if chen else None
+    d_dmax_all = torch.zeros(P, dtype=torch.float32, device=dev) if chen else None
     d_len = torch.from_numpy(lengths_np).to(dev)
     if world > 1:
         g_scores = [torch.empty_like(d_scores_local) for _ in range(world)]
@@ -251,23 +288,41 @@ def run_ours(args, rank, world, local_rank):
     result = {}
 
     def step_resident():
-        ctx.serra09_pairs_dev(my_pairs, prm, d_scores_local.data_ptr(), 0)     # syncs its stream at the end
+        ctx.serra09_pairs_dev(my_pairs, prm, d_scores_local.data_ptr(), d_dmax_local.data_ptr() if chen else 0)     # syncs its stream at the end
         st = ctx.pair_stats()
         launches[0] += st["n_launches"]
         if world > 1:
-            dist.all_gather(g_scores, d_scores_local)
-            for gi, gs in zip(g_idx, g_scores):
-                ok = gi >= 0
-                d_scores_all[gi[ok]] = gs[ok]
-            launches[0] += 2 * world
+            for loc, dst in ((d_scores_local, d_scores_all),) + (((d_dmax_local, d_dmax_all),) if chen else ()):
+                dist.all_gather(g_scores, loc)
+                for gi, gs in zip(g_idx, g_scores):
+                    ok = gi >= 0
+                    dst[gi[ok]] = gs[ok]
+                launches[0] += 2 * world
             torch.cuda.synchronize(dev)
-            src = d_scores_all
+            src, src_d = d_scores_all, d_dmax_all
         else:
-            src = d_scores_local      # `mine` is the identity permutation for world == 1
+            src, src_d = d_scores_local, d_dmax_local      # `mine` is the identity permutation for world == 1
         ctx.scores_to_matrix_dev(d_pairs_all.data_ptr(), src.data_ptr(), P, n, True, d_D.data_ptr())
-        ctx.normalize_by_length_dev(d_D.data_ptr(), n, d_len.data_ptr(), 0)
-        out, ranks = ctx.eval_statistics(d_D.data_ptr(), n, order, csize, cstart, tops)
-        launches[0] += 3
+        ctx.normalize_by_length_dev(d_D.data_ptr(), n, d_len.data_ptr(), 1 if chen else 0)
+        launches[0] += 2
+        if chen:
+            # LateFusionChen (latefusion_chen.py:75-91): both matrices become distances sqrt(len_j) / score, SNF (K = 20, 20
+            # iterations) of the two, evaluation of -qmax-distance, -dmax-distance and the fused matrix
+            ctx.scores_to_matrix_dev(d_pairs_all.data_ptr(), src_d.data_ptr(), P, n, True, d_D2.data_ptr())
+            ctx.normalize_by_length_dev(d_D2.data_ptr(), n, d_len.data_ptr(), 1)
+            ctx.synchronize()
+            _, fused = ctx.snf([d_D.cpu().numpy(), d_D2.cpu().numpy()], K=20, niters=20, reg_diag=1, want_Ws=False)
+            d_Df.copy_(torch.from_numpy(fused.astype(np.float32)))
+            torch.cuda.synchronize(dev)
+            result["eval_dmax"], _ = ctx.eval_statistics((-d_D2).data_ptr(), n, order, csize, cstart, tops)
+            result["eval_late"], _ = ctx.eval_statistics(d_Df.data_ptr(), n, order, csize, cstart, tops)
+            d_Dn = -d_D
+            torch.cuda.synchronize(dev)
+            out, ranks = ctx.eval_statistics(d_Dn.data_ptr(), n, order, csize, cstart, tops)
+            launches[0] += 2 + 8 + 3
+        else:
+            out, ranks = ctx.eval_statistics(d_D.data_ptr(), n, order, csize, cstart, tops)
+            launches[0] += 1
         result["eval"] = out
         return st
 
@@ -314,9 +369,10 @@ def run_ours(args, rank, world, local_rank):
     ms_tot = float(np.mean([s["ms_total"] for s in stats_acc]))
     st = stats_acc[-1]
     n_dp_launch = max(1, st["n_dp_launches"])
-    dp_bytes = st["crp_cells"] + 4 * len(mine)              # ALGORITHMIC: M*N CRP bytes read once + 4 B score per pair
+    n_dp_kinds = 2 if chen else 1
+    dp_bytes = n_dp_kinds * (st["crp_cells"] + 4 * len(mine))              # ALGORITHMIC: M*N CRP bytes read once + 4 B score per pair
     dp_gbs = dp_bytes / (ms_dp * 1e-3) / 1e9
-    dp_streamed = st["crp_bytes"] + 4 * len(mine)           # what the kernel streams: M*pitch (row pitch padded to the DP chunk)
+    dp_streamed = n_dp_kinds * (st["crp_bytes"] + 4 * len(mine))           # what the kernel streams: M*pitch (row pitch padded to the DP chunk)
     gcups = st["dp_cells"] / (ms_dp * 1e-3) / 1e9
     crp_flop = 2.0 * 108 * st["crp_cells"] + 5.0 * st["crp_cells"]
     crp_tflops = crp_flop / (ms_crp * 1e-3) / 1e12
@@ -372,16 +428,19 @@ def run_ours(args, rank, world, local_rank):
         return
     cpu = None
     if world == 1 and not args.no_cpu:
-        cpu = cpu_baseline_sample(tracks, all_pairs, args.cpu_seconds)
+        cpu = cpu_baseline_sample(tracks, all_pairs, args.cpu_seconds, full=args.cpu_full, want_dmax=chen)
+        if chen:
+            cpu = add_cpu_snf(cpu, n, len(all_pairs))
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
     ev = result["eval"]
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+    line = {"metric": "latefusionchen_allpairs_comparisons_per_sec" if chen else METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(args, n, P),
             "dp_gcups": gcups * world if world > 1 else gcups, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": roofline, "roofline_kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(n_launch), "clocks": clocks,
             "eval": {"MR": ev[0], "MRR": ev[1], "MDR": ev[2], "MAP": ev[3], "Top-1": ev[4]},
+            "eval_late_fusion": ({"MAP_dmax": result["eval_dmax"][3], "MAP_late": result["eval_late"][3]} if chen else None),
             "parity_sample": parity,
             "batches_per_step": int(st["n_batches"]), "crp_mode": args.crp_mode,
             "debug_counters": ctx.debug_counters(),
@@ -454,13 +513,413 @@ def run_e2e(args, ctx, ds, tracks, all_pairs, mine, world, rank, local_rank):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+# =====================================================================================================================
+# C3 (EarlyFusionTralie) and C5 (SiMPle + FTM2D): the other BASELINE.json configs, same JSON schema
+# =====================================================================================================================
+def _clique_layout(labels):
+    cl = {}
+    for k, l in enumerate(labels):
+        cl.setdefault(l, []).append(k)
+    cliques = list(cl.values())
+    Ks = np.array([len(c) for c in cliques])
+    o = np.argsort(-Ks)
+    cliques = [cliques[k] for k in o]
+    Ks = Ks[o]
+    order = np.concatenate(cliques).astype(np.int32)
+    csize = np.repeat(Ks, Ks).astype(np.int32)
+    cstart = np.repeat(np.concatenate([[0], np.cumsum(Ks)[:-1]]), Ks).astype(np.int32)
+    return order, csize, cstart
+
+
+def _c3_workload(args):
+    from acoss_b200 import synth
+    nw, pw, ns = synth.SHAPES["datacos1000"]
+    if args.scale != 1.0:
+        nw, ns = max(1, int(round(nw * args.scale))), int(round(ns * args.scale))
+    return synth.make_block_features(nw, pw, ns, 1001, 300, 600, noise=2.0)
+
+
+def _c5_workload(args):
+    """SiMPle features (12, L) float64 with L ~ U[150, 250], columns L2-normalised, covers share a warped latent; FTM2D
+    shingles (900,) unit vectors."""
+    from acoss_b200 import synth
+    nw, pw, ns = synth.SHAPES["datacos15000"]
+    if args.scale != 1.0:
+        nw, ns = max(1, int(round(nw * args.scale))), int(round(ns * args.scale))
+    rng = np.random.default_rng(15000)
+    feats, shingles, labels = [], [], []
+    for w in range(nw + ns):
+        lat = np.abs(np.cumsum(rng.standard_normal((12, 270)), 1)) + 0.05
+        sh = rng.random(900)
+        for c in range(pw if w < nw else 1):
+            L = int(rng.integers(150, 251))
+            s0 = int(rng.integers(0, 270 - L + 1))
+            f = np.roll(lat[:, s0:s0 + L], int(rng.integers(0, 12)), axis=0) + 0.3 * rng.random((12, L))
+            feats.append(f / np.sqrt(np.sum(f * f, 0, keepdims=True)))
+            v = sh + 0.2 * rng.random(900)
+            shingles.append(v / np.sqrt(np.sum(v * v)))
+            labels.append("W_%d" % w)
+    return feats, np.stack(shingles), labels
+
+
+def _pool_rate(fn, items, cores, target_seconds):
+    """items / second of fn over a fork pool with `cores` workers on a bounded prefix of `items` (about target_seconds)."""
+    import multiprocessing as mp
+    t0 = time.perf_counter()
+    for it in items[:2]:
+        fn(it)
+    per = max((time.perf_counter() - t0) / 2, 1e-5)
+    n = int(min(len(items), max(cores, cores * target_seconds / per)))
+    with mp.get_context("fork").Pool(cores, initializer=_one_blas_thread) as pool:
+        pool.map(fn, items[:cores], chunksize=1)          # start-up outside the timed region
+        t0 = time.perf_counter()
+        pool.map(fn, items[:n], chunksize=max(1, n // (8 * cores)))
+        dt = time.perf_counter() - t0
+    return n / dt, n, dt
+
+
+_POOL_STATE = {}
+
+
+def _one_blas_thread():
+    """one BLAS thread per worker process: `cores` processes x `cores` BLAS threads would oversubscribe the host"""
+    try:
+        from threadpoolctl import threadpool_limits
+        _POOL_STATE["_limit"] = threadpool_limits(1)
+    except Exception:
+        pass
+
+
+def _c3_cpu_one(pr):
+    from oracle import ports as P
+    bf = _POOL_STATE["bf"]
+    return P.early_pair(bf[pr[0]], bf[pr[1]], 0.1, 10)[3]
+
+
+def _c5_cpu_one(pr):
+    from oracle import ports as P
+    f = _POOL_STATE["feats"]
+    return P.simple_pair(f[pr[0]], f[pr[1]])
+
+
+def _finish_line(args, world, metric, unit, value, ms_per_step, workload, roofline, kernels, cpu, e2e, launches, clocks, dtype, extra):
+    line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": dtype,
+            "data": "synthetic", "config": workload, "roofline": roofline, "roofline_kernels": kernels, "cpu_baseline": cpu,
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+    line.update(extra)
+    print(json.dumps(line))
+
+
+def run_c3(args, rank, world, local_rank):
+    """EarlyFusionTralie on 1000 synthetic tracks of 300-600 blocks (mfccs 1000-d, ssms 1225-d, chromas 480-d): per pair 3
+    CSMs, 4 kNN binarisations, WCSM early fusion, 4 constrained Smith-Waterman; then the two N x N similarity network fusions
+    and the evaluation of all six matrices.  A step = `pairs_per_step` pairs of the grid (default: the whole grid)."""
+    import torch
+    import torch.distributed as dist
+    import acoss_b200
+    from acoss_b200.algorithm_template import shard_pairs
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    ctx = acoss_b200.Context(local_rank)
+    ds = _c3_workload(args)
+    bf = ds["block_feats"]
+    n = len(bf)
+    nb = np.array([f["mfccs"].shape[0] for f in bf], np.int64)
+    i, j = np.triu_indices(n, 1)
+    all_pairs = np.stack([i, j], 1).astype(np.int32)
+    if args.pairs_per_step and args.pairs_per_step < len(all_pairs):
+        all_pairs = all_pairs[np.sort(np.random.default_rng(3).choice(len(all_pairs), args.pairs_per_step, replace=False))]
+    P = len(all_pairs)
+    mine = shard_pairs(all_pairs, nb[all_pairs[:, 0]] * nb[all_pairs[:, 1]], rank, world)
+    my_pairs = np.ascontiguousarray(all_pairs[mine])
+    order, csize, cstart = _clique_layout(ds["labels"])
+    tops = np.array([1, 10, 100, 1000], np.int32)
+    ctx.earlyfusion_upload(bf)
+    h2d_feat = sum(f[k].nbytes for f in bf for k in ("mfccs", "ssms", "chromas", "chroma_med"))
+    stream = torch.cuda.ExternalStream(ctx.lib.acoss_ctx_stream(ctx.h), device=dev)
+    res = {}
+
+    def nxn(scores_local):
+        """(4, P) scores of all ranks -> four N x N matrices, the two late fusions, six evaluations."""
+        full = np.zeros((4, P), np.float64)
+        full[:, mine] = scores_local.T
+        if world > 1:
+            t = torch.from_numpy(full).to(dev)
+            dist.all_reduce(t)
+            full = t.cpu().numpy()
+        Ds = {}
+        for k, s_ in enumerate(("mfccs", "ssms", "chromas", "early")):
+            D = np.zeros((n, n), np.float32)
+            D[all_pairs[:, 0], all_pairs[:, 1]] = full[k]
+            Ds[s_] = D + D.T
+        Ds["late"] = ctx.snf([1.0 / (1.0 + Ds[s_]) for s_ in ("chromas", "ssms", "mfccs")], K=20, niters=20, reg_diag=1, want_Ws=False)[1]
+        Ds["early+late"] = ctx.snf([1.0 / (1.0 + Ds[s_]) for s_ in ("chromas", "ssms", "mfccs", "early")], K=20, niters=20, reg_diag=1, want_Ws=False)[1]
+        ev = {}
+        for s_, D in Ds.items():
+            Dd = torch.from_numpy(np.ascontiguousarray(D, np.float32)).to(dev)
+            torch.cuda.synchronize(dev)
+            ev[s_] = ctx.eval_statistics(Dd.data_ptr(), n, order, csize, cstart, tops)[0]
+        return ev
+
+    def step():
+        sc = ctx.earlyfusion_pairs(my_pairs, kappa=0.1, K=10)
+        res["stats"] = ctx.earlyfusion_stats()
+        res["eval"] = nxn(sc)
+        res["scores"] = sc
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        ctx.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    t0 = time.perf_counter()
+    acc = []
+    for _ in range(args.steps):
+        step()
+        acc.append(res["stats"])
+    e1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    tt = torch.tensor([max(e0.elapsed_time(e1), wall * 1e3)], dtype=torch.float64, device=dev)      # the call copies host buffers: wall bounds it
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_per_step = float(tt[0]) / args.steps
+    value = P / (ms_per_step * 1e-3)
+    # e2e: the class-level call with host features every step (upload inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        times = []
+        for it in range(2):
+            barrier()
+            t0 = time.perf_counter()
+            ctx.earlyfusion_upload(bf)
+            sc = ctx.earlyfusion_pairs(my_pairs, kappa=0.1, K=10)
+            ev = nxn(sc)
+            barrier()
+            if it:
+                times.append(time.perf_counter() - t0)
+        tt = torch.tensor([float(np.mean(times))], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e = {"value": P / float(tt[0]), "unit": UNIT, "h2d_bytes_per_step": int(h2d_feat + my_pairs.nbytes + 7 * 8 * n * n),
+               "d2h_bytes_per_step": int(32 * len(my_pairs) + 2 * 8 * n * n), "ms_per_step": float(tt[0]) * 1e3,
+               "api": "acoss_earlyfusion_upload + acoss_earlyfusion_pairs + acoss_snf x2 + acoss_eval_statistics x6 (EarlyFusion.similarity / do_late_fusion / getEvalStatistics)",
+               "MAP_early+late": float(ev["early+late"][3])}
+    pk = peaks()
+    st = acc[-1]
+    ms_csm, ms_sel, ms_sw = (float(np.mean([a[k] for a in acc])) for k in ("ms_csm", "ms_select", "ms_sw"))
+    cells = float(st["cells"])
+    tfl = st["gemm_flop"] / (ms_csm * 1e-3) / 1e12
+    sw_bytes = 4.0 * cells          # four uint8 binary matrices read once
+    kernels = [
+        {"kernel": "ef_csm kernels (3 cross-similarity GEMMs, d = 1000 / 1225 / 480)", "bound": "tensor", "achieved": tfl, "peak": pk["bf16_sus"],
+         "unit": "TFLOP/s", "frac": tfl / pk["bf16_sus"], "traffic": None, "ms_per_step": ms_csm, "share_of_step": ms_csm / ms_per_step},
+        {"kernel": "ef_row / ef_col / ef_early kernels (kNN binarise, WCSM, early fusion)", "bound": "hbm", "achieved": 16.0 * cells / (ms_sel * 1e-3) / 1e9,
+         "peak": pk["hbm"], "unit": "GB/s", "frac": 16.0 * cells / (ms_sel * 1e-3) / 1e9 / pk["hbm"], "traffic": None, "ms_per_step": ms_sel,
+         "share_of_step": ms_sel / ms_per_step, "note": "algorithmic bytes 3*4*M*N + 4*M*N per pair (SURVEY 8(d))"},
+        {"kernel": "sw_constrained kernel x4", "bound": "hbm", "achieved": sw_bytes / (ms_sw * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s",
+         "frac": sw_bytes / (ms_sw * 1e-3) / 1e9 / pk["hbm"], "traffic": None, "ms_per_step": ms_sw, "share_of_step": ms_sw / ms_per_step,
+         "gcups": 4.0 * cells / (ms_sw * 1e-3) / 1e9},
+    ]
+    dom = max(kernels, key=lambda k: k["ms_per_step"])
+    roofline = {k: dom[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}
+    roofline["kernel"] = dom["kernel"]
+    roofline["peak_source"] = pk["src"]
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        _POOL_STATE["bf"] = bf
+        rate, ns_, dt = _pool_rate(_c3_cpu_one, [tuple(p) for p in all_pairs[np.random.default_rng(0).permutation(P)[:4096]]], cores, args.cpu_seconds)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "%d random pairs of the %d-pair grid (%.1f s, %d processes, oracle/ports.py early_pair: numpy CSMs / kNN / WCSM + the C "
+                         "Smith-Waterman; the N x N fusion is not included)" % (ns_, P, dt, cores)}
+        # parity sample: CUDA scores vs the port on a few pairs (float GEMM order differs: compare to 1e-4 relative)
+        from oracle import ports as PT
+        pick = np.random.default_rng(1).choice(len(mine), size=min(8, len(mine)), replace=False)
+        exp = np.stack([PT.early_pair(bf[a], bf[b], 0.1, 10) for a, b in my_pairs[pick]])
+        got = res["scores"][pick]
+        parity = {"pairs": int(len(pick)), "mismatches": int(np.sum(np.abs(got - exp) > 1e-4 * np.maximum(1.0, np.abs(exp)))),
+                  "checker": "oracle/ports.py (numpy port pinned against the reference run verbatim)"}
+    else:
+        parity = None
+    workload = {"workload": "C3: EarlyFusionTralie all-pairs on %d synthetic tracks of 300-600 blocks (mfccs 50x20, ssms 1225, chromas 480), "
+                            "%d pairs per step, kappa=0.1 K=10; SNF K=20 x 20 iterations on 3 and 4 N x N matrices" % (n, P),
+                "tracks": n, "pairs": P, "debug_scale": args.scale,
+                "l2_policy": "inputs larger than L2: %.1f GB of block features, 4 x M x N float32 scratch per pair" % (h2d_feat / 1e9)}
+    ev = res["eval"]
+    _finish_line(args, world, "earlyfusion_allpairs_comparisons_per_sec", UNIT, value, ms_per_step, workload, roofline, kernels, cpu, e2e,
+                 (4 + 8) * args.steps, clocks, "f32",
+                 {"eval": {k: {"MR": v[0], "MAP": v[3]} for k, v in ev.items()}, "parity_sample": parity,
+                  "gpu_launches_note": "per step: >= 12 kernels per batch of pairs (3 CSM, 4 row-kNN, 1 column, 1 early, 4 SW) + SNF + eval"})
+
+
+def run_c5(args, rank, world, local_rank):
+    """SiMPle on 15 000 synthetic tracks (12 x L float64, L ~ U[150, 250]): a step = `pairs_per_step` ORDERED pairs of the
+    2.25e8-pair grid (default 2^24, a bounded sample: the whole grid is 100 s per step); FTM2D 15 000 x 900 all-pairs once per step."""
+    import torch
+    import torch.distributed as dist
+    import acoss_b200
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    ctx = acoss_b200.Context(local_rank)
+    feats, shingles, labels = _c5_workload(args)
+    n = len(feats)
+    P = args.pairs_per_step or (1 << 24)
+    rng = np.random.default_rng(5)
+    P = int(min(P, n * (n - 1)))
+    a = rng.integers(0, n, size=P).astype(np.int32)
+    b = (a + 1 + rng.integers(0, n - 1, size=P).astype(np.int32)) % n
+    all_pairs = np.stack([a, b], 1).astype(np.int32)
+    mine = np.arange(rank, P, world)
+    my_pairs = np.ascontiguousarray(all_pairs[mine])
+    ctx.simple_upload(feats)
+    stream = torch.cuda.ExternalStream(ctx.lib.acoss_ctx_stream(ctx.h), device=dev)
+    res = {}
+
+    def step():
+        res["scores"] = ctx.simple_pairs(my_pairs, 10)
+        t0 = time.perf_counter()
+        res["ftm"] = ctx.ftm2d_allpairs(shingles) if rank == 0 else None
+        res["t_ftm"] = time.perf_counter() - t0
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        ctx.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    t_ftm = []
+    for _ in range(args.steps):
+        step()
+        t_ftm.append(res["t_ftm"])
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    tt = torch.tensor([wall], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    sec_step = float(tt[0]) / args.steps
+    t_f = float(np.mean(t_ftm))
+    sec_simple = max(sec_step - t_f, 1e-9)
+    value = P / sec_simple
+    La = np.array([f.shape[1] for f in feats], np.int64)
+    flop = 26.0 * float(np.sum(La[my_pairs[:, 0]] * La[my_pairs[:, 1]])) * world
+    pk = peaks()
+    fp64_peak = 40.0          # B200 FP64 (non-tensor) ~ 40 TFLOP/s nominal; no measured figure in MEASURED_PEAKS.json
+    kernels = [
+        {"kernel": "simple_pair_kernel (matrix-profile join + median)", "bound": "fp64", "achieved": flop / sec_simple / 1e12, "peak": fp64_peak,
+         "unit": "TFLOP/s", "frac": flop / sec_simple / 1e12 / fp64_peak, "traffic": None, "ms_per_step": sec_simple * 1e3,
+         "note": "algorithmic flop 26 * La * Lb per ordered pair (SURVEY 8(d)); peak = nominal FP64 FMA rate (fallback: not in MEASURED_PEAKS.json)"},
+        {"kernel": "ftm2d_allpairs_kernel (15 000 x 900 x 15 000 fp64 Gram + exp epilogue)", "bound": "fp64", "achieved": 2.0 * 900 * n * n / t_f / 1e12,
+         "peak": fp64_peak, "unit": "TFLOP/s", "frac": 2.0 * 900 * n * n / t_f / 1e12 / fp64_peak, "traffic": None, "ms_per_step": t_f * 1e3,
+         "pairs_per_s": n * (n - 1) / 2 / t_f, "note": "includes the N x N float64 result copy to the host"},
+    ]
+    roofline = {k: kernels[0][k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}
+    roofline["kernel"] = kernels[0]["kernel"]
+    roofline["peak_source"] = "nominal FP64 (no measured FP64 peak on this pool)"
+    if rank != 0:
+        return
+    cpu = parity = None
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        _POOL_STATE["feats"] = feats
+        rate, ns_, dt = _pool_rate(_c5_cpu_one, [tuple(p) for p in all_pairs[:65536]], cores, args.cpu_seconds)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "%d ordered pairs of the step's %d (%.1f s, %d processes, oracle/ports.py simple_pair: numpy Gram + diagonal sums; the "
+                         "reference's Python row loop is ~10x slower per pair)" % (ns_, P, dt, cores)}
+        from oracle import ports as PT
+        pick = np.random.default_rng(1).choice(len(mine), size=32, replace=False)
+        exp = np.array([PT.simple_pair(feats[x], feats[y]) for x, y in my_pairs[pick]])
+        got = res["scores"][pick]
+        parity = {"pairs": 32, "mismatches": int(np.sum(np.abs(got - exp) > 1e-9 * np.maximum(1e-3, np.abs(exp)))),
+                  "checker": "oracle/ports.py (float64; tolerance 1e-9 relative)"}
+    e2e = {"value": value, "unit": UNIT, "h2d_bytes_per_step": int(my_pairs.nbytes), "d2h_bytes_per_step": int(8 * len(my_pairs)),
+           "ms_per_step": sec_simple * 1e3, "api": "acoss_simple_pairs (host pair list in, host float64 scores out: the timed call itself)",
+           "note": "features stay resident (Simple.preload uploads once per dataset); the pair list and the scores cross PCIe every step"}
+    workload = {"workload": "C5: SiMPle matrix-profile similarity, %d ORDERED pairs per step sampled from the %d x %d grid of %d synthetic tracks "
+                            "(12 x L float64, L~U[150,250], SSLEN 10); FTM2D %d x 900 all-pairs" % (P, n, n - 1, n, n),
+                "tracks": n, "pairs": P, "debug_scale": args.scale, "l2_policy": "290 MB of features, random pairs: inputs larger than L2"}
+    _finish_line(args, world, "simple_ordered_pairs_per_sec", UNIT, value, sec_simple * 1e3, workload, roofline, kernels, cpu, e2e,
+                 2 * args.steps, clocks, "f64", {"parity_sample": parity, "ftm2d_seconds_per_step": t_f})
+
+
+def run_reference_other(args, rank, world):
+    """--impl reference for C3 / C5: the numpy ports (oracle/ports.py) on all host cores, bounded samples."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = max(2.0, min(30.0, 150.0 / max(1, args.steps + args.warmup)))
+    if args.config == "C3":
+        ds = _c3_workload(args)
+        _POOL_STATE["bf"] = ds["block_feats"]
+        n = len(ds["block_feats"])
+        i, j = np.triu_indices(n, 1)
+        items = [tuple(p) for p in np.stack([i, j], 1)[np.random.default_rng(0).permutation(len(i))[:8192]]]
+        fn, metric, dtype, wl = _c3_cpu_one, "earlyfusion_allpairs_comparisons_per_sec", "f32", "C3: EarlyFusionTralie, %d tracks" % n
+    else:
+        feats, _, _ = _c5_workload(args)
+        _POOL_STATE["feats"] = feats
+        n = len(feats)
+        rng = np.random.default_rng(5)
+        a = rng.integers(0, n, size=65536)
+        items = [(int(x), int((x + 1 + y) % n)) for x, y in zip(a, rng.integers(0, n - 1, size=65536))]
+        fn, metric, dtype, wl = _c5_cpu_one, "simple_ordered_pairs_per_sec", "f64", "C5: SiMPle, %d tracks" % n
+    rates = []
+    for s_ in range(args.warmup + args.steps):
+        r, ns_, dt = _pool_rate(fn, items, cores, per_step)
+        if s_ >= args.warmup:
+            rates.append((r, ns_, dt))
+    value = sum(x[1] for x in rates) / sum(x[2] for x in rates)
+    line = {"impl": "reference", "metric": metric, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * sum(x[2] for x in rates) / max(1, len(rates)), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": dtype, "data": "synthetic", "config": {"workload": wl},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": "%d pairs per step, oracle/ports.py" % rates[-1][1]},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        run_reference(args, rank, world)
+        if args.config in ("C3", "C5"):
+            run_reference_other(args, rank, world)
+        else:
+            run_reference(args, rank, world)
+        return
+    if args.config in ("C3", "C5"):
+        if world > 1:
+            import torch
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        try:
+            (run_c3 if args.config == "C3" else run_c5)(args, rank, world, local_rank)
+        finally:
+            if world > 1:
+                import torch.distributed as dist
+                dist.destroy_process_group()
         return
     if world > 1:
         import torch

@@ -53,7 +53,9 @@ typedef struct acoss_crp_params {
     int32_t crp_mode;       /* 0 = auto, 1 = exact-everywhere strips,
                                2 = approximate (FMA sliding Gram) + rigorous band + exact recheck,
                                3 = same with tcgen05 G2 tiles, 4 = tcgen05 GEMM cross-similarity
-                               (128 x 256 tiles, Hankel operands) + band + exact recheck.
+                               (128 x 256 tiles, Hankel operands) + band + exact recheck in ONE kernel,
+                               5 = the same arithmetic as a phase-split pipeline (pivot / count / select /
+                               binarise kernels, TMA-staged precomputed operand planes).
                                Every mode returns the same bits.                 */
 } acoss_crp_params;
 

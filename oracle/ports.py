@@ -1,0 +1,178 @@
+# -*- coding: utf-8 -*-
+"""
+CPU ORACLE (ports) -- TEST INFRASTRUCTURE ONLY.
+
+numpy restatements of the reference's in-tree per-pair functions for EarlyFusionTralie, SiMPle, FTM2D and the
+N x N similarity network fusion.  /root/reference does not exist on the GPU box, so the CPU baselines of
+`bench.py --config C3|C4|C5` (cpu_baseline.kind = "port") and the `--impl reference` arm time THESE; they are pinned
+against the goldens generated from the reference run verbatim (tests/test_oracle.py::test_ports_vs_reference_goldens).
+Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this module.
+
+Each function cites the reference lines it follows (paths relative to the reference root).
+"""
+import numpy as np
+
+from . import oracle as O
+
+
+# ---- acoss/algorithms/utils/cross_recurrence.py -------------------------------------------------------------------
+def get_csm(X, Y):
+    """Euclidean cross-similarity by Gram expansion, negatives clipped (cross_recurrence.py:30-48).  float32 in -> float32."""
+    C = np.sum(X ** 2, 1)[:, None] + np.sum(Y ** 2, 1)[None, :] - 2 * X.dot(Y.T)
+    C[C < 0] = 0
+    return np.sqrt(C)
+
+
+def get_csm_cosine(X, Y):
+    """1 - cosine similarity, zero norms replaced by 1 (cross_recurrence.py:53-73)."""
+    xn = np.sqrt(np.sum(X ** 2, 1))
+    xn[xn == 0] = 1
+    yn = np.sqrt(np.sum(Y ** 2, 1))
+    yn[yn == 0] = 1
+    return 1 - (X / xn[:, None]).dot((Y / yn[:, None]).T)
+
+
+def get_oti(C1, C2):
+    """argmax_k sum(roll(C1, k) * C2), first maximum (cross_recurrence.py:75-103)."""
+    n = len(C1)
+    s = np.zeros(n)
+    for k in range(n):
+        s[k] = np.sum(np.roll(C1, k) * C2)
+    return int(np.argmax(s))
+
+
+def get_csm_blocked_oti(X, Y, C1, C2, csm_fn=get_csm_cosine):
+    """roll the 12 bins of every chroma frame of every block of X by the global OTI, then the CSM
+    (cross_recurrence.py:105-134)."""
+    nb = len(C1)
+    per = X.shape[1] // nb
+    X1 = np.roll(X.reshape(X.shape[0], per, nb), get_oti(C1, C2), axis=2).reshape(X.shape[0], per * nb)
+    return csm_fn(X1, Y)
+
+
+def csm_to_binary(D, kappa):
+    """row-wise: the int(round(kappa * n_cols)) smallest entries of every row -> 1 (cross_recurrence.py:136-161;
+    np.round is half-to-even)."""
+    M, N = D.shape
+    if kappa == 0:
+        return np.ones((M, N), np.uint8)
+    k = int(np.round(kappa * N)) if kappa < 1 else int(kappa)
+    J = np.argpartition(D, k, 1)[:, :k]
+    B = np.zeros((M, N), np.uint8)
+    B[np.arange(M)[:, None], J] = 1
+    return B
+
+
+# ---- acoss/algorithms/utils/similarity_fusion.py ------------------------------------------------------------------
+def getWCSM(C, k1, k2, Mu=0.5):
+    """similarity_fusion.py:38-54: row mean of the k2 smallest, column mean of the k1 smallest, eps = (r + c + C) / 3,
+    W = exp(-C^2 / (2 (Mu eps)^2))."""
+    m1 = np.mean(np.partition(C, k2, 1)[:, :k2], 1)
+    m2 = np.mean(np.partition(C, k1, 0)[:k1, :], 0)
+    eps = (m1[:, None] + m2[None, :] + C) / 3
+    return np.exp(-C ** 2 / (2 * (Mu * eps) ** 2))
+
+
+def getW(D, K, Mu=0.5):
+    """similarity_fusion.py:15-36."""
+    S = 0.5 * (D + D.T)
+    np.fill_diagonal(S, 0)
+    md = np.mean(np.partition(S, K + 1, 1)[:, :K + 1], 1) * float(K + 1) / float(K)
+    eps = (md[:, None] + md[None, :] + S) / 3
+    den = 2 * (Mu * eps) ** 2
+    den[den == 0] = 1
+    return np.exp(-S ** 2 / den)
+
+
+def getP(W):
+    """similarity_fusion.py:101-122 (diagRegularize=False branch, the only one used)."""
+    rs = np.sum(W, 1)
+    rs[rs == 0] = 1
+    return W / rs[:, None]
+
+
+def getS(W, K):
+    """similarity_fusion.py:124-144, as a dense (N, N) matrix with K non-zeros per row."""
+    N = W.shape[0]
+    J = np.argpartition(-W, K, 1)[:, :K]
+    V = W[np.arange(N)[:, None], J]
+    sn = np.sum(V, 1)
+    sn[sn == 0] = 1
+    S = np.zeros((N, N), W.dtype if W.dtype == np.float64 else np.float64)
+    S[np.arange(N)[:, None], J] = V / sn[:, None]
+    return S
+
+
+def snf_ws(Ws, K=5, niters=20, reg_diag=1):
+    """doSimilarityFusionWs (similarity_fusion.py:146-186) INCLUDING its list aliasing: after the first
+    iteration `Pts` and `nextPts` are one list, so matrix i sees the already-updated matrices k < i."""
+    Ps = [getP(W) for W in Ws]
+    Ss = [getS(W, K) for W in Ws]
+    Pts = [np.array(P, dtype=np.float64) for P in Ps]
+    nxt = [np.zeros(P.shape) for P in Pts]
+    n = len(Pts)
+    pix = np.arange(Ws[0].shape[0])
+    for _ in range(niters):
+        for i in range(n):
+            nxt[i] *= 0
+            for k in range(n):
+                if k != i:
+                    nxt[i] += Pts[k]
+            nxt[i] /= float(n - 1)
+            nxt[i] = Ss[i].dot((Ss[i].dot(nxt[i].T)).T)
+            if reg_diag > 0:
+                nxt[i][pix, pix] += reg_diag
+        Pts = nxt
+    out = np.zeros(Pts[0].shape)
+    for P in Pts:
+        out += P
+    return out / n
+
+
+def snf(mats, K=5, niters=5, reg_diag=1):
+    """doSimilarityFusion (similarity_fusion.py:188-196) -> (Ws, fused)."""
+    Ws = [getW(np.array(D), K) for D in mats]
+    return Ws, snf_ws(Ws, K, niters, reg_diag)
+
+
+# ---- acoss/algorithms/earlyfusion_traile.py:157-198 ----------------------------------------------------------------
+def early_pair(f1, f2, kappa=0.1, K=10, full=False):
+    """EarlyFusion.similarity for one pair of block-feature dicts: 4 scores (mfccs, ssms, chromas, early); the constrained
+    Smith-Waterman is the C oracle's (pinned against the reference's numba code)."""
+    C = [get_csm(f1["mfccs"], f2["mfccs"]), get_csm(f1["ssms"], f2["ssms"]),
+         get_csm_blocked_oti(f1["chromas"], f2["chromas"], f1["chroma_med"], f2["chroma_med"])]
+    Wsum = np.zeros_like(C[0])
+    for c in C:
+        Wsum += getWCSM(c, K, K)
+    C.append(np.exp(-Wsum))
+    B = [csm_to_binary(c, kappa) for c in C]
+    scores = np.array([O.sw_constrained(b) for b in B], np.float64)
+    return (scores, C, B) if full else scores
+
+
+# ---- acoss/algorithms/simple_silva.py:45-54, 68-118 ----------------------------------------------------------------
+def simple_pair(Si, Sj, sslen=10):
+    """-median_i min_j sum_{c, k < sslen} (a[c, i + k] - b[c, j + k])^2 with b = Sj rolled by the OTI of the time-summed
+    profiles (argsort, last index).  Evaluated directly (Gram + sliding diagonal sums) in float64; the reference's
+    FFT-seeded update gives the same values to ~1e-13."""
+    pa, pb = np.sum(Si, 1), np.sum(Sj, 1)
+    v = np.array([np.dot(pa, np.roll(pb, k)) for k in range(12)])
+    b = np.roll(Sj, int(np.argsort(v)[-1]), axis=0)
+    a = Si
+    La, Lb = a.shape[1], b.shape[1]
+    na, nb = La - sslen + 1, Lb - sslen + 1
+    G = a.T.dot(b)                                              # (La, Lb) frame Gram
+    cs = np.zeros((La + 1, Lb + 1))
+    # diagonal prefix sums: cs[i + 1, j + 1] = cs[i, j] + G[i, j]
+    for i in range(La):
+        cs[i + 1, 1:] = cs[i, :-1] + G[i]
+    dot = cs[sslen:sslen + na, sslen:sslen + nb] - cs[:na, :nb]
+    a2 = np.concatenate([[0.0], np.cumsum(np.sum(a * a, 0))])
+    b2 = np.concatenate([[0.0], np.cumsum(np.sum(b * b, 0))])
+    d = (a2[sslen:] - a2[:na])[:, None] + (b2[sslen:] - b2[:nb])[None, :] - 2 * dot
+    return -float(np.median(np.min(d, 1)))
+
+
+# ---- acoss/algorithms/ftm2d.py:85-97 --------------------------------------------------------------------------------
+def ftm2d_pair(s1, s2):
+    return float(np.exp(-np.sum((s1 - s2) ** 2)))

@@ -135,7 +135,7 @@ def test_crp_exact_ties_duplicate_frames(ctx, oracle):
     assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]) and np.array_equal(R, Ro)
 
 
-@pytest.mark.parametrize("mode", [1, 2, 3, 4])
+@pytest.mark.parametrize("mode", [1, 2, 3, 4, 5])
 def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
     """exact-everywhere strips (mode 1) and approximate + band + exact re-check (mode 2) give the
     same bits as the oracle; sizes large enough for the band path (NB >= 128), ragged tiles."""
@@ -153,14 +153,15 @@ def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
             assert np.array_equal(R, Ro), (mode, a, b)
 
 
+@pytest.mark.parametrize("mode", [4, 5])
 @pytest.mark.parametrize("kappa", [0.004, 0.02, 0.5, 0.93, 1.0, 0.0])
-def test_crp_gemm_extreme_percentiles(ctx, oracle, kappa):
+def test_crp_gemm_extreme_percentiles(ctx, oracle, kappa, mode):
     """tensor-core kernel with brackets that are unbounded below / above (tiny and huge percentiles), ragged last tiles
     and strips, against the oracle"""
     rng = np.random.default_rng(77)
     tracks = _tracks(rng, [300, 521, 777], noise=0.12)
     ctx.upload_tracks(tracks)
-    prm = ctx.params(kappa=kappa, crp_mode=4)
+    prm = ctx.params(kappa=kappa, crp_mode=mode)
     for (a, b) in [(0, 1), (1, 2), (2, 0)]:
         R, tq, tr, o = ctx.crp_pair(a, b, prm)
         Ro, info = oracle.chroma_cross_similarity(tracks[a], tracks[b], kappa=kappa, full=True)
@@ -179,7 +180,7 @@ def test_crp_band_degenerate_inputs(ctx, oracle):
     half = np.concatenate([const[:150], rng.random((200, 12)).astype(np.float32)], 0)
     tracks = [const, silent, dup, half, _tracks(rng, [400])[0]]
     ctx.upload_tracks(tracks)
-    for mode in (2, 3, 4):
+    for mode in (2, 3, 4, 5):
         prm = ctx.params(crp_mode=mode)
         for (x, y) in [(0, 0), (0, 1), (1, 1), (2, 2), (2, 4), (3, 0), (3, 2), (4, 3), (1, 4)]:
             R, tq, tr, o = ctx.crp_pair(x, y, prm)
@@ -197,13 +198,13 @@ def test_band_vs_exact_mode_scores_large(ctx):
     ctx.upload_tracks(tracks)
     pairs = np.array([(i, j) for i in range(10) for j in range(10) if i < j], np.int32)
     q1, d1 = ctx.serra09_pairs(pairs, ctx.params(crp_mode=1), want_dmax=True)
-    for mode in (2, 3, 4):
+    for mode in (2, 3, 4, 5):
         q2, d2 = ctx.serra09_pairs(pairs, ctx.params(crp_mode=mode), want_dmax=True)
         st = ctx.pair_stats()
         assert np.array_equal(q1, q2) and np.array_equal(d1, d2), mode
         assert st["n_exact_cells"] < 0.02 * st["crp_cells"], (mode, st)
     R1 = ctx.crp_pair(0, 1, ctx.params(crp_mode=1))
-    for mode in (2, 3, 4):
+    for mode in (2, 3, 4, 5):
         R2 = ctx.crp_pair(0, 1, ctx.params(crp_mode=mode))
         assert all(np.array_equal(x, y) for x, y in zip(R1[:3], R2[:3])), mode
 
@@ -273,7 +274,13 @@ def test_pairs_multibatch_and_alloc_retry_vs_oracle(oracle):
         q2, d2 = c.serra09_pairs(pairs, want_dmax=True)
         st = c.pair_stats()
         assert st["n_batches"] > 5, st
-        assert set(st["crp_kernels"]) >= {"gemm", "band"}, st       # both sides of the 512-frame switch ran
+        assert "gemm" in st["crp_kernels"] or "split" in st["crp_kernels"], st
+        short = np.array([(i, j) for i in range(8) for j in range(8) if i != j], np.int32)     # tracks below the 512-frame switch
+        q4, d4 = c.serra09_pairs(short, want_dmax=True)
+        st = c.pair_stats()
+        assert st["n_batches"] > 3 and st["crp_kernels"] == ["band"], st
+        sq, sd_, _ = oracle.serra09_pairs(tracks, short, want_dmax=True, n_threads=8)
+        assert np.array_equal(q4, sq) and np.array_equal(d4, sd_)
         assert np.array_equal(q1, oq) and np.array_equal(d1, od)
         assert np.array_equal(q2, oq) and np.array_equal(d2, od)
         c.set_option("crp_budget_bytes", 64 << 20)

@@ -122,3 +122,39 @@ def test_reference_verbatim_when_present(oracle):
     for _ in range(5):
         B = (rng.random((int(rng.integers(4, 90)), int(rng.integers(4, 90)))) < 0.2).astype(np.uint8)
         assert np.float32(ns.align.smith_waterman_constrained(B)) == np.float32(oracle.sw_constrained(B))
+
+
+def test_ports_vs_reference_goldens(oracle, golden):
+    """oracle/ports.py (the numpy ports that bench.py times as the CPU baseline of C3 / C4 / C5 on the GPU box, where the
+    reference itself is absent) against the goldens made from the reference run verbatim."""
+    from oracle import ports as P
+    from oracle.make_golden import early_dataset
+    # EarlyFusion: matrices and scores of the small golden pairs
+    g = golden("earlyfusion_reference.npz")
+    bf = early_dataset()["block_feats"]
+    for k, (a, b) in enumerate(g["mat_pairs"]):
+        sc, C, B = P.early_pair(bf[a], bf[b], 0.1, 10, full=True)
+        np.testing.assert_allclose(np.stack(C), g["csm%d" % k], rtol=1e-5, atol=1e-6)
+        assert np.array_equal(np.stack(B), g["bin%d" % k])
+        assert sc.astype(np.float32).tolist() == [g["D_" + s][a, b] for s in ("mfccs", "ssms", "chromas", "early")]
+        assert P.get_oti(bf[a]["chroma_med"], bf[b]["chroma_med"]) == int(g["oti%d" % k])
+    # SiMPle at both golden sizes
+    g = golden("simple_ftm2d_reference.npz")
+    feats = [g["simple_feat%d" % i] for i in range(10)]
+    got = [P.simple_pair(feats[a], feats[b]) for a, b in g["simple_pairs"]]
+    np.testing.assert_allclose(got, g["simple_scores"], rtol=1e-9, atol=1e-11)
+    g2 = golden("simple_large.npz")
+    f2 = [g2["feat%d" % i] for i in range(int(g2["n"]))]
+    got = [P.simple_pair(f2[a], f2[b]) for a, b in g2["pairs"][:12]]
+    np.testing.assert_allclose(got, g2["scores"][:12], rtol=1e-9, atol=1e-11)
+    # FTM2D
+    S = [g["ftm_shingle%d" % i] for i in range(10)]
+    assert np.float32(P.ftm2d_pair(S[0], S[3])) == g["ftm_D"][0, 3]
+    # SNF incl. the reference's list aliasing
+    gs = golden("snf_reference.npz")
+    for c in range(int(gs["n"])):
+        nm, N, K, nit = (int(x) for x in gs["cfg%d" % c])
+        if N > 128:
+            continue
+        mats = [gs["D%d_%d" % (c, k)] for k in range(nm)]
+        np.testing.assert_allclose(P.snf(mats, K=K, niters=nit, reg_diag=1)[1], gs["fused%d" % c], rtol=1e-9, atol=1e-12)
