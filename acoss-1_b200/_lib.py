@@ -65,6 +65,7 @@ SYMBOLS = {
                                       c_i32p, c_i32p, c_f32p, c_f32p, c_i32p]),
     "acoss_cover_similarity_from_crp": (ctypes.c_int, [c_vp, c_u8p, c_i32p, c_i32p, ctypes.c_int32, ctypes.c_int32,
                                                        ctypes.c_float, ctypes.c_float, c_f32p]),
+    "acoss_cover_similarity_from_crp_noalloc": (ctypes.c_int, [c_vp, c_vp, c_i32p, c_i32p, ctypes.c_int32, ctypes.c_int32, c_vp]),
     "acoss_scores_to_matrix_dev": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, c_vp]),
     "acoss_normalize_by_length_dev": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp, ctypes.c_int32]),
     "acoss_eval_statistics": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_i32p, c_i32p, c_i32p, c_i32p,
@@ -257,6 +258,13 @@ class Context(object):
                                                           _ptr(Ns, ctypes.c_int32), len(crps), a, dis_onset, dis_extension,
                                                           _ptr(out, ctypes.c_float)))
         return out
+
+    def cover_similarity_from_crp_noalloc(self, crps_dev_ptr, Ms, Ns, out_dev_ptr, alignment="serra09"):
+        """Allocation-free Qmax / Dmax on device-resident 0/1 matrices (include/acoss_b200.h): device pointers as ints."""
+        Ms, Ns = _np(Ms, np.int32), _np(Ns, np.int32)
+        a = {"serra09": 0, "chen17": 1}[alignment]
+        self._ck(self.lib.acoss_cover_similarity_from_crp_noalloc(self.h, c_vp(crps_dev_ptr), _ptr(Ms, ctypes.c_int32),
+                                                                  _ptr(Ns, ctypes.c_int32), len(Ms), a, c_vp(out_dev_ptr)))
 
     def sw_constrained(self, mats):
         flat, Ms, Ns = self._pack_mats(mats)

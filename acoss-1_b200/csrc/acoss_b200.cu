@@ -360,3 +360,100 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 #include "api_snf.inc"
 #include "api_simple.inc"
 #include "api_early.inc"
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of acoss_cover_similarity_from_crp (no counterpart in the reference: added
+// for callers that cannot call cudaMalloc -- CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The scratch the Qmax / Dmax kernel needs (pair descriptors + the CRPs re-coded into the pitched "delta" byte layout) lives in
+// ONE file-scope device array: every GPU that loads the library holds ACOSS_NOALLOC_SCRATCH_BYTES of it until exit, every call
+// on a device shares it (calls that overlap on the GPU race), and it keeps the previous call's contents (the error flag is
+// cleared at the start of every call; everything else is overwritten before it is read).
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress, once
+// per device with that device current.
+// ---------------------------------------------------------------------------
+#define NOALLOC_DESC_BYTES (ACOSS_NOALLOC_MAX_MATRICES * sizeof(PairDesc))      // 64 KB
+#define NOALLOC_FLAG_OFF NOALLOC_DESC_BYTES                                     // int error flag (+ padding to 256 B)
+#define NOALLOC_CRP_OFF (NOALLOC_DESC_BYTES + 256)
+#define ACOSS_NOALLOC_SCRATCH_BYTES (NOALLOC_CRP_OFF + ACOSS_NOALLOC_MAX_CRP_BYTES + 256)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[ACOSS_NOALLOC_SCRATCH_BYTES];
+static void* g_noalloc_ptr[64] = {};          // device address of the array, per device ordinal
+
+// plain 0 / 1 bytes -> delta code (0x02 / 0xFF) in the pitched layout of the DP kernel; padding columns = "no recurrence"
+__global__ void noalloc_recode_kernel(const PairDesc* __restrict__ descs, int n, const uint8_t* __restrict__ src,
+                                      uint8_t* __restrict__ dst, int* __restrict__ flag)
+{
+    for (int k = blockIdx.y; k < n; k += gridDim.y) {
+        const PairDesc pd = descs[k];
+        const int64_t total = (int64_t)pd.M * pd.pitch;
+        const uint8_t* s = src + pd.q_frame_off;            // q_frame_off: byte offset of this matrix in the caller's packed input
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+            const int i = (int)(e / pd.pitch), j = (int)(e - (int64_t)i * pd.pitch);
+            uint8_t code = (uint8_t)CRP_DELTA_ZERO;
+            if (j < pd.N) {
+                const uint8_t v = s[(int64_t)i * pd.N + j];
+                if (v > 1) atomicExch(flag, 1);
+                if (v == 1) code = (uint8_t)CRP_DELTA_ONE;
+            }
+            dst[pd.crp_off + e] = code;
+        }
+    }
+}
+
+extern "C" int acoss_cover_similarity_from_crp_noalloc(acoss_ctx* ctx, const uint8_t* crps_dev, const int32_t* Ms, const int32_t* Ns,
+                                                       int32_t n, int32_t alignment, float* out_scores_dev)
+{
+    if (!ctx) return ACOSS_ERR_ARG;
+    if (!crps_dev || !Ms || !Ns || n < 0 || !out_scores_dev || alignment < 0 || alignment > 1) { ctx->set_error("bad argument"); return ACOSS_ERR_ARG; }
+    if (n > ACOSS_NOALLOC_MAX_MATRICES) {
+        ctx->set_error("acoss_cover_similarity_from_crp_noalloc: more than ACOSS_NOALLOC_MAX_MATRICES (1024) matrices in one call");
+        return ACOSS_ERR_TOO_LONG;
+    }
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) return ACOSS_OK;
+    if (ctx->device >= 64) { ctx->set_error("acoss_cover_similarity_from_crp_noalloc: device ordinal >= 64"); return ACOSS_ERR_ARG; }
+    if (!g_noalloc_ptr[ctx->device]) {          // set-up, once per device, with that device current
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[ctx->device] = p;
+    }
+    unsigned char* scratch = static_cast<unsigned char*>(g_noalloc_ptr[ctx->device]);
+    int maxN = 0, max_min = 0;
+    for (int k = 0; k < n; ++k) {
+        if (Ms[k] < 1 || Ns[k] < 1) { ctx->set_error("empty matrix"); return ACOSS_ERR_ARG; }
+        maxN = std::max(maxN, Ns[k]); max_min = std::max(max_min, std::min(Ms[k], Ns[k]));
+    }
+    const DpConfig cfg = pick_dp_config(maxN, max_min, true);
+    if (cfg.G == 0) {
+        ctx->set_error("acoss_cover_similarity_from_crp_noalloc: matrices wider than 2560 columns (or scores beyond int16 half units) need the allocating entry point");
+        return ACOSS_ERR_TOO_LONG;
+    }
+    const int gran = 64 * cfg.G;
+    static thread_local PairDesc descs[ACOSS_NOALLOC_MAX_MATRICES];      // host staging: no heap allocation either
+    size_t bytes = 0, src = 0;
+    for (int k = 0; k < n; ++k) {
+        PairDesc pd = {};
+        pd.M = Ms[k]; pd.N = Ns[k]; pd.pitch = (Ns[k] + gran - 1) / gran * gran;
+        pd.crp_off = (int64_t)bytes; pd.out_idx = k; pd.q_frame_off = (int64_t)src;
+        bytes += (size_t)pd.M * pd.pitch; src += (size_t)pd.M * pd.N;
+        descs[k] = pd;
+    }
+    if (bytes > (size_t)ACOSS_NOALLOC_MAX_CRP_BYTES) {
+        ctx->set_error("acoss_cover_similarity_from_crp_noalloc: the matrices need " + std::to_string(bytes) +
+                       " bytes of scratch, the static array holds ACOSS_NOALLOC_MAX_CRP_BYTES (16 MiB)");
+        return ACOSS_ERR_TOO_LONG;
+    }
+    cudaStream_t st = ctx->stream;
+    PairDesc* d_descs = reinterpret_cast<PairDesc*>(scratch);
+    int* d_flag = reinterpret_cast<int*>(scratch + NOALLOC_FLAG_OFF);
+    uint8_t* d_crp = scratch + NOALLOC_CRP_OFF;
+    CK(cudaMemsetAsync(d_flag, 0, sizeof(int), st));
+    CK(cudaMemcpyAsync(d_descs, descs, sizeof(PairDesc) * n, cudaMemcpyHostToDevice, st));
+    noalloc_recode_kernel<<<dim3(64, std::min(n, 1024)), 256, 0, st>>>(d_descs, n, crps_dev, d_crp, d_flag);
+    CK_LAUNCH();
+    CK(launch_dp_any(ctx, cfg, alignment, d_descs, n, d_crp, out_scores_dev, 0.5f, 0.5f, maxN));
+    int flag = 0;
+    CK(cudaMemcpyAsync(&flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (flag) { ctx->set_error("CoverSongSimilarity: non-binary element in input"); return ACOSS_ERR_ARG; }
+    return ACOSS_OK;
+}

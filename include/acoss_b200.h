@@ -179,6 +179,24 @@ int acoss_cover_similarity_from_crp(acoss_ctx *ctx, const uint8_t *crps_host,
                                     float dis_onset, float dis_extension,
                                     float *out_scores_host);
 
+/* Allocation-free variant of acoss_cover_similarity_from_crp.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  The call performs no cudaMalloc / cudaFree and uses no allocating library routine: the
+ * kernel's scratch (pair descriptors and the matrices re-coded into the DP kernel's pitched byte layout) lives in a static
+ * device array of ACOSS_NOALLOC_MAX_CRP_BYTES + 65 KiB that every GPU loading the library holds until exit.
+ *   crps_dev        DEVICE pointer: concatenation of n (M_k, N_k) uint8 0/1 row-major matrices
+ *   Ms_host/Ns_host HOST arrays of n shapes;  alignment 0 = 'serra09' (Qmax), 1 = 'chen17' (Dmax); disOnset = disExtension = 0.5
+ *   out_scores_dev  DEVICE pointer, n float32 (valid when the call returns: it synchronises the context's stream)
+ * Limits (ACOSS_ERR_TOO_LONG beyond them): n <= ACOSS_NOALLOC_MAX_MATRICES, N_k <= 2560, sum_k M_k * pitch_k <=
+ * ACOSS_NOALLOC_MAX_CRP_BYTES with pitch_k = N_k rounded up to 128 / 256 / 512 (by the widest matrix: <= 512 / <= 1280 / wider).
+ * All calls on a device share the array and it keeps the last call's contents (what must start at zero is cleared by the
+ * call): calls that overlap on the GPU (two contexts / streams on one device) race -- serialise them. */
+#define ACOSS_NOALLOC_MAX_MATRICES 1024
+#define ACOSS_NOALLOC_MAX_CRP_BYTES (16 << 20)
+int acoss_cover_similarity_from_crp_noalloc(acoss_ctx *ctx, const uint8_t *crps_dev,
+                                            const int32_t *Ms_host, const int32_t *Ns_host,
+                                            int32_t n, int32_t alignment, float *out_scores_dev);
+
 /* ---- N x N score matrix: scatter, mirror, length normalisation, evaluation -- */
 
 /* D (n x n float32, device) := 0, then D[i,j] = score for each pair, then
