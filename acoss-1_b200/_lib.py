@@ -79,6 +79,8 @@ SYMBOLS = {
                                                ctypes.POINTER(ctypes.c_double), ctypes.c_int32, ctypes.POINTER(ctypes.c_double), c_i64p]),
     "acoss_simple_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_int32, c_f64p]),
     "acoss_ftm2d_allpairs": (ctypes.c_int, [c_vp, c_f64p, ctypes.c_int32, ctypes.c_int32, c_f64p]),
+    "acoss_ftm2d_shingles": (ctypes.c_int, [c_vp, c_f32p, c_i64p, c_i64p, c_i64p, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
+                                            ctypes.c_double, c_f64p]),
     "acoss_earlyfusion_upload": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32,
                                                 c_f32p, c_i64p, ctypes.c_int32]),
     "acoss_earlyfusion_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_double, ctypes.c_int32, c_f64p]),
@@ -342,6 +344,24 @@ class Context(object):
         D = np.zeros((n, n), np.float64)
         self._ck(self.lib.acoss_ftm2d_allpairs(self.h, _ptr(S, ctypes.c_double), n, d, _ptr(D, ctypes.c_double)))
         return D
+
+    def ftm2d_shingles(self, raw, onsets, pwr=1.96, win=75, C=5):
+        """FTM2D.load_features for a list of raw (T_t, 12) float32 chroma arrays and their beat onsets (frame indices), on the
+        device (ftm2d.py:52-66).  Returns (n_tracks, 12 * win) float64 unit shingles."""
+        raw = [_np(r, np.float32).reshape(-1, 12) for r in raw]
+        offs = np.zeros(len(raw) + 1, np.int64)
+        offs[1:] = np.cumsum([r.shape[0] for r in raw])
+        flat = _np(np.concatenate(raw, 0), np.float32)
+        ons = [_np(np.asarray(o).ravel(), np.int64) for o in onsets]
+        ooff = np.zeros(len(raw) + 1, np.int64)
+        ooff[1:] = np.cumsum([len(o) for o in ons])
+        oflat = _np(np.concatenate(ons) if ons else np.zeros(0), np.int64)
+        if len(oflat) == 0:
+            oflat = np.zeros(1, np.int64)
+        out = np.zeros((len(raw), 12 * int(win)), np.float64)
+        self._ck(self.lib.acoss_ftm2d_shingles(self.h, _ptr(flat, ctypes.c_float), _ptr(offs, ctypes.c_int64), _ptr(oflat, ctypes.c_int64),
+                                               _ptr(ooff, ctypes.c_int64), len(raw), float(pwr), int(win), float(C), _ptr(out, ctypes.c_double)))
+        return out
 
     # ---- EarlyFusionTralie ---------------------------------------------------------------
     def earlyfusion_upload(self, block_feats):

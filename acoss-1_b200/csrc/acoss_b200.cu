@@ -22,6 +22,8 @@
 #include "kernels_snf.cuh"
 #include "kernels_simple.cuh"
 #include "kernels_early.cuh"
+#include "kernels_early_tc.cuh"
+#include "kernels_ftm.cuh"
 
 static std::string g_create_error;
 
@@ -71,6 +73,11 @@ struct acoss_ctx {
     int ef_tracks = 0, ef_d[3] = {0, 0, 0};
     std::vector<int64_t> ef_offs;
     DevBuf d_ef_x[3], d_ef_sq[3], d_ef_cmed, d_ef_csm, d_ef_bin;
+    DevBuf d_ef_planes[3], d_ef_poff[3];   // tensor-core operand planes of the three features + per-track byte offsets
+    int ef_nkc[3] = {0, 0, 0};
+    bool have_ef_planes = false;
+    int ef_force_simt = 0;                // acoss_ctx_set_option "ef_simt_csm": keep the fp32 SIMT tile kernel (comparison / fallback)
+    int ef_csm_kernel_used = 0;           // 1 = SIMT tiles, 2 = tcgen05 GEMM (last acoss_earlyfusion_pairs call)
     double ef_ms[3] = {0, 0, 0}, ef_flop = 0;
     int64_t ef_cells = 0;
     // per-call scratch
@@ -142,7 +149,8 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
                       &ctx->d_edges, &ctx->d_fb,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
-                      &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin};
+                      &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin,
+                      &ctx->d_ef_planes[0], &ctx->d_ef_planes[1], &ctx->d_ef_planes[2], &ctx->d_ef_poff[0], &ctx->d_ef_poff[1], &ctx->d_ef_poff[2]};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
@@ -159,6 +167,7 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
         return ACOSS_OK;
     }
     if (k == "auto_split") { ctx->auto_split = value != 0; return ACOSS_OK; }
+    if (k == "ef_simt_csm") { ctx->ef_force_simt = value != 0; return ACOSS_OK; }
     if (k == "inject_alloc_failures") {
         ctx->inject_alloc_failures = (int)std::max<int64_t>(0, value);
         return ACOSS_OK;
@@ -360,6 +369,7 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 #include "api_snf.inc"
 #include "api_simple.inc"
 #include "api_early.inc"
+#include "api_features.inc"
 
 // ---------------------------------------------------------------------------
 // Allocation-free variant of acoss_cover_similarity_from_crp (no counterpart in the reference: added

@@ -36,9 +36,13 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
 
 // ---- coalesced chunk loads of 2G delta bytes per lane ---------------------------
 template <int G> struct RowBytes;
+// plain 0 / 1 bytes -> 0x00 (one) / 0xFF (zero): the sign-replicating PRMT of delta<P>() then yields 0x0000 / 0xFFFF halves
+__device__ __forceinline__ uint32_t sw_code(uint32_t w) { return ~(w * 0xFFu); }
+
 template <> struct RowBytes<8> {
     uint4 v;
     __device__ __forceinline__ void load(const uint8_t* p) { v = __ldg(reinterpret_cast<const uint4*>(p)); }
+    __device__ __forceinline__ void to_sw() { v = make_uint4(sw_code(v.x), sw_code(v.y), sw_code(v.z), sw_code(v.w)); }
     __device__ __forceinline__ void fill(uint32_t w) { v = make_uint4(w, w, w, w); }
     template <int P> __device__ __forceinline__ uint32_t delta() const {
         const uint32_t x = (P >> 2) == 0 ? v.x : v.y;
@@ -50,6 +54,7 @@ template <> struct RowBytes<8> {
 template <> struct RowBytes<4> {
     uint2 v;
     __device__ __forceinline__ void load(const uint8_t* p) { v = __ldg(reinterpret_cast<const uint2*>(p)); }
+    __device__ __forceinline__ void to_sw() { v = make_uint2(sw_code(v.x), sw_code(v.y)); }
     __device__ __forceinline__ void fill(uint32_t w) { v = make_uint2(w, w); }
     template <int P> __device__ __forceinline__ uint32_t delta() const {
         constexpr uint32_t b = P;
@@ -59,6 +64,7 @@ template <> struct RowBytes<4> {
 template <> struct RowBytes<2> {
     uint32_t v;
     __device__ __forceinline__ void load(const uint8_t* p) { v = __ldg(reinterpret_cast<const uint32_t*>(p)); }
+    __device__ __forceinline__ void to_sw() { v = sw_code(v); }
     __device__ __forceinline__ void fill(uint32_t w) { v = w; }
     template <int P> __device__ __forceinline__ uint32_t delta() const {
         constexpr uint32_t b = P;
@@ -101,7 +107,7 @@ __device__ __forceinline__ void dp_row_step(uint32_t (&Aprev)[NCH][G], uint32_t 
             const uint32_t s1_0 = prmt(n1, Aprev[ch][G - 1], 0x5432);   // (nbr cell 2G-1, own cell G-1)
             const uint32_t s2_0 = prmt(n2, Aprev[ch][G - 2], 0x5432);   // (nbr cell 2G-2, own cell G-2)
             uint32_t dsh = 0;   // chen17: packed delta of (i, j-1) for p = 0
-            if (ALIGN) {
+            if (ALIGN == 1) {
                 const uint32_t dl_last = cur[ch].template delta<G - 1>();
                 const uint32_t dprev = (ch > 0) ? cur[ch > 0 ? ch - 1 : 0].template delta<G - 1>() : 0xFFFFFFFFu;
                 const uint32_t nd = __shfl_sync(0xffffffffu, edge ? dprev : dl_last, src);
@@ -110,7 +116,21 @@ __device__ __forceinline__ void dp_row_step(uint32_t (&Aprev)[NCH][G], uint32_t 
             StepUnroll<G, G - 1>::template run<ALIGN>(Aprev[ch], Bold[ch], cur[ch], s1_0, s2_0, carry[ch], Bon[ch], dsh);
             if (ch == 0) { Bold[0][0] &= zmask; Bold[0][1] &= zmask; }
             carry[ch] = s1_0;
-            if (ALIGN) {
+            if (ALIGN == 2) {
+                // constrained Smith-Waterman: Bold holds S of the new row; the maximum is taken over S (last chunk: without
+                // the excluded last column and the padding), then the row is stored as U = S + dl(B) for its successors
+                if (ch == nch - 1) {
+#pragma unroll
+                    for (int p = 0; p < G; p += 2)
+                        rm = __vimax3_s16x2(rm, Bold[ch][p] & vmask[p], Bold[ch][p + 1] & vmask[p + 1]);
+                } else {
+#pragma unroll
+                    for (int p = 0; p < G; p += 2) rm = __vimax3_s16x2(rm, Bold[ch][p], Bold[ch][p + 1]);
+                }
+                StepUnroll<G, G - 1>::sw_penalty(cur[ch], Bold[ch]);
+                continue;
+            }
+            if (ALIGN == 1) {
                 StepUnroll<G, G - 1>::bonus(cur[ch], Bon[ch]);
                 if (ch == nch - 1) {
                     // a padded column can receive the +R bonus of the last valid column: keep it out of the maximum
@@ -233,6 +253,118 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
     }
 }
 
+// ---- constrained Smith-Waterman on the same row-parallel DPX scheme ---------------------------------------------------
+// smith_waterman_constrained(B) (acoss/algorithms/utils/alignment_tools.py:25-46), exact in integer tenths (increments
+// {+1, +0.3, -1, -1.7} x 10).  With the score matrix shifted by one row and one column, S'(i, j) = S(i + 1, j + 1),
+//     S'(i, j) = max(0, mv(B(i, j)) + max(U(i-1, j-1), U(i-2, j-1), U(i-1, j-2))),   U(i, j) = S'(i, j) + dl(B(i, j)),
+// mv = +10 / -10, dl = 0 / -7 by B(i, j): every term is indexed like B itself and the dependency shape is Qmax's (two previous
+// rows), so dp_row_step<G, NCH, 2> applies: rows of U in registers as int16x2, VIMNMX3 + 2 x VIADDMNMX per register.
+// S' = 0 for i < 2 or j < 2 (U = dl(B) there); the reference's loops stop at i = M - 1, j = N - 1, i.e. the last row and the
+// last column of B are never scored: the row loop ends at M - 2 and the maximum masks columns >= N - 1.
+// Input: plain 0 / 1 bytes, row pitch a multiple of the chunk (64 G bytes), padding bytes 0.  Output: the maximum in tenths.
+struct SwMat { int64_t off; int32_t M, N, pitch, out_idx; };
+
+template <int G, int NCH>
+__global__ void __launch_bounds__(128)
+sw_rowpar_kernel(const SwMat* __restrict__ mats, int64_t n_mats, const uint8_t* __restrict__ bin, float* __restrict__ out_tenths,
+                 unsigned* __restrict__ counter)
+{
+    constexpr int CHUNK = 64 * G, LB = 2 * G;
+    const int lane = threadIdx.x & 31;
+    const uint32_t zmask = (lane == 0) ? 0xFFFF0000u : 0xFFFFFFFFu;   // clears cells j = 0, 1
+    for (;;) {
+        unsigned kk = 0;
+        if (lane == 0) kk = atomicAdd(counter, 1u);
+        const int64_t k = __shfl_sync(0xffffffffu, kk, 0);
+        if (k >= n_mats) break;
+        const SwMat mt = mats[k];
+        const int M = mt.M, N = mt.N, pitch = mt.pitch;
+        const int nch = (N + CHUNK - 1) / CHUNK;
+        const uint8_t* base = bin + mt.off + (int64_t)lane * LB;
+        uint32_t A[NCH][G], B[NCH][G], carry[NCH], Bon[NCH][G];
+        uint32_t rm = 0;
+        uint32_t vmask[G];
+        {
+            const int c0 = (nch - 1) * CHUNK + lane * LB;
+#pragma unroll
+            for (int p = 0; p < G; ++p)
+                vmask[p] = ((c0 + p < N - 1) ? 0x0000FFFFu : 0u) | ((c0 + p + G < N - 1) ? 0xFFFF0000u : 0u);
+        }
+        RowBytes<G> r0[NCH], r1[NCH];
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+            carry[ch] = 0;
+            r0[ch].fill(0xFFFFFFFFu); r1[ch].fill(0xFFFFFFFFu);       // chunks beyond the matrix: B = 0
+#pragma unroll
+            for (int p = 0; p < G; ++p) { A[ch][p] = 0; B[ch][p] = 0; Bon[ch][p] = 0; }
+        }
+        if (M >= 4 && N >= 4) {
+            // rows 0 and 1: S' = 0, U = dl(B).  Row i-1 must sit in A and row i-2 in B for i = 2: row 0 -> B, row 1 -> A; the
+            // carried (i-2, j-1) edge of row 0 is rebuilt from B the way dp_row_step builds it
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch)
+                if (ch < nch) {
+                    RowBytes<G> t0, t1;
+                    t0.load(base + ch * CHUNK); t0.to_sw();
+                    t1.load(base + (int64_t)pitch + ch * CHUNK); t1.to_sw();
+                    StepUnroll<G, G - 1>::sw_penalty(t0, B[ch]);
+                    StepUnroll<G, G - 1>::sw_penalty(t1, A[ch]);
+                }
+            {
+                const int src = (lane + 31) & 31;
+                const bool edge = (lane == 31);
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch)
+                    if (ch < nch) {
+                        const uint32_t e1 = (ch > 0) ? B[ch > 0 ? ch - 1 : 0][G - 1] : 0u;
+                        const uint32_t g1 = edge ? e1 : B[ch][G - 1];
+                        const uint32_t n1 = __shfl_sync(0xffffffffu, g1, src);
+                        carry[ch] = prmt(n1, B[ch][G - 1], 0x5432);
+                    }
+            }
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch)
+                if (ch < nch) { r0[ch].load(base + (int64_t)2 * pitch + ch * CHUNK); r0[ch].to_sw(); }
+            const int64_t pitch64 = pitch;
+            const uint8_t* rp = base + 2 * pitch64;
+            const bool pf_lane = ((lane * LB) & 127) == 0;
+            const int Mend = M - 1;                              // the last row of B is never scored
+            for (int i = 2; i < Mend; i += 2, rp += 2 * pitch64) {
+                const bool more1 = (i + 1 < Mend);
+                if (more1) {
+                    const uint8_t* p1 = rp + pitch64;
+#pragma unroll
+                    for (int ch = 0; ch < NCH; ++ch)
+                        if (ch < nch) { r1[ch].load(p1 + ch * CHUNK); r1[ch].to_sw(); }
+                }
+                if (pf_lane && i + 7 < Mend) {
+                    const uint8_t* p6 = rp + 4 * pitch64;
+                    const uint8_t* p7 = p6 + pitch64;
+#pragma unroll
+                    for (int ch = 0; ch < NCH; ++ch)
+                        if (ch < nch) {
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(p6 + ch * CHUNK));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(p7 + ch * CHUNK));
+                        }
+                }
+                dp_row_step<G, NCH, 2>(A, B, carry, Bon, r0, vmask, nch, lane, zmask, rm);      // row i   -> B
+                if (more1) {
+                    if (i + 2 < Mend) {
+                        const uint8_t* p2 = rp + 2 * pitch64;
+#pragma unroll
+                        for (int ch = 0; ch < NCH; ++ch)
+                            if (ch < nch) { r0[ch].load(p2 + ch * CHUNK); r0[ch].to_sw(); }
+                    }
+                    dp_row_step<G, NCH, 2>(B, A, carry, Bon, r1, vmask, nch, lane, zmask, rm);  // row i+1 -> A
+                }
+            }
+        }
+        int best = max((int)(rm & 0xFFFFu), (int)(rm >> 16));
+        best = __reduce_max_sync(0xffffffffu, best);
+        if (lane == 0) out_tenths[mt.out_idx] = (float)best;
+    }
+}
+
 // Fully unrolled per-register update, P = G-1 .. 0 (recursion keeps every register index a compile-time
 // constant).  Writes the new row over B in place.
 template <int G, int P> struct StepUnroll {
@@ -246,6 +378,14 @@ template <int G, int P> struct StepUnroll {
         const uint32_t a2 = (P >= 2) ? A[P >= 2 ? P - 2 : 0] : (P == 1 ? s1_0 : s2_0); // row i-1, col j-2
         const uint32_t dl = row.template delta<P>();
         uint32_t m;
+        if (ALIGN == 2) {
+            // constrained Smith-Waterman in integer tenths (alignment_tools.py:25-46), rows hold U = S + dl(B):
+            //   S = max(0, mv + max(U(i-1,j-1), U(i-2,j-1), U(i-1,j-2))),  mv = +10 / -10 by B(i,j)   (dl: 0x0000 = one, 0xFFFF = zero)
+            m = __vimax3_s16x2(a1, b1, a2);
+            B[P] = __viaddmax_s16x2(m, 0x000A000Au ^ (dl & 0xFFFCFFFCu), 0u);
+            StepUnroll<G, P - 1>::template run<ALIGN>(A, B, row, s1_0, s2_0, carry, Bon, dsh);
+            return;
+        }
         if (ALIGN) {
             // chen17: (i-2,j-1) + R(i-1,j)  and  (i-1,j-2) + R(i,j-1)
             const uint32_t dprev = (P >= 1) ? row.template delta<(P >= 1 ? P - 1 : 0)>() : dsh;
@@ -263,12 +403,19 @@ template <int G, int P> struct StepUnroll {
         Bon[P] = delta_to_bonus(row.template delta<P>());
         StepUnroll<G, P - 1>::bonus(row, Bon);
     }
+    // U = S + dl(B): -7 tenths where B = 0 (packed add without carry between the halves: viaddmax against -32768)
+    __device__ __forceinline__ static void sw_penalty(const RowBytes<G>& row, uint32_t (&B)[G])
+    {
+        B[P] = __viaddmax_s16x2(B[P], row.template delta<P>() & 0xFFF9FFF9u, 0x80008000u);
+        StepUnroll<G, P - 1>::sw_penalty(row, B);
+    }
 };
 template <int G> struct StepUnroll<G, -1> {
     template <int ALIGN>
     __device__ __forceinline__ static void run(const uint32_t (&)[G], uint32_t (&)[G], const RowBytes<G>&,
                                                uint32_t, uint32_t, uint32_t, const uint32_t (&)[G], uint32_t) {}
     __device__ __forceinline__ static void bonus(const RowBytes<G>&, uint32_t (&)[G]) {}
+    __device__ __forceinline__ static void sw_penalty(const RowBytes<G>&, uint32_t (&)[G]) {}
 };
 
 // ---- generic fallback: any N, any gammas, fp32 like the oracle -------------------

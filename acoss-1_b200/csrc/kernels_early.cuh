@@ -22,6 +22,8 @@ struct EfPair {
     int32_t M, N;            // number of blocks
     int32_t oti;             // get_oti(chroma_med_i, chroma_med_j), device-written
     int32_t k_bin;           // int(np.round(kappa * N))
+    int32_t pitch;           // row pitch (bytes) of the binary matrices: N rounded up to the Smith-Waterman chunk, padding = 0
+    int32_t pad_;
     int64_t blk_a, blk_b;    // first block row of the two tracks in the block store
     int64_t csm_off;         // float offset of 4 consecutive M x N matrices (mfccs, ssms, chromas, early)
     int64_t bin_off;         // byte offset of 4 consecutive M x N binary matrices
@@ -205,7 +207,8 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
         uint32_t keys[R];
 #pragma unroll
         for (int q = 0; q < R; ++q) { const int j = q * 32 + lane; keys[q] = (j < N) ? ef_key(row[j]) : 0xffffffffu; }
-        uint8_t* brow = bin + pd.bin_off + ((int64_t)mat * pd.M + i) * N;
+        uint8_t* brow = bin + pd.bin_off + ((int64_t)mat * pd.M + i) * pd.pitch;
+        for (int j = N + lane; j < pd.pitch; j += 32) brow[j] = 0;
         const int kb = pd.k_bin;
         if (kb <= 0) {
 #pragma unroll

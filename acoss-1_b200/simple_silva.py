@@ -17,12 +17,6 @@ from .algorithm_template import CoverAlgorithm
 __all__ = ['Simple']
 
 
-def _hann_window(n):
-    """scipy.signal.get_window('hann', n, fftbins=False) == librosa.filters.get_window (symmetric Hann)."""
-    k = np.arange(n)
-    return 0.5 - 0.5 * np.cos(2.0 * np.pi * k / (n - 1))
-
-
 class Simple(CoverAlgorithm):
     """
     Attributes
@@ -45,37 +39,28 @@ class Simple(CoverAlgorithm):
                                 shortname=shortname, cachedir=cachedir, device=device)
 
     def load_features(self, i, do_plot=False):
-        if i in self.all_feats:
-            return self.all_feats[i]
-        feats = CoverAlgorithm.load_features(self, i)
-        feat_orig = np.asarray(feats[self.chroma_type]).T
-        new_feat = np.zeros((feat_orig.shape[0], int(feat_orig.shape[1] / self.SKIP)))
-        for k in range(new_feat.shape[1]):
-            new_feat[:, k] = np.mean(feat_orig[:, k * self.SKIP:k * self.SKIP + self.WIN], axis=1)
-        self.all_feats[i] = self.smooth(new_feat)
+        """(12, int(T / SKIP)) float64 features of song i (simple_silva.py:34-43): WIN-frame window means every SKIP frames,
+        Hann smoothing and column L2 normalisation run on the device (acoss_simple_preprocess); cached."""
+        if i not in self.all_feats:
+            feats = CoverAlgorithm.load_features(self, i)
+            raw = np.asarray(feats[self.chroma_type], np.float32)
+            self.all_feats[i] = self.context().simple_preprocess([raw], win=self.WIN, skip=self.SKIP)[0]
         return self.all_feats[i]
 
     def smooth(self, feat, win_len_smooth=4):
-        """Hann smoothing along time ('same', zero fill) then L2-normalise every column
-        (simple_silva.py:56-66; librosa.util.normalize(norm=2, axis=0) leaves tiny columns as is)."""
-        win = _hann_window(win_len_smooth + 2)
-        win = win / np.sum(win)
-        out = np.stack([np.convolve(row, win, mode='full') for row in feat])
-        start = (len(win) - 1) // 2
-        out = out[:, start:start + feat.shape[1]]
-        length = np.sqrt(np.sum(np.abs(out) ** 2, axis=0, keepdims=True))
-        length[length < np.finfo(out.dtype).tiny] = 1.0
-        return out / length
+        """Hann smoothing along time ('same', zero fill) then L2-normalise every column (simple_silva.py:56-66), on the device:
+        the smoothing stage of acoss_simple_preprocess applied to already-reduced (12, L) features (WIN = SKIP = 1)."""
+        feat = np.asarray(feat, np.float64)
+        return self.context().simple_preprocess([np.ascontiguousarray(feat.T, np.float32)], win=1, skip=1,
+                                                win_len_smooth=win_len_smooth)[0]
 
     def oti(self, seq_a, seq_b):
-        """Host restatement of simple_silva.py:45-54 (kept for API parity; `similarity` does it on the device)."""
-        profile_a = np.sum(seq_a, 1)
-        profile_b = np.sum(seq_b, 1)
-        oti_vec = np.zeros(12)
-        for i in range(12):
-            oti_vec[i] = np.dot(profile_a, np.roll(profile_b, i, axis=0))
-        sorted_index = np.argsort(oti_vec)
-        return np.roll(seq_b, sorted_index[-1], axis=0), sorted_index
+        """Simple.oti (simple_silva.py:45-54): roll seq_b's 12 bins by the shift that maximises the dot product of the two
+        time-summed profiles (np.argsort, last index).  Public helper of the reference class; `similarity` performs the same
+        step inside the pair kernel."""
+        prof_a, prof_b = np.sum(seq_a, 1), np.sum(seq_b, 1)
+        order = np.argsort([np.dot(prof_a, np.roll(prof_b, k, axis=0)) for k in range(12)])
+        return np.roll(seq_b, order[-1], axis=0), order
 
     def preload(self):
         """All tracks at once: WIN/SKIP means, Hann smoothing and column normalisation run on the device

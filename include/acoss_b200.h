@@ -106,6 +106,9 @@ int acoss_ctx_synchronize(acoss_ctx *ctx);
 /* Tuning / test knobs of a context.  Keys:
  *   "crp_budget_bytes"       per-batch CRP working set of acoss_serra09_pairs* (default: a quarter of the free HBM,
  *                            at most 32 GiB; also settable by the environment variable ACOSS_CRP_BUDGET_MB at creation)
+ *   "auto_split"             1: crp_mode 0 (auto) picks the phase-split CRP pipeline (crp_mode 5) where it applies
+ *   "ef_simt_csm"            1: acoss_earlyfusion_upload skips the tensor-core operand planes (the CSMs then run on the
+ *                            fp32 SIMT tile kernel); set before the upload
  *   "inject_alloc_failures"  test hook: the next `value` device allocations of the pair pipeline's batch buffers
  *                            report ACOSS_ERR_NOMEM (exercises the halve-the-budget retry)
  * Returns ACOSS_ERR_ARG for an unknown key or a non-positive budget. */
@@ -280,6 +283,16 @@ int acoss_simple_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pair
  * out_D_host[i*n + j] = exp(-sum((s_i - s_j)**2)), shingles_host = (n, d) float64 (d = 900). */
 int acoss_ftm2d_allpairs(acoss_ctx *ctx, const double *shingles_host, int32_t n, int32_t d,
                          double *out_D_host);
+
+/* Per-track FTM2D shingles on the device (replaces the body of FTM2D.load_features,
+ * acoss/algorithms/ftm2d.py:52-66, with chrompwr :100-117 and btchroma_to_fftmat :120-138): raw (T_t, 12) float32 chroma and the
+ * beat onsets (frame indices, concatenated; onset_offsets_host[n_tracks + 1]) of every track -> beat-synchronous median
+ * (librosa.util.sync, boundaries {0} u onsets u {T}), chrompwr(PWR), |fft2| of every 12 x WIN patch (fft-shifted, flattened),
+ * log(C * patch / |patch| + 1), median over the patches, unit norm.  out_shingles_host: (n_tracks, 12 * WIN) float64.
+ * ACOSS_ERR_TOO_SHORT when a track has fewer than WIN beats (the reference fails there). */
+int acoss_ftm2d_shingles(acoss_ctx *ctx, const float *raw_frames_host, const int64_t *raw_offsets_host,
+                         const int64_t *onsets_host, const int64_t *onset_offsets_host, int32_t n_tracks,
+                         double pwr, int32_t win, double C, double *out_shingles_host);
 
 /* ---- EarlyFusionTralie ------------------------------------------------------------ */
 

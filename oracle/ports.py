@@ -176,3 +176,63 @@ def simple_pair(Si, Sj, sslen=10):
 # ---- acoss/algorithms/ftm2d.py:85-97 --------------------------------------------------------------------------------
 def ftm2d_pair(s1, s2):
     return float(np.exp(-np.sum((s1 - s2) ** 2)))
+
+
+# ---- per-track features (acoss/algorithms/ftm2d.py:52-66, 100-138; simple_silva.py:34-43, 56-66) ---------------------
+def sync_median(data, idx):
+    """librosa.util.sync(data, idx, aggregate=np.median) (librosa 0.6.1): segments between the unique boundaries
+    {0} u idx u {T} along the last axis."""
+    T = data.shape[-1]
+    b = np.unique(np.concatenate([[0], np.asarray(idx, dtype=int), [T]])).astype(int)
+    b = b[(b >= 0) & (b <= T)]
+    out = np.empty(data.shape[:-1] + (len(b) - 1,), dtype=data.dtype)
+    for k in range(len(b) - 1):
+        out[..., k] = np.median(data[..., b[k]:b[k + 1]], axis=-1)
+    return out
+
+
+def chrompwr(X, P=.5):
+    """ftm2d.py:100-117: chroma columns to the power P, norms preserved."""
+    n = np.sqrt(np.sum(X * X, axis=0))[None, :].repeat(X.shape[0], 0)
+    n[n == 0] = 1
+    Xp = np.power(X / n, P)
+    npw = np.sqrt(np.sum(Xp * Xp, axis=0))[None, :].repeat(X.shape[0], 0)
+    npw[npw == 0] = 1.
+    return n * (Xp / npw)
+
+
+def ftm2d_shingle(chroma_T, onsets, PWR=1.96, WIN=75, C=5):
+    """FTM2D.load_features (ftm2d.py:52-66) for one track; chroma_T: (12, T) float32.  scipy.fftpack.fft2 keeps the float32
+    patch in single precision (complex64), like the reference."""
+    import scipy.fftpack
+    hp = sync_median(chroma_T, onsets)
+    ch = chrompwr(hp, PWR)
+    nb = ch.shape[1]
+    if nb < WIN:
+        raise ValueError("fewer beats than WIN")
+    mat = np.zeros((12 * WIN, nb - WIN + 1))
+    for i in range(nb - WIN + 1):
+        F = scipy.fftpack.fft2(ch[:, i:i + WIN])
+        mat[:, i] = scipy.fftpack.fftshift(np.sqrt(np.real(F) ** 2 + np.imag(F) ** 2)).flatten()
+    sh = mat.T
+    nrm = np.sqrt(np.sum(sh ** 2, 1))
+    nrm[nrm == 0] = 1
+    sh = np.log(C * sh / nrm[:, None] + 1)
+    s = np.median(sh, 0)
+    return s / np.sqrt(np.sum(s ** 2))
+
+
+def simple_features(chroma_T, WIN=200, SKIP=100, win_len_smooth=4):
+    """Simple.load_features + Simple.smooth (simple_silva.py:34-43, 56-66) for one track; chroma_T: (12, T)."""
+    nf = np.zeros((chroma_T.shape[0], int(chroma_T.shape[1] / SKIP)))
+    for k in range(nf.shape[1]):
+        nf[:, k] = np.mean(chroma_T[:, k * SKIP:k * SKIP + WIN], axis=1)
+    n = win_len_smooth + 2
+    win = 0.5 - 0.5 * np.cos(2.0 * np.pi * np.arange(n) / (n - 1))       # symmetric Hann (fftbins=False)
+    win = win / np.sum(win)
+    out = np.stack([np.convolve(r, win, mode='full') for r in nf])
+    st = (len(win) - 1) // 2
+    out = out[:, st:st + nf.shape[1]]
+    length = np.sqrt(np.sum(np.abs(out) ** 2, axis=0, keepdims=True))
+    length[length < np.finfo(out.dtype).tiny] = 1.0
+    return out / length

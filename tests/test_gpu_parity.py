@@ -603,19 +603,16 @@ def test_simple_preprocess_vs_reference_golden(ctx, golden):
         assert f.shape == ref.shape
         np.testing.assert_allclose(f, ref, rtol=1e-12, atol=1e-15)
     # ragged: T not a multiple of SKIP, last window clipped, a track shorter than SKIP (no columns), other WIN / SKIP
+    from oracle import ports as P
     rng = np.random.default_rng(5)
     raw = [rng.random((n, 12)).astype(np.float32) for n in (1234, 99, 100, 777, 2001)]
-    mirror = acoss_b200.Simple.__new__(acoss_b200.Simple)
     for win, skip in ((200, 100), (64, 50), (30, 70)):
         got = ctx.simple_preprocess(raw, win=win, skip=skip)
         for r, f in zip(raw, got):
-            fo = r.T
-            nf = np.zeros((12, int(fo.shape[1] / skip)))
-            for k in range(nf.shape[1]):
-                nf[:, k] = np.mean(fo[:, k * skip:k * skip + win], axis=1)
-            assert f.shape == nf.shape
-            if nf.shape[1]:
-                np.testing.assert_allclose(f, mirror.smooth(nf), rtol=1e-12, atol=1e-15)
+            exp = P.simple_features(r.T, WIN=win, SKIP=skip)
+            assert f.shape == exp.shape
+            if exp.shape[1]:
+                np.testing.assert_allclose(f, exp, rtol=1e-12, atol=1e-15)
 
 
 def test_simple_generic_sslen_and_errors(ctx):
@@ -643,6 +640,39 @@ def test_simple_generic_sslen_and_errors(ctx):
         ctx.simple_pairs(pairs, sslen=30)          # track 1 has 24 columns < SSLEN
 
 
+def test_ftm2d_shingles_vs_reference_golden(ctx, golden, workdir):
+    """Per-track FTM2D shingles on the device (beat-synchronous median, chrompwr, 12 x 75 2-D DFT magnitudes, log, median, unit
+    norm) against the reference's FTM2D.load_features run verbatim.  Tolerance 2e-5 of the largest entry: the reference's
+    scipy.fftpack.fft2 of the float32 chroma is complex64 (its magnitudes carry float32 FFT rounding), the device accumulates
+    the same DFT sums in float64 and rounds the magnitude to float32 once.  Also through the classes (cache files,
+    Simple.load_features / smooth on the device) and the error for a track with fewer beats than WIN."""
+    import acoss_b200
+    from oracle.make_golden import simple_ftm_dataset
+    from oracle import ports as P
+    g = golden("simple_ftm2d_reference.npz")
+    ds, extra = simple_ftm_dataset()
+    ons = [m["onsets"] for m in extra["madmom_features"]]
+    S = ctx.ftm2d_shingles(ds["hpcp"], ons)
+    assert S.shape == (10, 900)
+    for i in range(10):
+        ref = g["ftm_shingle%d" % i]
+        np.testing.assert_allclose(S[i], ref, rtol=0, atol=2e-5 * np.max(np.abs(ref)))
+        assert abs(np.sqrt(np.sum(S[i] ** 2)) - 1.0) < 1e-12
+    with pytest.raises(acoss_b200.AcossError) as e:
+        ctx.ftm2d_shingles([ds["hpcp"][0][:600]], [ons[0][ons[0] < 600]])
+    assert e.value.code == -3
+    csv, fdir = _simple_ftm_dataset(workdir)
+    f = acoss_b200.FTM2D(csv, fdir, shortname="gs")
+    np.testing.assert_allclose(f.load_features(3), g["ftm_shingle3"], rtol=0, atol=2e-5 * np.max(np.abs(g["ftm_shingle3"])))
+    f2 = acoss_b200.FTM2D(csv, fdir, shortname="gs")           # second object: served from the cache file of the first
+    assert np.array_equal(f2.load_features(3), f.load_features(3)) and len(f2.cliques) == 1
+    s = acoss_b200.Simple(csv, fdir, shortname="gs")
+    for i in (0, 7):
+        np.testing.assert_allclose(s.load_features(i), g["simple_feat%d" % i], rtol=1e-12, atol=1e-15)
+    x = np.random.default_rng(1).random((12, 40)).astype(np.float32).astype(np.float64)
+    np.testing.assert_allclose(s.smooth(x), P.simple_features(x, WIN=1, SKIP=1), rtol=1e-12, atol=1e-15)
+
+
 def test_ftm2d_allpairs_vs_reference_golden(ctx, golden):
     g = golden("simple_ftm2d_reference.npz")
     S = np.stack([g["ftm_shingle%d" % i] for i in range(10)])
@@ -668,7 +698,8 @@ def test_simple_and_ftm2d_classes_and_benchmark(golden, workdir):
     assert list(res["main"][:4]) == g["ftm_eval"].tolist()
     f = acoss_b200.FTM2D(csv, fdir, shortname="g2")
     f.all_pairwise(1, symmetric=True)
-    assert np.array_equal(np.array(f.Ds["main"]), g["ftm_D"])
+    # shingles now come from the device (float32-FFT-rounding tolerance, see test_ftm2d_shingles_vs_reference_golden)
+    np.testing.assert_allclose(np.array(f.Ds["main"]), g["ftm_D"], rtol=2e-5, atol=1e-7)
     f.cleanup_memmap()
 
 

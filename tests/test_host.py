@@ -147,22 +147,17 @@ def _simple_ftm_dataset(workdir):
     return str(workdir / "ds.csv"), fdir, ds
 
 
-def test_simple_and_ftm2d_load_features_match_reference(golden, workdir):
-    """Per-track preprocessing of SiMPle / FTM2D (host side) against the reference run verbatim."""
-    import acoss_b200
-    from acoss_b200.simple_silva import Simple
-    from acoss_b200.ftm2d import FTM2D
+def test_feature_ports_match_reference_goldens(golden, workdir):
+    """oracle/ports.py restatements of the per-track SiMPle / FTM2D features against the reference run verbatim (the
+    product classes compute them on the device: tests/test_gpu_parity.py)."""
+    from oracle import ports as P
+    from oracle.make_golden import simple_ftm_dataset
     g = golden("simple_ftm2d_reference.npz")
-    csv, fdir, ds = _simple_ftm_dataset(workdir)
+    ds, extra = simple_ftm_dataset()
     assert np.allclose([float(np.sum(h, dtype=np.float64)) for h in ds["hpcp"]], g["hpcp_sum"], rtol=0, atol=0)
-    s = Simple(csv, fdir, shortname="g")
-    f = FTM2D(csv, fdir, shortname="g")
-    for i in range(s.N):
-        np.testing.assert_allclose(s.load_features(i), g["simple_feat%d" % i], rtol=1e-12, atol=1e-15)
-        np.testing.assert_allclose(f.load_features(i), g["ftm_shingle%d" % i], rtol=1e-10, atol=1e-14)
-    a, b = g["simple_feat0"], g["simple_feat1"]
-    rolled, idx = s.oti(a, b)
-    assert rolled.shape == b.shape and len(idx) == 12
+    for i, h in enumerate(ds["hpcp"]):
+        np.testing.assert_allclose(P.simple_features(h.T), g["simple_feat%d" % i], rtol=1e-12, atol=1e-15)
+        np.testing.assert_allclose(P.ftm2d_shingle(h.T, extra["madmom_features"][i]["onsets"]), g["ftm_shingle%d" % i], rtol=1e-10, atol=1e-14)
 
 
 def test_packed_feature_store_roundtrip_and_errors(tmp_path):
