@@ -81,6 +81,8 @@ SYMBOLS = {
     "acoss_ftm2d_allpairs": (ctypes.c_int, [c_vp, c_f64p, ctypes.c_int32, ctypes.c_int32, c_f64p]),
     "acoss_ftm2d_shingles": (ctypes.c_int, [c_vp, c_f32p, c_i64p, c_i64p, c_i64p, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
                                             ctypes.c_double, c_f64p]),
+    "acoss_earlyfusion_block_features": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_i64p, c_f32p, c_i64p, c_i64p, c_i64p, ctypes.c_int32,
+                                                        ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, c_f32p, c_f32p, c_f32p, c_f32p, c_i64p]),
     "acoss_earlyfusion_upload": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32,
                                                 c_f32p, c_i64p, ctypes.c_int32]),
     "acoss_earlyfusion_pairs": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.c_double, ctypes.c_int32, c_f64p]),
@@ -364,6 +366,36 @@ class Context(object):
         return out
 
     # ---- EarlyFusionTralie ---------------------------------------------------------------
+    def earlyfusion_block_features(self, mfccs, chromas, onsets, blocksize=20, mfccs_per_block=50, chromas_per_block=40):
+        """EarlyFusion.load_features on the device for a list of tracks: mfccs[t] (T, n_mfcc) float32 (= feats['mfcc_htk'].T),
+        chromas[t] (T, 12) float32, onsets[t] beat frame indices.  Returns a list of dicts 'mfccs', 'ssms', 'chromas',
+        'chroma_med' (earlyfusion_traile.py:104-150)."""
+        n = len(mfccs)
+        mf = [_np(m, np.float32) for m in mfccs]
+        n_mfcc = int(mf[0].shape[1])
+        ch = [_np(c, np.float32).reshape(-1, 12) for c in chromas]
+        ons = [_np(np.asarray(o).ravel(), np.int64) for o in onsets]
+
+        def offs(lens):
+            o = np.zeros(n + 1, np.int64)
+            o[1:] = np.cumsum(lens)
+            return o
+        moff, coff, ooff = offs([m.shape[0] for m in mf]), offs([c.shape[0] for c in ch]), offs([len(o) for o in ons])
+        mflat, cflat, oflat = _np(np.concatenate(mf, 0), np.float32), _np(np.concatenate(ch, 0), np.float32), _np(np.concatenate(ons), np.int64)
+        boff = np.zeros(n + 1, np.int64)
+        args = [self.h, _ptr(mflat, ctypes.c_float), n_mfcc, _ptr(moff, ctypes.c_int64), _ptr(cflat, ctypes.c_float), _ptr(coff, ctypes.c_int64),
+                _ptr(oflat, ctypes.c_int64), _ptr(ooff, ctypes.c_int64), n, int(blocksize), int(mfccs_per_block), int(chromas_per_block)]
+        self._ck(self.lib.acoss_earlyfusion_block_features(*(args + [None, None, None, None, _ptr(boff, ctypes.c_int64)])))
+        NB = int(boff[-1])
+        om = np.zeros((NB, mfccs_per_block * n_mfcc), np.float32)
+        os_ = np.zeros((NB, mfccs_per_block * (mfccs_per_block - 1) // 2), np.float32)
+        oc = np.zeros((NB, chromas_per_block * 12), np.float32)
+        omed = np.zeros((n, 12), np.float32)
+        self._ck(self.lib.acoss_earlyfusion_block_features(*(args + [_ptr(om, ctypes.c_float), _ptr(os_, ctypes.c_float), _ptr(oc, ctypes.c_float),
+                                                                     _ptr(omed, ctypes.c_float), _ptr(boff, ctypes.c_int64)])))
+        return [{"mfccs": om[boff[t]:boff[t + 1]].copy(), "ssms": os_[boff[t]:boff[t + 1]].copy(), "chromas": oc[boff[t]:boff[t + 1]].copy(),
+                 "chroma_med": omed[t].copy()} for t in range(n)]
+
     def earlyfusion_upload(self, block_feats):
         """block_feats: list of dicts with 'mfccs', 'ssms', 'chromas' (n_blocks, d) and 'chroma_med' (12)."""
         nb = [int(f['mfccs'].shape[0]) for f in block_feats]

@@ -60,6 +60,7 @@ def benchmark(dataset_csv, feature_dir, feature_type="hpcp", algorithm="Serra09"
         from .earlyfusion_traile import EarlyFusion
         algo = EarlyFusion(dataset_csv=dataset_csv, datapath=feature_dir, chroma_type=feature_type,
                            shortname=shortname, **algo_kwargs)
+        algo.preload_features()                       # all tracks in one device batch (the reference loops over load_features)
         for i in range(len(algo.filepaths)):
             algo.load_features(i)
         _logger().info('Feature loading done...')
@@ -69,6 +70,7 @@ def benchmark(dataset_csv, feature_dir, feature_type="hpcp", algorithm="Serra09"
         from .ftm2d import FTM2D
         algo = FTM2D(dataset_csv=dataset_csv, datapath=feature_dir, chroma_type=feature_type,
                      shortname=shortname, **algo_kwargs)
+        algo.preload()                                # all shingles in one device batch
         for i in range(len(algo.filepaths)):
             algo.load_features(i)
         _logger().info('Feature loading done...')
@@ -77,6 +79,7 @@ def benchmark(dataset_csv, feature_dir, feature_type="hpcp", algorithm="Serra09"
         from .simple_silva import Simple
         algo = Simple(dataset_csv=dataset_csv, datapath=feature_dir, chroma_type=feature_type,
                       shortname=shortname, **algo_kwargs)
+        algo.preload()                                # WIN/SKIP means, smoothing, normalisation of all tracks in one device batch
         for i in range(len(algo.filepaths)):
             algo.load_features(i)
         _logger().info('Feature loading done...')

@@ -698,7 +698,7 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 //   (C) warp per row: exact order statistics among the candidates -> percentile -> threshold
 //   rows that could not be bracketed (bracket miss, list overflow, tiny side B): the whole row exactly
 // =====================================================================================================================
-#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * GM_ROWS * 32 * 4)
+#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * GM_ROWS * 32 * 4 + SP_SEL_WARPS * 64 * 4)
 
 __global__ void __launch_bounds__(SP_SEL_THREADS, 4)
 crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
@@ -717,6 +717,7 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     int* s_off = s_flag + GM_ROWS;                                          // [GM_ROWS + 1]
     int* pool_col = s_off + GM_ROWS + 2;                                    // [GM_ROWS][32]
     float* pool_dex = reinterpret_cast<float*>(pool_col + GM_ROWS * 32);    // [GM_ROWS][32]
+    int* s_hist = reinterpret_cast<int*>(pool_dex + GM_ROWS * 32);          // [SP_SEL_WARPS][64]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_exact = 0;
     float max_err = 0.0f;
@@ -759,72 +760,81 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     if (lane == 0) { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); if (ovf) atomicAdd(&counters[15], 1ull); else atomicAdd(&counters[13], 1ull); }
                     continue;
                 }
+                // The row's list (<= 512 entries in [pa, pb), 16 slots per lane, of which ~6 are in use) goes through ONE 64-bin
+                // histogram over the bracket (shared-memory atomics, 64 counters per warp): a prefix scan finds the bin(s) holding the
+                // wanted ranks; everything within 2E of those bins is a candidate for the exact chains.  ~250 warp instructions per
+                // row; the value bisection this replaces cost ~1300 (ncu: the kernel was issue-bound at 180 k warp instructions per strip).
                 const float2* lst = lists + srow * SP_LIST_STRIDE;
-                float l2[SP_SEL_LPL];
-                float vmn = INFINITY, vmx = -INFINITY;
+                int* h = s_hist + warp * 64;
+                h[lane] = 0; h[lane + 32] = 0;
+                float lx[SP_SEL_LPL];
+                int ly[SP_SEL_LPL];
 #pragma unroll
                 for (int q = 0; q < SP_SEL_LPL; ++q) {              // slot (q % 4) * 32 + lane of segment q / 4
-                    const int sl = (q & 3) * 32 + lane;
-                    l2[q] = INFINITY;
-                    if (sl < cseg[q >> 2]) { l2[q] = lst[(q >> 2) * GM_SUBCAP + sl].x; vmn = fminf(vmn, l2[q]); vmx = fmaxf(vmx, l2[q]); }
-                }
-                for (int o = 16; o > 0; o >>= 1) {
-                    vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
-                    vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
-                }
-                const int kkr = pr.lo - c_ar;                   // invariant: #(list < w_lo) <= kkr < #(list < w_hi)
-                float w_lo = vmn, w_hi = INFINITY, b_hi = vmx;
-                int c_lo = 0, c_hi = c_abr;
-                for (int it = 0; it < 48 && c_hi - c_lo > 3; ++it) {
-                    // interpolation step towards the wanted rank (the list is close to uniform inside the narrow bracket),
-                    // every third step a plain bisection so that the loop converges on any input
-                    float mid;
-                    if (it % 3 != 2 && w_hi != INFINITY) {
-                        const float fr = ((float)(kkr - c_lo) + 0.5f) / (float)(c_hi - c_lo);
-                        mid = w_lo + (b_hi - w_lo) * fminf(fmaxf(fr, 0.02f), 0.98f);
-                    } else {
-                        mid = 0.5f * (w_lo + b_hi);
+                    lx[q] = INFINITY; ly[q] = 0;
+                    if ((q & 3) * 32 < cseg[q >> 2]) {              // warp-uniform: most sub-lists end inside their second block
+                        const int sl = (q & 3) * 32 + lane;
+                        if (sl < cseg[q >> 2]) { const float2 e = lst[(q >> 2) * GM_SUBCAP + sl]; lx[q] = e.x; ly[q] = __float_as_int(e.y); }
                     }
-                    if (!(mid > w_lo) || !(mid < b_hi)) { mid = 0.5f * (w_lo + b_hi); if (!(mid > w_lo) || !(mid < b_hi)) break; }
-                    int cm = 0;
-#pragma unroll
-                    for (int q = 0; q < SP_SEL_LPL; ++q) cm += (l2[q] < mid);
-                    cm = __reduce_add_sync(0xffffffffu, cm);
-                    if (cm <= kkr) { w_lo = mid; c_lo = cm; }
-                    else { w_hi = mid; b_hi = mid; c_hi = cm; }
                 }
-                if (pr.hi != pr.lo && c_hi < kkr + 2) {         // rank kkr + 1 is the smallest element >= w_hi
-                    float nx = INFINITY;
+                float base = par, top = pbr;
+                if (par == plow || pbr == GM_PMAX) {                // unbounded bracket: the list's own value range
+                    float vmn = INFINITY, vmx = -INFINITY;
 #pragma unroll
-                    for (int q = 0; q < SP_SEL_LPL; ++q) if (l2[q] >= w_hi) nx = fminf(nx, l2[q]);
-                    for (int o = 16; o > 0; o >>= 1) nx = fminf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
-                    w_hi = nx;
+                    for (int q = 0; q < SP_SEL_LPL; ++q) if (lx[q] != INFINITY) { vmn = fminf(vmn, lx[q]); vmx = fmaxf(vmx, lx[q]); }
+                    for (int o = 16; o > 0; o >>= 1) {
+                        vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
+                        vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
+                    }
+                    base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
                 }
-                const float hi_edge = (w_hi == INFINITY) ? vmx : w_hi;
-                okr = (w_lo - 2.0f * E > par || par == plow) && (hi_edge + 2.0f * E < pbr || pbr == GM_PMAX);
+                const float bw = (top - base) * (1.0f / 64.0f);
+                const float bsc = (bw > 0.0f) ? 1.0f / bw : 0.0f;
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < SP_SEL_LPL; ++q)
+                    if ((q & 3) * 32 < cseg[q >> 2]) {
+                        if (lx[q] != INFINITY) atomicAdd(&h[min(63, max(0, (int)((lx[q] - base) * bsc)))], 1);
+                    }
+                __syncwarp();
+                const int kkr = pr.lo - c_ar, kkr2 = kkr + (pr.hi - pr.lo);      // ranks wanted inside the list
+                const int h0 = h[2 * lane], h1 = h[2 * lane + 1];
+                __syncwarp();                                       // the counters are cleared again for the warp's next row
+                int incl = h0 + h1;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                const int excl = incl - h0 - h1;
+                const int my_lo = (kkr >= excl && kkr < incl) ? (kkr < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
+                const int my_hi = (kkr2 >= excl && kkr2 < incl) ? (kkr2 < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
+                const unsigned m_lo = __ballot_sync(0xffffffffu, my_lo >= 0), m_hi = __ballot_sync(0xffffffffu, my_hi >= 0);
                 int n_c = 0, kx = 0;
+                okr = m_lo != 0 && m_hi != 0;
                 if (okr) {
-                    const float c_min = w_lo - 2.0f * E;
-                    const float c_max = (w_hi == INFINITY) ? INFINITY : w_hi + 2.0f * E;
-                    int n_below = c_ar;
+                    const int b_lo = __shfl_sync(0xffffffffu, my_lo, __ffs(m_lo) - 1), b_hi = __shfl_sync(0xffffffffu, my_hi, __ffs(m_hi) - 1);
+                    // bin edges with 1 % slack for the rounding of the binning map, then the 2E band
+                    const float w_lo = base + ((float)b_lo - 0.01f) * bw, w_hi = base + ((float)b_hi + 1.01f) * bw;
+                    const float c_min = w_lo - 2.0f * E, c_max = w_hi + 2.0f * E;
+                    // the candidate window must lie strictly inside the list's value range [pa, pb)
+                    okr = (c_min > par || par == plow) && (c_max < pbr || pbr == GM_PMAX);
+                    if (okr) {
+                        int n_below = c_ar;
 #pragma unroll
-                    for (int q = 0; q < SP_SEL_LPL; ++q) {
-                        const bool valid = l2[q] != INFINITY;
-                        const bool below = valid && l2[q] < c_min;
-                        const bool cand = valid && !below && l2[q] <= c_max;
-                        n_below += __popc(__ballot_sync(0xffffffffu, below));
-                        const unsigned mc = __ballot_sync(0xffffffffu, cand);
-                        if (cand) {
-                            const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
-                            if (slot < 32) {
-                                pool_col[r * 32 + slot] = __float_as_int(lst[(q >> 2) * GM_SUBCAP + (q & 3) * 32 + lane].y);
-                                pool_dex[r * 32 + slot] = l2[q];
+                        for (int q = 0; q < SP_SEL_LPL; ++q)
+                            if ((q & 3) * 32 < cseg[q >> 2]) {
+                                const bool valid = lx[q] != INFINITY;
+                                const bool below = valid && lx[q] < c_min;
+                                const bool cand = valid && !below && lx[q] <= c_max;
+                                n_below += __popc(__ballot_sync(0xffffffffu, below));
+                                const unsigned mc = __ballot_sync(0xffffffffu, cand);
+                                if (cand) {
+                                    const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
+                                    if (slot < 32) { pool_col[r * 32 + slot] = ly[q]; pool_dex[r * 32 + slot] = lx[q]; }
+                                }
+                                n_c += __popc(mc);
                             }
-                        }
-                        n_c += __popc(mc);
+                        kx = pr.lo - n_below;
+                        if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) okr = false;
                     }
-                    kx = pr.lo - n_below;
-                    if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) okr = false;
                 }
                 if (lane == 0) {
                     if (okr) { s_nc[r] = n_c; s_kx[r] = kx; }

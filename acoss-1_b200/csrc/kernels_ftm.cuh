@@ -187,3 +187,162 @@ ftm_normalize_kernel(double* __restrict__ shingle, int total)
     norm = sqrt(norm);
     for (int e = threadIdx.x; e < total; e += blockDim.x) s[e] = s[e] / norm;
 }
+
+// =====================================================================================================================
+// EarlyFusionTralie block features (acoss/algorithms/earlyfusion_traile.py:104-150, resize_block :214-247).
+//
+// resize_block(X, i1, i2, n_out) = skimage.transform.resize(X[i1:i2].astype(float64), (n_out, n_feats), anti_aliasing=True,
+// mode='constant').  skimage is an unpinned dependency that is absent here (parity of this stage is UNPINNED); the restatement
+// (oracle/ports.py:resize_block, which uses the real scipy.ndimage.gaussian_filter for step 1) follows skimage 0.15 / 0.16:
+// with f = (i2 - i1) / n_out,
+//   1. Gaussian filter along time only (the feature axis keeps its size: sigma = 0): sigma = max(0, (f - 1) / 2), taps
+//      exp(-k^2 / (2 sigma^2)) for |k| <= int(4 sigma + 0.5), normalised, samples outside the block = 0 (mode='constant');
+//   2. order-1 warp: output frame o samples row r = f (o + 0.5) - 0.5 by linear interpolation between floor(r) and ceil(r),
+//      rows outside [0, n_in - 1] count as 0 (cval).
+// Both steps are fused: an output needs the filtered values of two rows only.  float64 like the reference.
+// =====================================================================================================================
+#define EF_MAXLW 1024           // Gaussian half-width limit (frames)
+
+// normalised Gaussian taps of one resize in shared memory, w[|k|]; returns the half-width.  All threads of the block call it.
+__device__ __forceinline__ int ef_resize_taps(double* w, int n_in, int n_out, int tid, int nthreads)
+{
+    const double f = (double)n_in / (double)n_out;
+    const double sigma = fmax(0.0, (f - 1.0) / 2.0);
+    const int lw = sigma > 1e-15 ? min((int)(4.0 * sigma + 0.5), EF_MAXLW) : 0;
+    __syncthreads();
+    for (int k = tid; k <= lw; k += nthreads) w[k] = lw ? exp(-0.5 / (sigma * sigma) * (double)k * (double)k) : 1.0;
+    __syncthreads();
+    if (tid == 0) {
+        double sum = 0.0;
+        for (int k = -lw; k <= lw; ++k) sum += w[k < 0 ? -k : k];
+        w[EF_MAXLW + 1] = sum;
+    }
+    __syncthreads();
+    const double sum = w[EF_MAXLW + 1];
+    __syncthreads();
+    for (int k = tid; k <= lw; k += nthreads) w[k] = w[k] / sum;
+    __syncthreads();
+    return lw;
+}
+
+__device__ __forceinline__ double ef_resized(const float* __restrict__ X, int64_t row0, int n_in, int n_feat, int c, int n_out, int o,
+                                             const double* __restrict__ w, int lw)
+{
+    const double f = (double)n_in / (double)n_out;
+    const double r = f * ((double)o + 0.5) - 0.5;
+    const double rf = floor(r), rc = ceil(r);
+    const double dr = r - rf;
+    double out = 0.0;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        if (side == 1 && rc == rf) break;               // r is an integer: one sample, weight 1
+        const int rr = (int)(side ? rc : rf);
+        const double wgt = side ? dr : 1.0 - dr;
+        if (rr < 0 || rr > n_in - 1) continue;
+        double g = 0.0;
+        for (int k = -lw; k <= lw; ++k) {
+            const int q = rr + k;
+            if (q < 0 || q >= n_in) continue;
+            double v = (double)X[(row0 + q) * n_feat + c];
+            if (isnan(v)) v = 0.0;                       // mfcc[np.isnan(mfcc)] = 0 (earlyfusion_traile.py:107)
+            g += w[k < 0 ? -k : k] * v;
+        }
+        out += wgt * g;
+    }
+    if (isinf(out) || isnan(out)) out = 0.0;            // ret[np.isinf(ret)] = 0; ret[np.isnan(ret)] = 0
+    return out;
+}
+
+struct EfBlockTask { int64_t frame0_m, frame0_c, out_blk; int32_t i1, i2m, i2c, pad; };   // MFCC frames [i1, i2m), chroma [i1, i2c)
+
+// one CTA per block: resized + z-normalised MFCC block (n_mf frames x n_mfcc), its SSM lower triangle, resized chroma block
+__global__ void __launch_bounds__(256)
+ef_block_features_kernel(const float* __restrict__ mfcc, const float* __restrict__ chroma, const EfBlockTask* __restrict__ tasks, int n_tasks,
+                         int n_mfcc, int n_mf, int n_ch, float* __restrict__ out_mfccs, float* __restrict__ out_ssms, float* __restrict__ out_chromas)
+{
+    extern __shared__ double bsm[];
+    double* x = bsm;                         // [n_mf][n_mfcc]
+    double* colmean = x + n_mf * n_mfcc;     // [n_mfcc]
+    double* rnorm = colmean + n_mfcc;        // [n_mf] row norms, then squared norms of the normalised rows
+    double* taps = rnorm + n_mf;             // [EF_MAXLW + 2]
+    const int tid = threadIdx.x;
+    for (int t = blockIdx.x; t < n_tasks; t += gridDim.x) {
+        const EfBlockTask tk = tasks[t];
+        int lw = ef_resize_taps(taps, tk.i2m - tk.i1, n_mf, tid, blockDim.x);
+        for (int e = tid; e < n_mf * n_mfcc; e += blockDim.x) {
+            const int o = e / n_mfcc, c = e - o * n_mfcc;
+            x[e] = ef_resized(mfcc, tk.frame0_m + tk.i1, tk.i2m - tk.i1, n_mfcc, c, n_mf, o, taps, lw);
+        }
+        __syncthreads();
+        for (int c = tid; c < n_mfcc; c += blockDim.x) {            // x -= np.mean(x, 0)
+            double s = 0.0;
+            for (int o = 0; o < n_mf; ++o) s += x[o * n_mfcc + c];
+            colmean[c] = s / (double)n_mf;
+        }
+        __syncthreads();
+        for (int e = tid; e < n_mf * n_mfcc; e += blockDim.x) x[e] -= colmean[e % n_mfcc];
+        __syncthreads();
+        for (int o = tid; o < n_mf; o += blockDim.x) {              // xn = x / sqrt(sum(x ** 2, 1)), zero norms -> 1
+            double s = 0.0;
+            for (int c = 0; c < n_mfcc; ++c) s += x[o * n_mfcc + c] * x[o * n_mfcc + c];
+            s = sqrt(s);
+            rnorm[o] = s == 0.0 ? 1.0 : s;
+        }
+        __syncthreads();
+        float* om = out_mfccs + tk.out_blk * (int64_t)(n_mf * n_mfcc);
+        for (int e = tid; e < n_mf * n_mfcc; e += blockDim.x) { x[e] = x[e] / rnorm[e / n_mfcc]; om[e] = (float)x[e]; }
+        __syncthreads();
+        for (int o = tid; o < n_mf; o += blockDim.x) {
+            double s = 0.0;
+            for (int c = 0; c < n_mfcc; ++c) s += x[o * n_mfcc + c] * x[o * n_mfcc + c];
+            rnorm[o] = s;
+        }
+        __syncthreads();
+        // get_ssm(xn)[I < J] with I, J = np.meshgrid(pix, pix): entries (r, c), c < r, in row-major order
+        float* os = out_ssms + tk.out_blk * (int64_t)(n_mf * (n_mf - 1) / 2);
+        for (int e = tid; e < n_mf * (n_mf - 1) / 2; e += blockDim.x) {
+            int r = (int)((1.0 + sqrt(1.0 + 8.0 * (double)e)) / 2.0);
+            while (r * (r - 1) / 2 > e) --r;
+            while ((r + 1) * r / 2 <= e) ++r;
+            const int c = e - r * (r - 1) / 2;
+            double dot = 0.0;
+            for (int k = 0; k < n_mfcc; ++k) dot += x[r * n_mfcc + k] * x[c * n_mfcc + k];
+            double d2 = rnorm[r] + rnorm[c] - 2.0 * dot;
+            if (d2 < 0.0) d2 = 0.0;
+            os[e] = (float)sqrt(d2);
+        }
+        float* oc = out_chromas + tk.out_blk * (int64_t)(n_ch * ACOSS_NBINS);
+        lw = ef_resize_taps(taps, tk.i2c - tk.i1, n_ch, tid, blockDim.x);
+        for (int e = tid; e < n_ch * ACOSS_NBINS; e += blockDim.x) {
+            const int o = e / ACOSS_NBINS, c = e - o * ACOSS_NBINS;
+            oc[e] = (float)ef_resized(chroma, tk.frame0_c + tk.i1, tk.i2c - tk.i1, ACOSS_NBINS, c, n_ch, o, taps, lw);
+        }
+    }
+}
+
+// np.median(chroma, axis=0) per track: warp per (track, bin), bisection on the float32 key
+__global__ void __launch_bounds__(128)
+ef_chroma_median_kernel(const float* __restrict__ chroma, const int64_t* __restrict__ frame_off, int n_tracks, float* __restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (wid >= n_tracks * ACOSS_NBINS) return;
+    const int track = wid / ACOSS_NBINS, c = wid - track * ACOSS_NBINS;
+    const int n = (int)(frame_off[track + 1] - frame_off[track]);
+    const float* col = chroma + frame_off[track] * ACOSS_NBINS + c;
+    auto key = [](float f) { const uint32_t b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); };
+    auto kth = [&](int k) {
+        uint32_t ans = 0;
+        for (int bit = 31; bit >= 0; --bit) {
+            const uint32_t cand = ans | (1u << bit);
+            int cnt = 0;
+            for (int j = lane; j < n; j += 32) cnt += (key(col[(int64_t)j * ACOSS_NBINS]) < cand);
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (cnt <= k) ans = cand;
+        }
+        return __uint_as_float((ans & 0x80000000u) ? (ans & 0x7fffffffu) : ~ans);
+    };
+    float med = 0.0f;
+    if (n > 0) med = (n & 1) ? kth(n >> 1) : __fdiv_rn(__fadd_rn(kth((n >> 1) - 1), kth(n >> 1)), 2.0f);
+    if (lane == 0) out[track * ACOSS_NBINS + c] = med;
+}

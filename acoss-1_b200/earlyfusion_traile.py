@@ -9,10 +9,11 @@ same constructor keywords, similarity types ("mfccs", "ssms", "chromas", "early"
 Smith-Waterman x4, kernel early fusion) runs on the GPU through acoss_earlyfusion_pairs; the N x N
 similarity network fusion through acoss_snf.
 
-Not built in this round: computing the blocked features from raw MFCC / chroma / beat onsets
-(`resize_block` needs skimage.transform.resize, absent here).  `load_features`
-therefore serves the reference's own cache files `<prefix>_<i>.h5` (or features injected with
-`set_block_features`) and raises otherwise.
+The blocked features (`load_features`, earlyfusion_traile.py:104-150: beat-synchronous blocks, anti-aliased
+resize, z-normalisation, per-block SSM, chroma blocks and medians) are computed on the GPU too
+(acoss_earlyfusion_block_features), for all uncached tracks in one batch (`preload_features`), and written to
+the reference's cache files `<prefix>_<i>.h5`.  `resize_block` is skimage.transform.resize restated (skimage is
+absent here: that stage's parity is unpinned).
 """
 import os
 
@@ -54,20 +55,43 @@ class EarlyFusion(CoverAlgorithm):
         featio.save("%s_%i.h5" % (self.get_cacheprefix(), i), block_feats)
         self._uploaded = False
 
+    def preload_features(self, indices=None):
+        """Blocked features of every track that is neither in memory nor in the on-disk cache, computed on the device in one
+        batch and written to the reference's cache files."""
+        todo = []
+        for i in (range(self.N) if indices is None else indices):
+            if i in self.all_block_feats:
+                continue
+            filepath = "%s_%i.h5" % (self.get_cacheprefix(), i)
+            if os.path.exists(filepath):
+                self.all_block_feats[i] = featio.load(filepath)
+                CoverAlgorithm.load_features(self, i)      # clique info as a side effect
+            else:
+                todo.append(i)
+        if not todo:
+            return
+        mf, ch, on = [], [], []
+        for i in todo:
+            feats = CoverAlgorithm.load_features(self, i)
+            mf.append(np.ascontiguousarray(np.asarray(feats['mfcc_htk'], np.float32).T))
+            ch.append(np.asarray(feats[self.chroma_type], np.float32))
+            on.append(np.asarray(feats['madmom_features']['onsets']))
+        out = self.context().earlyfusion_block_features(mf, ch, on, blocksize=self.blocksize, mfccs_per_block=self.mfccs_per_block,
+                                                        chromas_per_block=self.chromas_per_block)
+        for i, bf in zip(todo, out):
+            self.all_block_feats[i] = bf
+            featio.save("%s_%i.h5" % (self.get_cacheprefix(), i), bf)
+        self._uploaded = False
+
     def load_features(self, i, do_plot=False):
-        filepath = "%s_%i.h5" % (self.get_cacheprefix(), i)
-        if i in self.all_block_feats:
-            return self.all_block_feats[i]
-        elif os.path.exists(filepath):
-            self.all_block_feats[i] = featio.load(filepath)
-            CoverAlgorithm.load_features(self, i)      # clique info as a side effect
-            return self.all_block_feats[i]
-        raise NotImplementedError("acoss_b200.EarlyFusion: blocked features of song %d are not cached (%s); computing them "
-                                  "from raw features needs skimage.transform.resize (not built, see DESIGN.md)" % (i, filepath))
+        if i not in self.all_block_feats:
+            self.preload_features([i])
+        return self.all_block_feats[i]
 
     def preload(self):
         if self._uploaded:
             return
+        self.preload_features()
         self.context().earlyfusion_upload([self.load_features(i) for i in range(self.N)])
         self._uploaded = True
 

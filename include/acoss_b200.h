@@ -306,6 +306,22 @@ int acoss_earlyfusion_upload(acoss_ctx *ctx, const float *mfccs_host, int32_t d_
                              const float *chroma_med_host, const int64_t *block_offsets_host,
                              int32_t n_tracks);
 
+/* Blocked features of all tracks on the device (replaces the body of EarlyFusion.load_features,
+ * acoss/algorithms/earlyfusion_traile.py:104-150, and resize_block :214-247 = skimage.transform.resize(anti_aliasing=True,
+ * mode='constant'), restated: Gaussian anti-alias filter sigma = (f - 1) / 2 along time + order-1 interpolation; parity of the
+ * resize is UNPINNED, skimage is absent).  Inputs, concatenated over tracks: mfcc (T_t, n_mfcc) float32 (feats['mfcc_htk'].T, NaN -> 0),
+ * chroma (T_t, 12) float32, beat onsets (frame indices).  Per track n_blocks = n_beats - blocksize; per block: MFCC frames
+ * [onset_b, onset_{b+blocksize-1}) resized to mfccs_per_block frames, column-centred, rows L2-normalised -> 'mfccs'; the lower
+ * triangle of their Euclidean SSM -> 'ssms'; chroma frames [onset_b, onset_{b+blocksize}) resized to chromas_per_block -> 'chromas';
+ * np.median(chroma, 0) -> 'chroma_med'.  out_block_offsets_host[n_tracks + 1] is always written; pass NULL for the four feature
+ * outputs to size them first ((n_blocks_total, mfccs_per_block * n_mfcc), (.., mpb (mpb - 1) / 2), (.., 12 cpb), (n_tracks, 12)). */
+int acoss_earlyfusion_block_features(acoss_ctx *ctx, const float *mfcc_host, int32_t n_mfcc, const int64_t *mfcc_offsets_host,
+                                     const float *chroma_host, const int64_t *chroma_offsets_host,
+                                     const int64_t *onsets_host, const int64_t *onset_offsets_host, int32_t n_tracks,
+                                     int32_t blocksize, int32_t mfccs_per_block, int32_t chromas_per_block,
+                                     float *out_mfccs_host, float *out_ssms_host, float *out_chromas_host,
+                                     float *out_chroma_med_host, int64_t *out_block_offsets_host);
+
 /* The body of EarlyFusion.similarity (earlyfusion_traile.py:157-198) for every pair (i, j):
  * get_csm x2, get_csm_blocked_oti(get_csm_cosine), csm_to_binary(kappa), getWCSM(K, K), the early
  * fusion exp(-sum W) and four smith_waterman_constrained scores.

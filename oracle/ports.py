@@ -236,3 +236,59 @@ def simple_features(chroma_T, WIN=200, SKIP=100, win_len_smooth=4):
     length = np.sqrt(np.sum(np.abs(out) ** 2, axis=0, keepdims=True))
     length[length < np.finfo(out.dtype).tiny] = 1.0
     return out / length
+
+
+# ---- acoss/algorithms/earlyfusion_traile.py:104-150, 214-247 ---------------------------------------------------------
+def resize_block(X, i1, i2, frames_per_block):
+    """resize_block (earlyfusion_traile.py:214-247, median_aggregate=False) = skimage.transform.resize(X[i1:i2].astype(float64),
+    (frames_per_block, n_feats), anti_aliasing=True, mode='constant').  skimage is absent from this image (UNPINNED); restated
+    from skimage 0.15 / 0.16: (1) scipy.ndimage.gaussian_filter with sigma = max(0, (factor - 1) / 2) per axis, mode='constant',
+    cval=0 -- the REAL scipy routine is used here; (2) order-1 warp sampling source row factor * (o + 0.5) - 0.5, neighbours
+    outside the image = 0; the final clip to the input range is a no-op for bilinear weights."""
+    import scipy.ndimage as ndi
+    x = np.asarray(X[i1:i2, :], dtype=np.float64)
+    n_in, n_out = x.shape[0], int(frames_per_block)
+    f = float(n_in) / float(n_out)
+    sig = max(0.0, (f - 1.0) / 2.0)
+    g = ndi.gaussian_filter(x, (sig, 0.0), mode='constant', cval=0.0)
+    r = f * (np.arange(n_out) + 0.5) - 0.5
+    rf, rc = np.floor(r).astype(int), np.ceil(r).astype(int)
+    dr = r - rf
+
+    def rows(idx):
+        ok = (idx >= 0) & (idx <= n_in - 1)
+        out = np.zeros((n_out, x.shape[1]))
+        out[ok] = g[idx[ok]]
+        return out
+    ret = (1.0 - dr)[:, None] * rows(rf) + np.where(rc != rf, dr, 0.0)[:, None] * rows(rc)
+    ret[np.isinf(ret)] = 0
+    ret[np.isnan(ret)] = 0
+    return ret
+
+
+def early_block_features(mfcc_htk, chroma, onsets, blocksize=20, mfccs_per_block=50, chromas_per_block=40):
+    """EarlyFusion.load_features (earlyfusion_traile.py:104-150) for one track: mfcc_htk (n_mfcc, T), chroma (T, 12), onsets."""
+    mfcc = np.array(mfcc_htk).T
+    mfcc[np.isnan(mfcc)] = 0
+    n_blocks = len(onsets) - blocksize
+    bf = {'mfccs': np.zeros((n_blocks, mfccs_per_block * mfcc.shape[1]), np.float32)}
+    pix = np.arange(mfccs_per_block)
+    I, J = np.meshgrid(pix, pix)
+    bf['ssms'] = np.zeros((n_blocks, mfccs_per_block * (mfccs_per_block - 1) // 2), np.float32)
+    for b in range(n_blocks):
+        x = resize_block(mfcc, onsets[b], onsets[b + blocksize - 1], mfccs_per_block)
+        x -= np.mean(x, 0)[None, :]
+        xnorm = np.sqrt(np.sum(x ** 2, 1))[:, None]
+        xnorm[xnorm == 0] = 1
+        xn = x / xnorm
+        bf['mfccs'][b, :] = xn.flatten()
+        sq = np.sum(xn ** 2, 1)                                  # get_ssm (cross_recurrence.py:10-28)
+        D = sq[:, None] + sq[None, :] - 2 * xn.dot(xn.T)
+        D[D < 0] = 0
+        np.fill_diagonal(D, 0)
+        bf['ssms'][b, :] = np.sqrt(D)[I < J]
+    bf['chromas'] = np.zeros((n_blocks, chromas_per_block * chroma.shape[1]), np.float32)
+    bf['chroma_med'] = np.median(chroma, axis=0)
+    for b in range(n_blocks):
+        bf['chromas'][b, :] = resize_block(chroma, onsets[b], onsets[b + blocksize], chromas_per_block).flatten()
+    return bf

@@ -780,6 +780,61 @@ def test_earlyfusion_large_vs_reference_golden(ctx, golden):
     assert n_diff_total <= 8
 
 
+def _raw_early_tracks(seed, n_tracks):
+    """raw inputs of EarlyFusion.load_features: mfcc_htk (20, T) with a few NaNs, chroma (T, 12), beat onsets"""
+    rng = np.random.default_rng(seed)
+    out = []
+    for t in range(n_tracks):
+        T = int(rng.integers(1500, 2200))
+        mf = (np.cumsum(rng.standard_normal((20, T)), 1) * 0.1 + rng.standard_normal((20, T))).astype(np.float32)
+        mf[rng.integers(0, 20), rng.integers(0, T)] = np.nan
+        ch = rng.random((T, 12)).astype(np.float32)
+        gaps = rng.integers(18, 45, size=T // 18 + 2)            # 18-44 frames per beat: blocks of ~ 360-880 frames -> 50 / 40
+        on = np.cumsum(gaps)
+        out.append((mf, ch, on[on < T - 1].astype(np.int64)))
+    return out
+
+
+def test_earlyfusion_block_features_vs_port(ctx, workdir):
+    """EarlyFusion.load_features on the device (blocks, anti-aliased resize, z-normalisation, SSM triangle, chroma blocks, chroma
+    median) against oracle/ports.py:early_block_features -- a restatement whose resize uses the real scipy.ndimage Gaussian
+    filter and restates skimage's order-1 warp (skimage is absent: this stage's parity is UNPINNED).  float32 outputs of float64
+    arithmetic: rtol 2e-6 (summation order of the 20- / 50-term sums), SSM entries near 0 to 2e-6 absolute.  Then the class:
+    benchmark(\"EarlyFusionTraile\") runs from a RAW feature directory."""
+    import acoss_b200
+    from acoss_b200 import synth
+    from oracle import ports as P
+    raw = _raw_early_tracks(11, 3)
+    got = ctx.earlyfusion_block_features([m.T for m, _, _ in raw], [c for _, c, _ in raw], [o for _, _, o in raw])
+    for (mf, ch, on), g in zip(raw, got):
+        exp = P.early_block_features(mf, ch, on)
+        assert g["mfccs"].shape == exp["mfccs"].shape == (len(on) - 20, 1000)
+        np.testing.assert_allclose(g["mfccs"], exp["mfccs"], rtol=2e-6, atol=1e-7)
+        np.testing.assert_allclose(g["ssms"], exp["ssms"], rtol=2e-6, atol=2e-6)
+        np.testing.assert_allclose(g["chromas"], exp["chromas"], rtol=2e-6, atol=1e-7)
+        assert np.array_equal(g["chroma_med"], exp["chroma_med"])
+    # upsampling blocks (fewer frames than output rows: no anti-alias filter, zero-padded borders)
+    short = [(raw[0][0][:, :400], raw[0][1][:400], np.arange(0, 400, 2).astype(np.int64))]
+    g2 = ctx.earlyfusion_block_features([short[0][0].T], [short[0][1]], [short[0][2]])[0]
+    e2 = P.early_block_features(*short[0])
+    np.testing.assert_allclose(g2["mfccs"], e2["mfccs"], rtol=2e-6, atol=1e-7)
+    np.testing.assert_allclose(g2["chromas"], e2["chromas"], rtol=2e-6, atol=1e-7)
+    with pytest.raises(acoss_b200.AcossError) as e:
+        ctx.earlyfusion_block_features([raw[0][0].T], [raw[0][1]], [raw[0][2][:15]])
+    assert e.value.code == -3
+    # the entry point from raw feature files (12 tracks: K + 1 = 21 neighbours need more than 21 songs for the fusion -> 24)
+    raw = _raw_early_tracks(12, 24)
+    labels = ["W_%d" % (k // 2) for k in range(24)]
+    ds = dict(labels=labels, work_ids=labels, track_ids=["P_%d" % k for k in range(24)], hpcp=[c for _, c, _ in raw], fac=1)
+    extra = {"mfcc_htk": [m for m, _, _ in raw], "madmom_features": [{"onsets": o} for _, _, o in raw]}
+    fdir = synth.write_dataset(str(workdir / "feat"), ds, str(workdir / "ds.csv"), extra=extra)
+    res = acoss_b200.benchmark(str(workdir / "ds.csv"), fdir, algorithm="EarlyFusionTraile", shortname="raw")
+    assert set(res) == {"mfccs", "ssms", "chromas", "early", "late", "early+late"}
+    e = acoss_b200.EarlyFusion(str(workdir / "ds.csv"), fdir, shortname="raw")
+    f5 = e.load_features(5)                                    # served from the cache file written by the run above
+    np.testing.assert_allclose(f5["mfccs"], P.early_block_features(*raw[5])["mfccs"], rtol=2e-6, atol=1e-7)
+
+
 def test_earlyfusion_class_matches_reference_golden(golden, workdir):
     import acoss_b200
     g = golden("earlyfusion_reference.npz")
