@@ -4,7 +4,7 @@ acoss_b200 -- B200-native implementation of acoss's all-pairs cover-song-similar
 behind the reference's CoverAlgorithm API.  The directory is named `acoss-1_b200`; import it as
 `acoss_b200` through the shim module at the repository root.
 """
-from . import coverid, synth, featio, utils
+from . import coverid, synth, featio, utils, algorithm_utils
 from ._lib import AcossError, Context, load_library, LIB_PATH
 from .algorithm_template import CoverAlgorithm
 from .coverid import algorithm_names, benchmark

@@ -81,6 +81,14 @@ SYMBOLS = {
     "acoss_ftm2d_allpairs": (ctypes.c_int, [c_vp, c_f64p, ctypes.c_int32, ctypes.c_int32, c_f64p]),
     "acoss_ftm2d_shingles": (ctypes.c_int, [c_vp, c_f32p, c_i64p, c_i64p, c_i64p, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
                                             ctypes.c_double, c_f64p]),
+    "acoss_serra09_topk": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int32, c_i32p, ctypes.c_int32, ctypes.POINTER(CrpParams), ctypes.c_int32,
+                                          ctypes.c_int32, ctypes.c_int32, c_i32p, c_f32p]),
+    "acoss_snf_ex": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                    ctypes.c_double, c_f64p, c_vp, c_f64p, c_f64p]),
+    "acoss_csm": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, c_f32p]),
+    "acoss_oti": (ctypes.c_int, [c_vp, c_f32p, c_f32p, ctypes.c_int32, c_i32p]),
+    "acoss_csm_to_binary": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, ctypes.c_int32, ctypes.c_double, c_u8p]),
+    "acoss_wcsm": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, c_f32p]),
     "acoss_earlyfusion_block_features": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_i64p, c_f32p, c_i64p, c_i64p, c_i64p, ctypes.c_int32,
                                                         ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, c_f32p, c_f32p, c_f32p, c_f32p, c_i64p]),
     "acoss_earlyfusion_upload": (ctypes.c_int, [c_vp, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32, c_f32p, ctypes.c_int32,
@@ -218,6 +226,19 @@ class Context(object):
         self._ck(self.lib.acoss_serra09_pairs_dev(self.h, _ptr(pairs, ctypes.c_int32), pairs.shape[0], ctypes.byref(params),
                                                   c_vp(out_q_ptr or 0), c_vp(out_d_ptr or 0)))
 
+    def serra09_topk(self, queries, db, k, params=None, which="qmax", norm="serra09"):
+        """Per-query top-k of queries x db (track indices of the uploaded store) without the Q x N matrix: returns
+        (idx (Q, k) int32 positions in `db`, -1 = none; score (Q, k) float32).  which: 'qmax' | 'dmax';
+        norm: None (raw, higher first) | 'serra09' (score / sqrt(len), higher first) | 'chen' (sqrt(len) / score, lower first)."""
+        params = params or self.params()
+        queries = _np(queries, np.int32).ravel(); db = _np(db, np.int32).ravel()
+        idx = np.zeros((len(queries), int(k)), np.int32)
+        sc = np.zeros((len(queries), int(k)), np.float32)
+        self._ck(self.lib.acoss_serra09_topk(self.h, _ptr(queries, ctypes.c_int32), len(queries), _ptr(db, ctypes.c_int32), len(db),
+                                             ctypes.byref(params), {"qmax": 0, "dmax": 1}[which], {None: -1, "serra09": 0, "chen": 1}[norm],
+                                             int(k), _ptr(idx, ctypes.c_int32), _ptr(sc, ctypes.c_float)))
+        return idx, sc
+
     def pair_stats(self):
         s = PairStats()
         self._ck(self.lib.acoss_get_pair_stats(self.h, ctypes.byref(s)))
@@ -306,6 +327,55 @@ class Context(object):
         self._ck(self.lib.acoss_snf(self.h, stack.ctypes.data_as(c_vp), 0 if dt == np.float32 else 1, nm, n, int(K), int(niters),
                                     float(reg_diag), _ptr(fused, ctypes.c_double), Ws.ctypes.data_as(c_vp) if want_Ws else None))
         return ([Ws[k] for k in range(nm)] if want_Ws else None), fused
+
+    def snf_stages(self, mats, K, niters=0, reg_diag=1, affinities=False, want=("fused",)):
+        """acoss_snf_ex: the stages of doSimilarityFusion on a list of (n, n) matrices (distances, or affinities when
+        `affinities`).  `want` names the outputs: 'fused', 'Ws', 'P', 'S' (S dense).  Returns a dict."""
+        dt = np.float64 if any(np.asarray(m).dtype == np.float64 for m in mats) else np.float32
+        stack = np.ascontiguousarray(np.stack([np.asarray(m, dtype=dt) for m in mats]))
+        nm, n = stack.shape[0], stack.shape[1]
+        if stack.ndim != 3 or stack.shape[2] != n:
+            raise ValueError("square matrices expected")
+        out = {}
+        if "fused" in want: out["fused"] = np.zeros((n, n), np.float64)
+        if "Ws" in want: out["Ws"] = np.zeros_like(stack)
+        if "P" in want: out["P"] = np.zeros((nm, n, n), np.float64)
+        if "S" in want: out["S"] = np.zeros((nm, n, n), np.float64)
+        self._ck(self.lib.acoss_snf_ex(self.h, stack.ctypes.data_as(c_vp), 0 if dt == np.float32 else 1, 1 if affinities else 0, nm, n,
+                                       int(K), int(niters), float(reg_diag), _ptr(out.get("fused"), ctypes.c_double),
+                                       out["Ws"].ctypes.data_as(c_vp) if "Ws" in out else None,
+                                       _ptr(out.get("P"), ctypes.c_double), _ptr(out.get("S"), ctypes.c_double)))
+        return out
+
+    # ---- free functions of acoss/algorithms/utils ------------------------------------------
+    def csm(self, X, Y, cosine=False, roll=0):
+        """get_csm / get_csm_cosine (roll: get_csm_blocked_oti's shift of X) -> (M, N) float32."""
+        X = _np(X, np.float32); Y = _np(Y, np.float32)
+        if X.ndim != 2 or Y.ndim != 2 or X.shape[1] != Y.shape[1]:
+            raise ValueError("X (M, d) and Y (N, d) expected")
+        out = np.zeros((X.shape[0], Y.shape[0]), np.float32)
+        self._ck(self.lib.acoss_csm(self.h, _ptr(X, ctypes.c_float), X.shape[0], _ptr(Y, ctypes.c_float), Y.shape[0], X.shape[1],
+                                    1 if cosine else 0, int(roll), _ptr(out, ctypes.c_float)))
+        return out
+
+    def oti(self, C1, C2):
+        """get_oti for (n, 12) float32 pairs of chroma vectors -> int32 (n,)."""
+        C1 = _np(C1, np.float32).reshape(-1, 12); C2 = _np(C2, np.float32).reshape(-1, 12)
+        out = np.zeros(len(C1), np.int32)
+        self._ck(self.lib.acoss_oti(self.h, _ptr(C1, ctypes.c_float), _ptr(C2, ctypes.c_float), len(C1), _ptr(out, ctypes.c_int32)))
+        return out
+
+    def csm_to_binary(self, D, kappa):
+        D = _np(D, np.float32)
+        out = np.zeros(D.shape, np.uint8)
+        self._ck(self.lib.acoss_csm_to_binary(self.h, _ptr(D, ctypes.c_float), D.shape[0], D.shape[1], float(kappa), _ptr(out, ctypes.c_uint8)))
+        return out
+
+    def wcsm(self, C, k1, k2):
+        C = _np(C, np.float32)
+        out = np.zeros(C.shape, np.float32)
+        self._ck(self.lib.acoss_wcsm(self.h, _ptr(C, ctypes.c_float), C.shape[0], C.shape[1], int(k1), int(k2), _ptr(out, ctypes.c_float)))
+        return out
 
     # ---- SiMPle / FTM2D ---------------------------------------------------------------
     def simple_preprocess(self, raw, win=200, skip=100, win_len_smooth=4):

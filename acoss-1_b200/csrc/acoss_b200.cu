@@ -24,6 +24,7 @@
 #include "kernels_early.cuh"
 #include "kernels_early_tc.cuh"
 #include "kernels_ftm.cuh"
+#include "kernels_topk.cuh"
 
 static std::string g_create_error;
 
@@ -64,6 +65,7 @@ struct acoss_ctx {
     DevBuf d_opb, d_opn, d_op_off, d_sdmax, d_piv, d_cnt4, d_lcnt, d_slists, d_edges, d_fb;
     bool have_split = false;
     int64_t split_launches = 0;
+    int count_hh = 0;                 // phase-split count pass on the hi.hi product alone ("count_hh")
     int auto_split = 0;               // crp_mode 0 picks the phase-split pipeline (acoss_ctx_set_option "auto_split")
     // SiMPle feature store (frame-major float64) + per-track chroma profiles
     int sp_tracks = 0;
@@ -166,6 +168,7 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
         ctx->crp_budget = (size_t)value;
         return ACOSS_OK;
     }
+    if (k == "count_hh") { ctx->count_hh = value != 0; return ACOSS_OK; }
     if (k == "auto_split") { ctx->auto_split = value != 0; return ACOSS_OK; }
     if (k == "ef_simt_csm") { ctx->ef_force_simt = value != 0; return ACOSS_OK; }
     if (k == "inject_alloc_failures") {
@@ -370,6 +373,7 @@ extern "C" int acoss_median_downsample(acoss_ctx* ctx, const float* raw_frames_h
 #include "api_simple.inc"
 #include "api_early.inc"
 #include "api_features.inc"
+#include "api_topk.inc"
 
 // ---------------------------------------------------------------------------
 // Allocation-free variant of acoss_cover_similarity_from_crp (no counterpart in the reference: added

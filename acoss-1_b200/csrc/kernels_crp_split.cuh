@@ -34,6 +34,11 @@
 #define SP_EDGE_SLOTS 6                      // column-edge ring (see crp_stream_kernel: >= 5 slots make the reuse safe)
 #define SP_AMB_CAP 8192                      // ambiguous cells per strip before the exact-everything path
 #define SP_LIST_STRIDE (4 * GM_SUBCAP)       // float2 entries per row
+// crp_stream_kernel<2>: count pass on the hi.hi product alone (14 MMAs per tile instead of 41), see SP_EPS_REL_HH; context option "count_hh"
+// Error bound of the hi.hi-only radicand against the oracle's, relative to xx + yy: TF32 rounding of both operands (unit roundoff
+// 2^-11 each) gives |x_h.y_h - x.y| <= (2^-10 + 2^-22) sum |x_k y_k| <= 2^-11 (xx + yy); the radicand carries -2 x.y: 2^-10 (xx + yy);
+// plus the three-product bound GM_EPS_REL = 2^-13 for everything else (norms, accumulation, the oracle's own rounding).  1.25 x 2^-10.
+#define SP_EPS_REL_HH 1.220703125e-03f
 #define SP_SEL_THREADS 256
 #define SP_SEL_WARPS (SP_SEL_THREADS / 32)
 #define SP_SEL_LPL (SP_LIST_STRIDE / 32)     // list entries per lane in the selection kernel
@@ -110,13 +115,14 @@ __global__ void sp_sdmax_kernel(const int32_t* __restrict__ emb_len, const int64
 }
 
 // per-pair error bound and "unbounded below" pivot: functions of the two tracks only, so that all four kernels agree
-struct SpPairBound { float E, plow; };
+struct SpPairBound { float E, plow, E_hh; };      // E: three-product streams; E_hh: the hi.hi-only count pass
 __device__ __forceinline__ SpPairBound sp_pair_bound(const PairDesc& pd, const float* __restrict__ sdmax)
 {
     const int rot = pd.oti % ACOSS_NBINS;
     const float s = __ldg(sdmax + pd.q * ACOSS_NBINS) + __ldg(sdmax + pd.r * ACOSS_NBINS + rot);
     SpPairBound b;
     b.E = GM_EPS_REL * s;
+    b.E_hh = SP_EPS_REL_HH * s;
     b.plow = -(4.0f * s + 1.0e-30f);
     return b;
 }
@@ -145,6 +151,23 @@ __device__ __forceinline__ void sp_stage_a(unsigned char* Apl, const float* __re
         if (tid < nrows) { tf32_split(sdA[row0 + tid], nv.x, nv.y); nv.z = 1.0f; nv.w = 1.0f; }
         *reinterpret_cast<float4*>(Apl + 6 * GM_APLANE + tid * 16) = nv;
     }
+}
+
+// the 14 MMAs of the hi.hi product of one 128 x 256 tile (operand layouts of gm_issue_tile: A planes H0 H1 H2 L0 L1 L2 NRM,
+// B planes L0 L1 L2 H0 H1 H2 NRM)
+__device__ __forceinline__ void sp_issue_tile_hh(uint32_t d_tmem, uint32_t a0, uint32_t b0)
+{
+    const uint32_t al = (a0 & 0x3FFFFu) >> 4, bl = (b0 & 0x3FFFFu) >> 4;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int c3 = 0; c3 < 3; ++c3)
+#pragma unroll
+        for (int kp = 0; kp < 4; ++kp) {
+            gm_mma(d_tmem, GM_DLO(al, c3 * GM_APLANE + 32 * kp, 16), GM_DLO(bl, (3 + c3) * GM_BPLANE + 32 * kp, 16), acc);
+            acc = 1;
+        }
+    gm_mma(d_tmem, GM_DLO(al, 128, GM_APLANE), GM_DLO(bl, 3 * GM_BPLANE + 128, GM_BPLANE), 1);                                        // (H0,H0) (H1,H1), offset 8
+    gm_mma(d_tmem, GM_DLO(al, 2 * GM_APLANE + 128, 4 * GM_APLANE - 128), GM_DLO(bl, 5 * GM_BPLANE + 128, GM_BPLANE - 128), 1);        // (H2,H2) norms
 }
 
 // geometry of one strip task, shared by all kernels
@@ -341,7 +364,7 @@ crp_pivot_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict
 }
 
 // =====================================================================================================================
-// K2 / K4: the streaming kernels.  MODE 0 = count pass, MODE 1 = binarise pass (pass 2 only).
+// K2 / K4: the streaming kernels.  MODE 0 = count pass, MODE 2 = count pass on hi.hi alone, MODE 1 = binarise pass (pass 2 only).
 //   warps 0..15  epilogue: thread (row = 32 lq + lane, column group cg) reads its 4 x 16 accumulator columns of every tile
 //   warp 16      MMA issuer: 41 tcgen05.mma per tile from one elected lane, commits to tmem_full[] and b_empty[]
 //   warp 17      TMA producer: 7 (8) cp.async.bulk per tile -- six operand planes, the norm plane (and the column edges) --
@@ -357,9 +380,9 @@ template <int MODE> struct SpStreamSmem {
     static constexpr int A_OFF = 0;
     static constexpr int B_OFF = 2 * GM_A_BYTES;
     static constexpr int EDGE_OFF = B_OFF + SP_NB_RING * GM_B_BYTES;
-    static constexpr int ARAW_OFF = EDGE_OFF + (MODE ? SP_EDGE_SLOTS * GM_TN * 4 : 0);
-    static constexpr int AMB_OFF = ARAW_OFF + (MODE ? GM_ARAW_BYTES : 0);
-    static constexpr int ROWV_OFF = AMB_OFF + (MODE ? SP_AMB_CAP * 4 : 0);
+    static constexpr int ARAW_OFF = EDGE_OFF + (MODE == 1 ? SP_EDGE_SLOTS * GM_TN * 4 : 0);
+    static constexpr int AMB_OFF = ARAW_OFF + (MODE == 1 ? GM_ARAW_BYTES : 0);
+    static constexpr int ROWV_OFF = AMB_OFF + (MODE == 1 ? SP_AMB_CAP * 4 : 0);
     static constexpr int MBAR_OFF = ROWV_OFF + 4 * GM_ROWV_BYTES;           // s_xx s_th s_loq + spare
     static constexpr int BYTES = MBAR_OFF + 16 * 8 + 64;
 };
@@ -409,7 +432,7 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     const uint32_t a_saddr = smem_u32(Apl), b_saddr = smem_u32(Bbuf);
 
     // tiny strips (NB < GM_MIN_NB) have no count pass: every role skips them the same way
-    auto skip = [&](const PairDesc& pd) { return MODE == 0 && (side_a_is_query ? pd.N : pd.M) < GM_MIN_NB; };
+    auto skip = [&](const PairDesc& pd) { return MODE != 1 && (side_a_is_query ? pd.N : pd.M) < GM_MIN_NB; };
 
     if (warp == GM_WARPS + 1) {
         // ================= TMA producer =================
@@ -427,22 +450,23 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 const size_t P = (size_t)GM_TN * ntb + 8;
                 const unsigned char* pl = opb + op_off[2 * trackB];
                 const unsigned char* nr = opn + op_off[2 * trackB + 1] + (size_t)rotB * GM_TN * ntb * 16;
-                const float* ed = MODE ? edges + pd.edge_off : nullptr;
+                const float* ed = MODE == 1 ? edges + pd.edge_off : nullptr;
                 for (int t = 0; t < n_tiles; ++t, ++g) {
                     const uint32_t sb = g % SP_NB_RING;
                     if (g >= SP_NB_RING) mbar_wait(mb_bempty + sb, ((g / SP_NB_RING) - 1) & 1u);
                     unsigned char* dst = Bbuf + sb * GM_B_BYTES;
-                    const uint32_t total = 6 * GM_BPLANE + GM_TN * 16 + (MODE ? GM_TN * 4 : 0);
+                    constexpr int P0 = (MODE == 2) ? 3 : 0;          // hi.hi count pass: the H planes only
+                    const uint32_t total = (6 - P0) * GM_BPLANE + GM_TN * 16 + (MODE == 1 ? GM_TN * 4 : 0);
                     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mb_bfull + sb)), "r"(total) : "memory");
 #pragma unroll
-                    for (int p = 0; p < 6; ++p)
+                    for (int p = P0; p < 6; ++p)
                         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                                      ::"r"(smem_u32(dst + p * GM_BPLANE)), "l"(pl + ((size_t)p * P + (size_t)GM_TN * t) * 16),
                                        "r"((uint32_t)GM_BPLANE), "r"(smem_u32(mb_bfull + sb)) : "memory");
                     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                                  ::"r"(smem_u32(dst + 6 * GM_BPLANE)), "l"(nr + (size_t)GM_TN * t * 16),
                                    "r"((uint32_t)(GM_TN * 16)), "r"(smem_u32(mb_bfull + sb)) : "memory");
-                    if (MODE)
+                    if (MODE == 1)
                         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                                      ::"r"(smem_u32(loC + (g % SP_EDGE_SLOTS) * GM_TN)), "l"(ed + (size_t)GM_TN * t),
                                        "r"((uint32_t)(GM_TN * 4)), "r"(smem_u32(mb_bfull + sb)) : "memory");
@@ -466,7 +490,8 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 if (g >= 2) mbar_wait(mb_tempty + buf, ((g >> 1) - 1) & 1u);
                 tc_fence_after();
                 if (gm_elect_one()) {
-                    gm_issue_tile(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES);
+                    if (MODE == 2) sp_issue_tile_hh(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES);
+                    else gm_issue_tile(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES);
                     umma_commit(mb_tfull + buf);
                     umma_commit(mb_bempty + sb);
                 }
@@ -502,7 +527,7 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
             const bool rowvalid = myrow < tk.nrows;
             const int nxt = next_task(task + gridDim.x);
             float E = 0.0f;
-            if (MODE) {
+            if (MODE == 1) {
                 E = sp_pair_bound(pd, sdmax).E;
                 gm_csync();                          // the previous strip's exact chains are done with Araw / amb / s_*
                 for (int e = tid; e < (GM_ROWS + 8) * ACOSS_NBINS; e += GM_THREADS) {
@@ -520,9 +545,9 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 if (tid == 0) *amb_cnt = 0;
             }
             if (nxt < n_tasks) stage(nxt, (i + 1) & 1);
-            if (MODE) gm_csync();
+            if (MODE == 1) gm_csync();
 
-            if (MODE == 0) {
+            if (MODE != 1) {
                 // ---- count pass: c_a = #(rho~ < pa); elements of [pa, pb) go to the row's list.  d = rho~ - pa: "below" is the
                 //      sign bit of d, "inside [pa, pb)" is one unsigned compare of d's bit pattern against that of pb - pa.
                 const size_t srow = (size_t)task * GM_ROWS + myrow;
@@ -700,12 +725,12 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 // =====================================================================================================================
 #define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * GM_ROWS * 32 * 4 + SP_SEL_WARPS * 64 * 4)
 
-__global__ void __launch_bounds__(SP_SEL_THREADS, 4)
+__global__ void __launch_bounds__(SP_SEL_THREADS, 3)
 crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
                   const float* __restrict__ frames, const float* __restrict__ selfdot, const float* __restrict__ sdmax,
                   float* __restrict__ thr, int side_a_is_query, float qf,
                   const float2* __restrict__ piv, const int* __restrict__ cnt4, const int* __restrict__ lcnt,
-                  const float2* __restrict__ lists, float* __restrict__ fb_scratch, int fb_stride,
+                  const float2* __restrict__ lists, float* __restrict__ fb_scratch, int fb_stride, int count_hh,
                   unsigned long long* __restrict__ counters)
 {
     extern __shared__ __align__(16) unsigned char ssm[];
@@ -729,7 +754,7 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         const int rot = g.rot, NB = g.NB;
         const PercentileRank pr = percentile_rank(NB, qf);
         const SpPairBound pbd = sp_pair_bound(pd, sdmax);
-        const float E = pbd.E, plow = pbd.plow;
+        const float E = count_hh ? pbd.E_hh : pbd.E, plow = pbd.plow;
         float* thr_out = thr + (side_a_is_query ? pd.thr_q_off : pd.thr_r_off);
         const bool tiny = NB < GM_MIN_NB;
         __syncthreads();
@@ -777,8 +802,12 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                         if (sl < cseg[q >> 2]) { const float2 e = lst[(q >> 2) * GM_SUBCAP + sl]; lx[q] = e.x; ly[q] = __float_as_int(e.y); }
                     }
                 }
+                // value range of the list: the bracket, or the list's own extremes where the bracket is open-ended
                 float base = par, top = pbr;
-                if (par == plow || pbr == GM_PMAX) {                // unbounded bracket: the list's own value range
+                uint32_t act = 0;                                   // slots still inside the window
+#pragma unroll
+                for (int q = 0; q < SP_SEL_LPL; ++q) act |= (uint32_t)(lx[q] != INFINITY) << q;
+                if (par == plow || pbr == GM_PMAX) {
                     float vmn = INFINITY, vmx = -INFINITY;
 #pragma unroll
                     for (int q = 0; q < SP_SEL_LPL; ++q) if (lx[q] != INFINITY) { vmn = fminf(vmn, lx[q]); vmx = fmaxf(vmx, lx[q]); }
@@ -788,31 +817,65 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     }
                     base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
                 }
-                const float bw = (top - base) * (1.0f / 64.0f);
-                const float bsc = (bw > 0.0f) ? 1.0f / bw : 0.0f;
-                __syncwarp();
+                int klo = pr.lo - c_ar, khi = klo + (pr.hi - pr.lo);                // ranks wanted among the active slots
+                float w_lo = base, w_hi = top;
+                okr = true;
+                // up to three rounds: histogram the active slots over [base, top), keep the bin(s) holding the wanted ranks, shrink the
+                // window to the actual extremes of what is left.  One round leaves ~list/64 slots; it stops at <= 6.
+                for (int round = 0; round < 3; ++round) {
+                    const float bw = (top - base) * (1.0f / 64.0f);
+                    const float bsc = (bw > 0.0f) ? 1.0f / bw : 0.0f;
+                    h[lane] = 0; h[lane + 32] = 0;
+                    __syncwarp();
+                    uint32_t binw[(SP_SEL_LPL + 3) / 4];                            // 6 + 2 bits per slot: four slots per word
 #pragma unroll
-                for (int q = 0; q < SP_SEL_LPL; ++q)
-                    if ((q & 3) * 32 < cseg[q >> 2]) {
-                        if (lx[q] != INFINITY) atomicAdd(&h[min(63, max(0, (int)((lx[q] - base) * bsc)))], 1);
+                    for (int q = 0; q < (SP_SEL_LPL + 3) / 4; ++q) binw[q] = 0;
+#pragma unroll
+                    for (int q = 0; q < SP_SEL_LPL; ++q)
+                        if ((q & 3) * 32 < cseg[q >> 2]) {
+                            if (act & (1u << q)) {
+                                const int b = min(63, max(0, (int)((lx[q] - base) * bsc)));
+                                binw[q >> 2] |= (uint32_t)b << (8 * (q & 3));
+                                atomicAdd(&h[b], 1);
+                            }
+                        }
+                    __syncwarp();
+                    const int h0 = h[2 * lane], h1 = h[2 * lane + 1];
+                    __syncwarp();
+                    int incl = h0 + h1;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                    const int excl = incl - h0 - h1;
+                    const int my_lo = (klo >= excl && klo < incl) ? (klo < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
+                    const int my_hi = (khi >= excl && khi < incl) ? (khi < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
+                    const unsigned m_lo = __ballot_sync(0xffffffffu, my_lo >= 0), m_hi = __ballot_sync(0xffffffffu, my_hi >= 0);
+                    if (m_lo == 0 || m_hi == 0) { okr = false; break; }
+                    const int l_lo = __ffs(m_lo) - 1, l_hi = __ffs(m_hi) - 1;
+                    const int b_lo = __shfl_sync(0xffffffffu, my_lo, l_lo), b_hi = __shfl_sync(0xffffffffu, my_hi, l_hi);
+                    // slots below bin b_lo leave the rank; the window keeps bins b_lo .. b_hi
+                    const int below_pair = __shfl_sync(0xffffffffu, excl, l_lo), h0_lo = __shfl_sync(0xffffffffu, h0, l_lo);
+                    const int n_below_bin = below_pair + ((b_lo & 1) ? h0_lo : 0);
+                    const int incl_hi = __shfl_sync(0xffffffffu, incl, l_hi), h1_hi = __shfl_sync(0xffffffffu, h1, l_hi);
+                    const int n_upto_bin = incl_hi - ((b_hi & 1) ? 0 : h1_hi);
+                    klo -= n_below_bin; khi -= n_below_bin;
+                    float vmn = INFINITY, vmx = -INFINITY;
+#pragma unroll
+                    for (int q = 0; q < SP_SEL_LPL; ++q)
+                        if ((q & 3) * 32 < cseg[q >> 2]) {
+                            const int b = (binw[q >> 2] >> (8 * (q & 3))) & 0xFF;
+                            if ((act & (1u << q)) && b >= b_lo && b <= b_hi) { vmn = fminf(vmn, lx[q]); vmx = fmaxf(vmx, lx[q]); }
+                            else act &= ~(1u << q);
+                        }
+                    for (int o = 16; o > 0; o >>= 1) {
+                        vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
+                        vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
                     }
-                __syncwarp();
-                const int kkr = pr.lo - c_ar, kkr2 = kkr + (pr.hi - pr.lo);      // ranks wanted inside the list
-                const int h0 = h[2 * lane], h1 = h[2 * lane + 1];
-                __syncwarp();                                       // the counters are cleared again for the warp's next row
-                int incl = h0 + h1;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
-                const int excl = incl - h0 - h1;
-                const int my_lo = (kkr >= excl && kkr < incl) ? (kkr < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
-                const int my_hi = (kkr2 >= excl && kkr2 < incl) ? (kkr2 < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
-                const unsigned m_lo = __ballot_sync(0xffffffffu, my_lo >= 0), m_hi = __ballot_sync(0xffffffffu, my_hi >= 0);
+                    w_lo = vmn; w_hi = vmx;
+                    if (n_upto_bin - n_below_bin <= 6 || !(vmx > vmn)) break;
+                    base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
+                }
                 int n_c = 0, kx = 0;
-                okr = m_lo != 0 && m_hi != 0;
                 if (okr) {
-                    const int b_lo = __shfl_sync(0xffffffffu, my_lo, __ffs(m_lo) - 1), b_hi = __shfl_sync(0xffffffffu, my_hi, __ffs(m_hi) - 1);
-                    // bin edges with 1 % slack for the rounding of the binning map, then the 2E band
-                    const float w_lo = base + ((float)b_lo - 0.01f) * bw, w_hi = base + ((float)b_hi + 1.01f) * bw;
                     const float c_min = w_lo - 2.0f * E, c_max = w_hi + 2.0f * E;
                     // the candidate window must lie strictly inside the list's value range [pa, pb)
                     okr = (c_min > par || par == plow) && (c_max < pbr || pbr == GM_PMAX);

@@ -215,6 +215,15 @@ snf_topk_kernel(const T* __restrict__ W, int n, int K, int32_t* __restrict__ J, 
     }
 }
 
+// dense image of the K-per-row matrix S (getS returns it sparse; the free function hands back scipy CSR built from this)
+__global__ void snf_dense_S_kernel(const int32_t* __restrict__ J, const double* __restrict__ V, int n, int K, double* __restrict__ S)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (int64_t)n * K) return;
+    const int i = (int)(e / K);
+    S[(int64_t)i * n + J[e]] = V[e];
+}
+
 // Xt = transpose( (sum_{k != skip} P_k) / (n_mats - 1) )        (similarity_fusion.py:168-174)
 // Ps: n_mats consecutive n x n float64 matrices.
 __global__ void snf_mean_others_T_kernel(const double* __restrict__ Ps, int n_mats, int skip, int n, double* __restrict__ Xt)

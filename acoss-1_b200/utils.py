@@ -2,12 +2,18 @@
 """
 Host utilities mirrored from the reference's acoss/utils.py: `log` (:24-35) and
 `create_dataset_filepaths` (:87-102).  Same names, arguments and error behaviour.
+
+The free functions of the reference's `acoss/algorithms/utils/` package (get_csm, csm_to_binary, getW, ...) are re-exported
+here from `algorithm_utils.py`; they run on the device through the C-ABI.
 """
 import logging
 
 import pandas as pd
 
-__all__ = ["log", "create_dataset_filepaths"]
+from . import algorithm_utils as _au
+from .algorithm_utils import *          # noqa: F401,F403  (the reference's free-function names)
+
+__all__ = ["log", "create_dataset_filepaths"] + list(_au.__all__)
 
 
 def log(log_file):

@@ -107,6 +107,8 @@ int acoss_ctx_synchronize(acoss_ctx *ctx);
  *   "crp_budget_bytes"       per-batch CRP working set of acoss_serra09_pairs* (default: a quarter of the free HBM,
  *                            at most 32 GiB; also settable by the environment variable ACOSS_CRP_BUDGET_MB at creation)
  *   "auto_split"             1: crp_mode 0 (auto) picks the phase-split CRP pipeline (crp_mode 5) where it applies
+ *   "count_hh"               1: the phase-split count pass multiplies the TF32 hi parts only (a third of the tensor work, a wider
+ *                            candidate band in the selection); results are bit-identical either way
  *   "ef_simt_csm"            1: acoss_earlyfusion_upload skips the tensor-core operand planes (the CSMs then run on the
  *                            fp32 SIMT tile kernel); set before the upload
  *   "inject_alloc_failures"  test hook: the next `value` device allocations of the pair pipeline's batch buffers
@@ -153,6 +155,20 @@ int acoss_serra09_pairs(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pai
 int acoss_serra09_pairs_dev(acoss_ctx *ctx, const int32_t *pairs_host, int64_t n_pairs,
                             const acoss_crp_params *params,
                             float *out_qmax_dev, float *out_dmax_dev);
+
+/* Query-versus-database mode: the scores of every (queries[a], db[b]) pair -- the body of
+ * `similarity(idxs)` (algorithm_template.py:121-140) over a Q x N_db rectangle instead of the upper triangle -- ranked per query
+ * the way getEvalStatistics ranks a row (:233-235, argsort of the similarity, the query itself left out), keeping only the best k.
+ * The Q x N_db matrix exists nowhere: the device holds k + one database chunk of keys per query and merges chunk by chunk.
+ * which: 0 Qmax, 1 Dmax.  norm_mode: -1 raw score (higher first); 0 score / sqrt(len_db) (Serra09.normalize_by_length,
+ * rqa_serra09.py:71-83; higher first); 1 sqrt(len_db) / score (ChenFusion.normalize_by_length, latefusion_chen.py:75-85, a distance:
+ * lower first).  Ties go to the lower database position.  out_idx_host (Q, k) int32: positions in db_host (-1 where the database has
+ * fewer than k other tracks); out_score_host (Q, k) float32: the normalised scores.  1 <= k <= ACOSS_TOPK_MAX.
+ * Shard over GPUs by splitting queries_host; there is no exchange between ranks. */
+#define ACOSS_TOPK_MAX 1000
+int acoss_serra09_topk(acoss_ctx *ctx, const int32_t *queries_host, int32_t n_queries, const int32_t *db_host, int32_t n_db,
+                       const acoss_crp_params *params, int32_t which, int32_t norm_mode, int32_t k,
+                       int32_t *out_idx_host, float *out_score_host);
 
 /* Accounting of the last acoss_serra09_pairs* call (synchronises the stream). */
 int acoss_get_pair_stats(acoss_ctx *ctx, acoss_pair_stats *out);
@@ -255,6 +271,35 @@ int acoss_sw_constrained_from_binary(acoss_ctx *ctx, const uint8_t *mats_host,
  * (iteration 0 Jacobi, then Gauss-Seidel) is reproduced. */
 int acoss_snf(acoss_ctx *ctx, const void *mats_host, int32_t dtype, int32_t n_mats, int32_t n,
               int32_t K, int32_t niters, double reg_diag, double *out_fused_host, void *out_Ws_host);
+
+/* The stages of doSimilarityFusion one at a time, for callers of the reference's free functions (getW :15-36, getP :101-122,
+ * getS :124-144, doSimilarityFusionWs :146-186).  input_kind 0: mats are distances (as acoss_snf); 1: mats are the affinities Ws
+ * themselves.  n_mats >= 1; the diffusion (niters > 0 or out_fused_host) needs >= 2.  Optional outputs (NULL to skip):
+ * out_fused_host (n, n) float64; out_Ws_host n_mats x (n, n) in the input dtype; out_P_host n_mats x (n, n) float64 = getP(W);
+ * out_S_host n_mats x (n, n) float64 = getS(W, K) as a dense matrix (K non-zeros per row). */
+int acoss_snf_ex(acoss_ctx *ctx, const void *mats_host, int32_t dtype, int32_t input_kind, int32_t n_mats, int32_t n,
+                 int32_t K, int32_t niters, double reg_diag, double *out_fused_host, void *out_Ws_host,
+                 double *out_P_host, double *out_S_host);
+
+/* ---- free functions of acoss/algorithms/utils on caller-supplied matrices ------------------------------------------ */
+
+/* get_csm(X, Y) (kind 0, cross_recurrence.py:31-48) / get_csm_cosine(X, Y) (kind 1, :54-73) of two row-major float32 point
+ * clouds (M, d), (N, d) -> (M, N) float32.  roll in 1..11 (kind 1, d a multiple of 12): the 12-bin frames of X are rolled
+ * by `roll` first, which is what get_csm_blocked_oti (:106-134) does with roll = get_oti(C1, C2). */
+int acoss_csm(acoss_ctx *ctx, const float *X_host, int32_t M, const float *Y_host, int32_t N, int32_t d,
+              int32_t kind, int32_t roll, float *out_host);
+
+/* get_oti(C1, C2) (cross_recurrence.py:76-103) for n pairs of 12-bin float32 chroma vectors, (n, 12) each: out_host[p] =
+ * argmax_i sum(roll(C1_p, i) * C2_p), first maximum. */
+int acoss_oti(acoss_ctx *ctx, const float *C1_host, const float *C2_host, int32_t n, int32_t *out_host);
+
+/* csm_to_binary(D, kappa) (cross_recurrence.py:137-161): (M, N) float32 -> (M, N) uint8, the kappa-nearest columns of every
+ * row (kappa = 0: all ones; kappa < 1: round(kappa * N), half to even; else int(kappa)); ties towards the lowest column.
+ * N <= 2048.  ACOSS_ERR_ARG where np.argpartition raises (kth >= N). */
+int acoss_csm_to_binary(acoss_ctx *ctx, const float *D_host, int32_t M, int32_t N, double kappa, uint8_t *out_bin_host);
+
+/* getWCSM(CSMAB, k1, k2) (similarity_fusion.py:38-54, Mu = 0.5): (M, N) float32 -> (M, N) float32.  k1 <= 16, N <= 2048. */
+int acoss_wcsm(acoss_ctx *ctx, const float *C_host, int32_t M, int32_t N, int32_t k1, int32_t k2, float *out_W_host);
 
 /* ---- SiMPle (matrix profile) and FTM2D ------------------------------------------- */
 

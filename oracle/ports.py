@@ -227,6 +227,8 @@ def simple_features(chroma_T, WIN=200, SKIP=100, win_len_smooth=4):
     nf = np.zeros((chroma_T.shape[0], int(chroma_T.shape[1] / SKIP)))
     for k in range(nf.shape[1]):
         nf[:, k] = np.mean(chroma_T[:, k * SKIP:k * SKIP + WIN], axis=1)
+    if nf.shape[1] == 0:
+        return nf                                                       # a track shorter than SKIP: no columns (np.convolve refuses empty input)
     n = win_len_smooth + 2
     win = 0.5 - 0.5 * np.cos(2.0 * np.pi * np.arange(n) / (n - 1))       # symmetric Hann (fftbins=False)
     win = win / np.sum(win)

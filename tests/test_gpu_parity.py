@@ -868,3 +868,108 @@ def test_earlyfusion_errors(ctx):
     sc = ctx.earlyfusion_pairs(np.array([[0, 1]], np.int32), kappa=0)         # kappa = 0: all ones
     M, N = ds["block_feats"][0]["mfccs"].shape[0], ds["block_feats"][1]["mfccs"].shape[0]
     assert sc[0].tolist() == [float(min(M, N) - 3)] * 4
+
+
+def test_free_functions_vs_ports(ctx, oracle):
+    """The reference's free functions (acoss/algorithms/utils/{alignment_tools,cross_recurrence,similarity_fusion}.py) under
+    acoss_b200.utils, each through the C-ABI, against the numpy restatements of oracle/ports.py (pinned against the reference's own
+    outputs in tests/test_oracle.py).  float32 GEMM-shaped results: rtol 2e-5 (summation order); selections: exact."""
+    from acoss_b200 import utils as U
+    from oracle import ports as P
+    U.set_default_context(ctx)
+    try:
+        rng = np.random.default_rng(11)
+        X = rng.random((70, 36)).astype(np.float32)
+        Y = rng.random((93, 36)).astype(np.float32)
+        np.testing.assert_allclose(U.get_csm(X, Y), P.get_csm(X, Y), rtol=2e-5, atol=2e-6)
+        np.testing.assert_allclose(U.get_csm_cosine(X, Y), P.get_csm_cosine(X, Y), rtol=2e-5, atol=2e-6)
+        S = U.get_ssm(X)
+        assert S.shape == (70, 70) and np.all(np.diag(S) == 0)
+        np.testing.assert_allclose(S[np.triu_indices(70, 1)], P.get_csm(X, X)[np.triu_indices(70, 1)], rtol=2e-5, atol=2e-5)
+        C1 = rng.random(12).astype(np.float32)
+        for sh in (0, 3, 11):
+            C2 = np.roll(C1, sh) + 0.01 * rng.random(12).astype(np.float32)
+            assert U.get_oti(C1, C2) == P.get_oti(C1, C2) == sh
+        C2 = np.roll(C1, 5)
+        for fn_u, fn_p in ((U.get_csm_cosine, P.get_csm_cosine), (U.get_csm, P.get_csm)):
+            got = U.get_csm_blocked_oti(X, Y, C1, C2, fn_u)
+            oti = P.get_oti(C1, C2)
+            X1 = np.roll(X.reshape(70, 3, 12), oti, axis=2).reshape(70, 36)
+            np.testing.assert_allclose(got, fn_p(X1, Y), rtol=2e-5, atol=2e-6)
+        # selections on a matrix without ties
+        D = P.get_csm(X, Y)
+        for kappa in (0, 0.1, 0.25, 7):
+            got = U.csm_to_binary(D, kappa)
+            exp = P.csm_to_binary(D, kappa)
+            assert got.dtype == np.uint8 and np.array_equal(got, np.asarray(exp, dtype=np.uint8)), kappa
+        import acoss_b200
+        with pytest.raises(acoss_b200.AcossError):
+            U.csm_to_binary(D, 93)
+        np.testing.assert_allclose(U.getWCSM(D, 5, 8), P.getWCSM(D, 5, 8), rtol=2e-5, atol=1e-7)
+        B = (rng.random((40, 57)) < 0.3).astype(np.uint8)
+        assert float(np.float32(U.smith_waterman_constrained(B))) == float(np.float32(oracle.sw_constrained(B)))
+        # similarity fusion stages, float64 (exact arithmetic order: 1e-12) and float32
+        n = 48
+        Ds = []
+        for _ in range(3):
+            A = rng.random((n, 6))
+            Ds.append(np.sqrt(((A[:, None, :] - A[None, :, :]) ** 2).sum(2)))
+        for dt, tol in ((np.float64, 1e-12), (np.float32, 2e-5)):
+            Dk = [d.astype(dt) for d in Ds]
+            Ws = [P.getW(np.array(d), 5) for d in Dk]
+            for d, w in zip(Dk, Ws):
+                got = U.getW(d, 5)
+                assert got.dtype == dt
+                np.testing.assert_allclose(got, w, rtol=tol, atol=1e-12)
+            np.testing.assert_allclose(U.getP(Ws[0]), P.getP(Ws[0]), rtol=tol)
+            Sg = U.getS(Ws[1], 5)
+            assert Sg.shape == (n, n) and np.all(np.diff(Sg.indptr) == 5)
+            np.testing.assert_allclose(Sg.toarray(), P.getS(Ws[1], 5), rtol=tol)
+            np.testing.assert_allclose(U.doSimilarityFusionWs(Ws, K=5, niters=4, reg_diag=1), P.snf_ws(Ws, 5, 4, 1), rtol=10 * tol)
+        Wsg, fused = U.doSimilarityFusion(Ds, K=5, niters=3)
+        Wsp, fusedp = P.snf(Ds, 5, 3, 1)
+        np.testing.assert_allclose(fused, fusedp, rtol=1e-11)
+    finally:
+        U.set_default_context(None)
+
+
+def test_serra09_topk_vs_full_matrix(ctx):
+    """acoss_serra09_topk (query x database, per-query top-k kept on the device) against a stable argsort of the full rectangle
+    computed pair by pair through acoss_serra09_pairs and normalised the way Serra09 / ChenFusion.normalize_by_length do
+    (float64 arithmetic, float32 store): indices and scores exact.  The database repeats tracks (exact ties -> lowest position),
+    spans two device chunks (5000 > 4096 - k) and contains the queries themselves (left out of their own ranking)."""
+    from acoss_b200 import synth
+    import acoss_b200
+    labels, works, tids, hp = synth.make_tracks(10, 4, 0, 7, 40, 90)
+    ctx.upload_tracks(hp)
+    n = len(hp)
+    lens = np.array([len(h) for h in hp], np.float64)
+    rng = np.random.default_rng(3)
+    queries = np.array([0, 17, 39], np.int32)
+    db = rng.integers(0, n, 5000).astype(np.int32)
+    prm = ctx.params()
+    pairs = np.stack([np.repeat(queries, len(db)), np.tile(db, len(queries))], 1).astype(np.int32)
+    q, d = ctx.serra09_pairs(pairs, prm, want_dmax=True)
+    for which, norm, raw in (("qmax", "serra09", q), ("dmax", "chen", d), ("qmax", None, q)):
+        full = raw.reshape(len(queries), len(db)).astype(np.float32)
+        if norm == "serra09":
+            full = (full.astype(np.float64) / np.sqrt(lens[db])[None, :]).astype(np.float32)
+        elif norm == "chen":
+            with np.errstate(divide="ignore"):
+                full = (np.sqrt(lens[db])[None, :] / full.astype(np.float64)).astype(np.float32)
+        for k in (1, 10, 1000):
+            idx, sc = ctx.serra09_topk(queries, db, k, prm, which=which, norm=norm)
+            assert idx.shape == (3, k) and sc.shape == (3, k)
+            for a, qt in enumerate(queries):
+                keep = np.flatnonzero(db != qt)
+                row = full[a, keep]
+                order = np.argsort(row if norm == "chen" else -row, kind="stable")[:k]
+                assert np.array_equal(idx[a, :len(order)], keep[order]), (which, norm, k, a)
+                assert np.array_equal(sc[a, :len(order)], row[order])
+    # fewer database entries than k: -1 / -inf fill; argument errors
+    idx, sc = ctx.serra09_topk([1], [1, 2, 3], 5, prm)
+    assert list(idx[0, 2:]) == [-1, -1, -1] and np.all(np.isneginf(sc[0, 2:])) and set(idx[0, :2]) == {1, 2}
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.serra09_topk([0], [1], 1001, prm)
+    with pytest.raises(acoss_b200.AcossError):
+        ctx.serra09_topk([n], [1], 3, prm)

@@ -11,6 +11,10 @@ def main():
     mode = int(sys.argv[2]) if len(sys.argv) > 2 else 2
     n = int(os.environ.get("ACOSS_PROBE_N", "64"))
     ctx = acoss_b200.Context(0)
+    for kv in os.environ.get("ACOSS_PROBE_OPTS", "").split(","):
+        if kv:
+            k, v = kv.split("=")
+            ctx.set_option(k, int(v))
     for L in lens:
         labels, works, tids, hp = synth.make_tracks(n // 2, 2, 0, 5, L, L)
         hp = [h[:L] for h in hp]
@@ -19,8 +23,12 @@ def main():
         pairs = np.stack([i, j], 1).astype(np.int32)
         prm = ctx.params(crp_mode=mode)
         ctx.serra09_pairs(pairs, prm)
+        c0 = ctx.debug_counters_ext(16) if hasattr(ctx, "debug_counters_ext") else None
         ctx.serra09_pairs(pairs, prm)
         st = ctx.pair_stats()
+        if c0 is not None:
+            c1 = ctx.debug_counters_ext(16)
+            print("  counters", [int(b) for b in c1])
         print("L=%d mode=%d pairs=%d crp %.1f ms  %.3e cells/s   dp %.2f ms %.0f GCUPS  exact %.4f fallback %d" % (
             L, mode, len(pairs), st["ms_crp"], st["crp_cells"] / st["ms_crp"] * 1e3, st["ms_dp"],
             st["dp_cells"] / st["ms_dp"] / 1e6, st["n_exact_cells"] / (2.0 * st["crp_cells"]), st["n_fallback_rows"]))
