@@ -723,7 +723,9 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 //   (C) warp per row: exact order statistics among the candidates -> percentile -> threshold
 //   rows that could not be bracketed (bracket miss, list overflow, tiny side B): the whole row exactly
 // =====================================================================================================================
-#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * GM_ROWS * 32 * 4 + SP_SEL_WARPS * 64 * 4)
+#define SP_POOL 6144                         // candidate entries per strip (flat: a row takes what it needs, at most SP_CAND_MAX)
+#define SP_CAND_MAX 96
+#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * SP_POOL * 4 + SP_SEL_WARPS * 64 * 4)
 
 __global__ void __launch_bounds__(SP_SEL_THREADS, 3)
 crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
@@ -740,9 +742,10 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     int* s_kx = s_nc + GM_ROWS;
     int* s_flag = s_kx + GM_ROWS;
     int* s_off = s_flag + GM_ROWS;                                          // [GM_ROWS + 1]
-    int* pool_col = s_off + GM_ROWS + 2;                                    // [GM_ROWS][32]
-    float* pool_dex = reinterpret_cast<float*>(pool_col + GM_ROWS * 32);    // [GM_ROWS][32]
-    int* s_hist = reinterpret_cast<int*>(pool_dex + GM_ROWS * 32);          // [SP_SEL_WARPS][64]
+    int* s_used = s_off + GM_ROWS;                                          // pool entries handed out
+    int* pool_col = s_off + GM_ROWS + 2;                                    // [SP_POOL] (row << 24) | column
+    float* pool_dex = reinterpret_cast<float*>(pool_col + SP_POOL);         // [SP_POOL] approximate radicand, then the exact distance
+    int* s_hist = reinterpret_cast<int*>(pool_dex + SP_POOL);               // [SP_SEL_WARPS][64]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_exact = 0;
     float max_err = 0.0f;
@@ -765,7 +768,8 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         }
         if (tid < GM_ROWS) {
             s_xx[tid] = (tid < tk.nrows) ? g.sdA[tk.row0 + tid] : 0.0f;
-            s_nc[tid] = 0; s_kx[tid] = 0;
+            s_nc[tid] = 0; s_kx[tid] = 0; s_off[tid] = 0;
+            if (tid == 0) *s_used = 0;
             s_flag[tid] = (tid < tk.nrows && tiny) ? 1 : 0;
         }
         __syncthreads();
@@ -785,59 +789,64 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     if (lane == 0) { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); if (ovf) atomicAdd(&counters[15], 1ull); else atomicAdd(&counters[13], 1ull); }
                     continue;
                 }
-                // The row's list (<= 512 entries in [pa, pb), 16 slots per lane, of which ~6 are in use) goes through ONE 64-bin
-                // histogram over the bracket (shared-memory atomics, 64 counters per warp): a prefix scan finds the bin(s) holding the
-                // wanted ranks; everything within 2E of those bins is a candidate for the exact chains.  ~250 warp instructions per
-                // row; the value bisection this replaces cost ~1300 (ncu: the kernel was issue-bound at 180 k warp instructions per strip).
+                // The row's list (four sub-lists, <= 512 entries of [pa, pb) in all, ~200 typically) is read COMPACTED: entry
+                // e = 32 i + lane for i < ceil(T / 32), so every later pass costs per entry in use, not per slot of the 16 x 32
+                // layout (ncu, source view: the slot-wise passes cost 1600 warp instructions per row, nine tenths on empty slots).
+                // One 64-bin histogram over the bracket (shared-memory atomics) + a prefix scan find the bin(s) holding the wanted
+                // ranks; the window shrinks to the extremes of those bins (again if it still holds more than 8 entries); everything
+                // within 2E of the window is a candidate for the exact chains.
                 const float2* lst = lists + srow * SP_LIST_STRIDE;
                 int* h = s_hist + warp * 64;
-                h[lane] = 0; h[lane + 32] = 0;
+                const int T = c_abr, p1 = c4r.x, p2 = p1 + c4r.y, p3 = p2 + c4r.z;
+                const int nI = (T + 31) >> 5;                                       // warp-uniform, <= SP_SEL_LPL
                 float lx[SP_SEL_LPL];
                 int ly[SP_SEL_LPL];
 #pragma unroll
-                for (int q = 0; q < SP_SEL_LPL; ++q) {              // slot (q % 4) * 32 + lane of segment q / 4
-                    lx[q] = INFINITY; ly[q] = 0;
-                    if ((q & 3) * 32 < cseg[q >> 2]) {              // warp-uniform: most sub-lists end inside their second block
-                        const int sl = (q & 3) * 32 + lane;
-                        if (sl < cseg[q >> 2]) { const float2 e = lst[(q >> 2) * GM_SUBCAP + sl]; lx[q] = e.x; ly[q] = __float_as_int(e.y); }
+                for (int i = 0; i < SP_SEL_LPL; ++i) {
+                    lx[i] = INFINITY; ly[i] = 0;
+                    if (i < nI) {
+                        const int e = 32 * i + lane;
+                        if (e < T) {
+                            const int seg = (e >= p1) + (e >= p2) + (e >= p3);
+                            const int sl = e - (seg == 0 ? 0 : seg == 1 ? p1 : seg == 2 ? p2 : p3);
+                            const float2 v = lst[seg * GM_SUBCAP + sl];
+                            lx[i] = v.x; ly[i] = __float_as_int(v.y);
+                        }
                     }
                 }
-                // value range of the list: the bracket, or the list's own extremes where the bracket is open-ended
                 float base = par, top = pbr;
-                uint32_t act = 0;                                   // slots still inside the window
-#pragma unroll
-                for (int q = 0; q < SP_SEL_LPL; ++q) act |= (uint32_t)(lx[q] != INFINITY) << q;
-                if (par == plow || pbr == GM_PMAX) {
+                if (par == plow || pbr == GM_PMAX) {                // open-ended bracket: the list's own value range
                     float vmn = INFINITY, vmx = -INFINITY;
 #pragma unroll
-                    for (int q = 0; q < SP_SEL_LPL; ++q) if (lx[q] != INFINITY) { vmn = fminf(vmn, lx[q]); vmx = fmaxf(vmx, lx[q]); }
+                    for (int i = 0; i < SP_SEL_LPL; ++i) if (i < nI && lx[i] != INFINITY) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); }
                     for (int o = 16; o > 0; o >>= 1) {
                         vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
                         vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
                     }
                     base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
                 }
-                int klo = pr.lo - c_ar, khi = klo + (pr.hi - pr.lo);                // ranks wanted among the active slots
+                int klo = pr.lo - c_ar, khi = klo + (pr.hi - pr.lo);                // ranks wanted among the entries in the window
                 float w_lo = base, w_hi = top;
+                uint32_t binw[SP_SEL_LPL / 4];                                      // bin of entry i: byte i % 4 of word i / 4; 0xFF = outside
+#pragma unroll
+                for (int q = 0; q < SP_SEL_LPL / 4; ++q) binw[q] = 0xFFFFFFFFu;
                 okr = true;
-                // up to three rounds: histogram the active slots over [base, top), keep the bin(s) holding the wanted ranks, shrink the
-                // window to the actual extremes of what is left.  One round leaves ~list/64 slots; it stops at <= 6.
                 for (int round = 0; round < 3; ++round) {
                     const float bw = (top - base) * (1.0f / 64.0f);
                     const float bsc = (bw > 0.0f) ? 1.0f / bw : 0.0f;
                     h[lane] = 0; h[lane + 32] = 0;
                     __syncwarp();
-                    uint32_t binw[(SP_SEL_LPL + 3) / 4];                            // 6 + 2 bits per slot: four slots per word
 #pragma unroll
-                    for (int q = 0; q < (SP_SEL_LPL + 3) / 4; ++q) binw[q] = 0;
-#pragma unroll
-                    for (int q = 0; q < SP_SEL_LPL; ++q)
-                        if ((q & 3) * 32 < cseg[q >> 2]) {
-                            if (act & (1u << q)) {
-                                const int b = min(63, max(0, (int)((lx[q] - base) * bsc)));
-                                binw[q >> 2] |= (uint32_t)b << (8 * (q & 3));
+                    for (int i = 0; i < SP_SEL_LPL; ++i)
+                        if (i < nI) {
+                            const uint32_t ob = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+                            const bool in = round == 0 ? (lx[i] != INFINITY) : (ob != 0xFFu);
+                            uint32_t b = 0xFFu;
+                            if (in) {
+                                b = (uint32_t)min(63, max(0, (int)((lx[i] - base) * bsc)));
                                 atomicAdd(&h[b], 1);
                             }
+                            binw[i >> 2] = (binw[i >> 2] & ~(0xFFu << (8 * (i & 3)))) | (b << (8 * (i & 3)));
                         }
                     __syncwarp();
                     const int h0 = h[2 * lane], h1 = h[2 * lane + 1];
@@ -851,8 +860,7 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     const unsigned m_lo = __ballot_sync(0xffffffffu, my_lo >= 0), m_hi = __ballot_sync(0xffffffffu, my_hi >= 0);
                     if (m_lo == 0 || m_hi == 0) { okr = false; break; }
                     const int l_lo = __ffs(m_lo) - 1, l_hi = __ffs(m_hi) - 1;
-                    const int b_lo = __shfl_sync(0xffffffffu, my_lo, l_lo), b_hi = __shfl_sync(0xffffffffu, my_hi, l_hi);
-                    // slots below bin b_lo leave the rank; the window keeps bins b_lo .. b_hi
+                    const uint32_t b_lo = (uint32_t)__shfl_sync(0xffffffffu, my_lo, l_lo), b_hi = (uint32_t)__shfl_sync(0xffffffffu, my_hi, l_hi);
                     const int below_pair = __shfl_sync(0xffffffffu, excl, l_lo), h0_lo = __shfl_sync(0xffffffffu, h0, l_lo);
                     const int n_below_bin = below_pair + ((b_lo & 1) ? h0_lo : 0);
                     const int incl_hi = __shfl_sync(0xffffffffu, incl, l_hi), h1_hi = __shfl_sync(0xffffffffu, h1, l_hi);
@@ -860,18 +868,18 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     klo -= n_below_bin; khi -= n_below_bin;
                     float vmn = INFINITY, vmx = -INFINITY;
 #pragma unroll
-                    for (int q = 0; q < SP_SEL_LPL; ++q)
-                        if ((q & 3) * 32 < cseg[q >> 2]) {
-                            const int b = (binw[q >> 2] >> (8 * (q & 3))) & 0xFF;
-                            if ((act & (1u << q)) && b >= b_lo && b <= b_hi) { vmn = fminf(vmn, lx[q]); vmx = fmaxf(vmx, lx[q]); }
-                            else act &= ~(1u << q);
+                    for (int i = 0; i < SP_SEL_LPL; ++i)
+                        if (i < nI) {
+                            const uint32_t b = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+                            if (b - b_lo <= b_hi - b_lo) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); }     // 0xFF is never inside
+                            else binw[i >> 2] |= 0xFFu << (8 * (i & 3));
                         }
                     for (int o = 16; o > 0; o >>= 1) {
                         vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
                         vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
                     }
                     w_lo = vmn; w_hi = vmx;
-                    if (n_upto_bin - n_below_bin <= 6 || !(vmx > vmn)) break;
+                    if (n_upto_bin - n_below_bin <= 8 || !(vmx > vmn)) break;
                     base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
                 }
                 int n_c = 0, kx = 0;
@@ -879,24 +887,39 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     const float c_min = w_lo - 2.0f * E, c_max = w_hi + 2.0f * E;
                     // the candidate window must lie strictly inside the list's value range [pa, pb)
                     okr = (c_min > par || par == plow) && (c_max < pbr || pbr == GM_PMAX);
+                    int my_c = 0;
                     if (okr) {
-                        int n_below = c_ar;
+                        int my_below = 0;
 #pragma unroll
-                        for (int q = 0; q < SP_SEL_LPL; ++q)
-                            if ((q & 3) * 32 < cseg[q >> 2]) {
-                                const bool valid = lx[q] != INFINITY;
-                                const bool below = valid && lx[q] < c_min;
-                                const bool cand = valid && !below && lx[q] <= c_max;
-                                n_below += __popc(__ballot_sync(0xffffffffu, below));
-                                const unsigned mc = __ballot_sync(0xffffffffu, cand);
-                                if (cand) {
-                                    const int slot = n_c + __popc(mc & ((1u << lane) - 1u));
-                                    if (slot < 32) { pool_col[r * 32 + slot] = ly[q]; pool_dex[r * 32 + slot] = lx[q]; }
-                                }
-                                n_c += __popc(mc);
+                        for (int i = 0; i < SP_SEL_LPL; ++i)
+                            if (i < nI) {                               // empty entries hold +inf: neither below nor candidates
+                                my_below += lx[i] < c_min;
+                                my_c += (lx[i] >= c_min) && (lx[i] <= c_max);
                             }
+                        const int n_below = c_ar + __reduce_add_sync(0xffffffffu, my_below);
+                        n_c = __reduce_add_sync(0xffffffffu, my_c);
                         kx = pr.lo - n_below;
-                        if (n_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) okr = false;
+                        if (n_c > SP_CAND_MAX || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) okr = false;
+                    }
+                    if (okr) {
+                        int incl = my_c;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+                        int off = 0;
+                        if (lane == 0) off = atomicAdd(s_used, n_c);
+                        off = __shfl_sync(0xffffffffu, off, 0);
+                        if (off + n_c > SP_POOL) {                  // pool exhausted: the row goes the exact way; its slots stay marked empty
+                            okr = false;
+                            for (int sl = off + lane; sl < min(off + n_c, SP_POOL); sl += 32) pool_col[sl] = -1;
+                        } else {
+                            int at = off + incl - my_c;
+#pragma unroll
+                            for (int i = 0; i < SP_SEL_LPL; ++i)
+                                if (i < nI) {
+                                    if ((lx[i] >= c_min) && (lx[i] <= c_max)) { pool_col[at] = (r << 24) | ly[i]; pool_dex[at] = lx[i]; ++at; }
+                                }
+                            if (lane == 0) s_off[r] = off;
+                        }
                     }
                 }
                 if (lane == 0) {
@@ -905,30 +928,14 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 }
             }
         __syncthreads();
-        // offsets of the rows' candidates in the flat task list
-        if (warp == 0) {
-            int c[4], tot = 0;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) { const int r = 4 * lane + q; c[q] = (r < tk.nrows) ? s_nc[r] : 0; tot += c[q]; }
-            int incl = tot;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
-            int run = incl - tot;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) { s_off[4 * lane + q] = run; run += c[q]; }
-            if (lane == 31) s_off[GM_ROWS] = run;
-        }
-        __syncthreads();
         // ---- (B)
         {
             const int boff = side_a_is_query ? (ACOSS_NBINS - rot) % ACOSS_NBINS : 0;     // rot_src(c, rot) = (c + boff) % 12
-            const int n_tasks_c = s_off[GM_ROWS];
+            const int n_tasks_c = min(*s_used, SP_POOL);             // entries of rows that did not fit are never written: their rows are flagged
             for (int idx = tid; idx < n_tasks_c; idx += SP_SEL_THREADS) {
-                int r = 0;                                            // last row with s_off[r] <= idx
-#pragma unroll
-                for (int st = 64; st > 0; st >>= 1) if (s_off[r + st] <= idx) r += st;
-                const int slot = idx - s_off[r];
-                const int jj = pool_col[r * 32 + slot];
+                const int code = pool_col[idx];
+                if (code < 0) continue;
+                const int r = (code >> 24) & 0xFF, jj = code & 0xFFFFFF;
                 const float4* bp = reinterpret_cast<const float4*>(g.fr_b + (int64_t)jj * ACOSS_NBINS);
                 const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
                 float acc = 0.0f;
@@ -943,27 +950,47 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 const float sa = s_xx[r], sb = __ldg(g.sdB + jj);
                 const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
                 float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
-                max_err = fmaxf(max_err, fabsf(item - pool_dex[r * 32 + slot]) / (sa + sb));
+                max_err = fmaxf(max_err, fabsf(item - pool_dex[idx]) / (sa + sb));
                 if (item < 0.0f) item = 0.0f;
-                pool_dex[r * 32 + slot] = __fsqrt_rn(item);
+                pool_dex[idx] = __fsqrt_rn(item);
                 ++n_exact;
             }
         }
         __syncthreads();
-        // ---- (C) warp per row: ranks kx and kx + 1 among the row's exact candidate distances (ties by slot)
+        // ---- (C) warp per row: ranks kx and kx + 1 among the row's exact candidate distances (ties by slot); up to three
+        //      candidates per lane, the others read as shared-memory broadcasts
         for (int r = warp; r < tk.nrows; r += SP_SEL_WARPS) {
             const int n_c = s_nc[r], kx = s_kx[r];
             if (n_c == 0) continue;
-            const float da = (lane < n_c) ? pool_dex[r * 32 + lane] : INFINITY;
-            int rank = 0;
-            for (int b_ = 0; b_ < n_c; ++b_) {
-                const float db = __shfl_sync(0xffffffffu, da, b_);
-                rank += (db < da) || (db == da && b_ < lane);
+            const float* dex = pool_dex + s_off[r];
+            float da[3];
+            int rank[3] = {0, 0, 0};
+#pragma unroll
+            for (int c = 0; c < 3; ++c) da[c] = (32 * c + lane < n_c) ? dex[32 * c + lane] : INFINITY;
+            if (n_c <= 32) {
+                for (int b_ = 0; b_ < n_c; ++b_) {
+                    const float db = dex[b_];
+                    rank[0] += (db < da[0]) || (db == da[0] && b_ < lane);
+                }
+            } else {
+                for (int b_ = 0; b_ < n_c; ++b_) {
+                    const float db = dex[b_];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) rank[c] += (db < da[c]) || (db == da[c] && b_ < 32 * c + lane);
+                }
             }
-            const unsigned m_lo = __ballot_sync(0xffffffffu, lane < n_c && rank == kx);
-            const unsigned m_hi = __ballot_sync(0xffffffffu, lane < n_c && rank == kx + 1);
-            const float v_lo = __shfl_sync(0xffffffffu, da, __ffs(m_lo) - 1);
-            const float v_hi = m_hi ? __shfl_sync(0xffffffffu, da, __ffs(m_hi) - 1) : v_lo;
+            float v_lo = 0.0f, v_hi = 0.0f;
+            bool have_hi = false;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                if (32 * c >= n_c) break;
+                const bool in = 32 * c + lane < n_c;
+                const unsigned m_lo = __ballot_sync(0xffffffffu, in && rank[c] == kx);
+                const unsigned m_hi = __ballot_sync(0xffffffffu, in && rank[c] == kx + 1);
+                if (m_lo) v_lo = __shfl_sync(0xffffffffu, da[c], __ffs(m_lo) - 1);
+                if (m_hi) { v_hi = __shfl_sync(0xffffffffu, da[c], __ffs(m_hi) - 1); have_hi = true; }
+            }
+            if (!have_hi) v_hi = v_lo;
             if (lane == 0) thr_out[tk.row0 + r] = percentile_combine(pr, v_lo, v_hi);
         }
         // ---- rows that could not be bracketed (and tiny side B): the whole row exactly, one row at a time
