@@ -50,6 +50,10 @@ struct DevBuf {
 struct acoss_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;   // phase-split pipeline: the selection kernels run beside the next chunk's streaming kernels
+    cudaEvent_t ev_cnt[2] = {}, ev_sel[2] = {};
+    float piv_nsigma = 2.5f;          // bracket half-width of the phase-split pivots in binomial sigmas ("piv_nsigma_x10")
+    int split_overlap = 0;            // "split_overlap": 0 = all phase-split kernels on one stream
     std::string err;
     // track store
     int n_tracks = 0, m = 0, tau = 0;
@@ -66,7 +70,7 @@ struct acoss_ctx {
     bool have_split = false;
     int64_t split_launches = 0;
     int count_hh = 0;                 // phase-split count pass on the hi.hi product alone ("count_hh")
-    int auto_split = 0;               // crp_mode 0 picks the phase-split pipeline (acoss_ctx_set_option "auto_split")
+    int auto_split = 1;               // crp_mode 0 picks the phase-split pipeline (acoss_ctx_set_option "auto_split")
     // SiMPle feature store (frame-major float64) + per-track chroma profiles
     int sp_tracks = 0;
     std::vector<int64_t> sp_offs;
@@ -123,6 +127,11 @@ extern "C" int acoss_ctx_create(int device, acoss_ctx** out)
     e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return ACOSS_ERR_CUDA; }
     for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+    if (cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess) ctx->stream2 = nullptr;
+    for (int i = 0; i < 2; ++i) {
+        cudaEventCreateWithFlags(&ctx->ev_cnt[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_sel[i], cudaEventDisableTiming);
+    }
     cudaDeviceGetAttribute(&ctx->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
     {   // CRP working set per batch: a quarter of the free HBM, at most 32 GiB (several DP waves per batch: with the
@@ -155,6 +164,8 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
                       &ctx->d_ef_planes[0], &ctx->d_ef_planes[1], &ctx->d_ef_planes[2], &ctx->d_ef_poff[0], &ctx->d_ef_poff[1], &ctx->d_ef_poff[2]};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    for (int i = 0; i < 2; ++i) { if (ctx->ev_cnt[i]) cudaEventDestroy(ctx->ev_cnt[i]); if (ctx->ev_sel[i]) cudaEventDestroy(ctx->ev_sel[i]); }
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -168,6 +179,8 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
         ctx->crp_budget = (size_t)value;
         return ACOSS_OK;
     }
+    if (k == "piv_nsigma_x10") { if (value < 1 || value > 100) return ACOSS_ERR_ARG; ctx->piv_nsigma = 0.1f * (float)value; return ACOSS_OK; }
+    if (k == "split_overlap") { ctx->split_overlap = value != 0; return ACOSS_OK; }
     if (k == "count_hh") { ctx->count_hh = value != 0; return ACOSS_OK; }
     if (k == "auto_split") { ctx->auto_split = value != 0; return ACOSS_OK; }
     if (k == "ef_simt_csm") { ctx->ef_force_simt = value != 0; return ACOSS_OK; }

@@ -206,7 +206,7 @@ __device__ __forceinline__ SpGeom sp_geom(const PairDesc& pd, int side_a_is_quer
 __global__ void __launch_bounds__(GM_THREADS, 1)
 crp_pivot_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
                  const float* __restrict__ frames, const float* __restrict__ selfdot, const float* __restrict__ sdmax,
-                 const unsigned char* __restrict__ smpop, int side_a_is_query, float qf,
+                 const unsigned char* __restrict__ smpop, int side_a_is_query, float qf, float nsigma,
                  float2* __restrict__ piv, unsigned long long* __restrict__ counters)
 {
     extern __shared__ __align__(128) unsigned char gsm[];
@@ -308,8 +308,8 @@ crp_pivot_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict
         const float frac = ((float)pr.lo + 0.5f) / (float)g.NB;
         const float rs = frac * (float)GM_S;
         const float sg = sqrtf(fmaxf(rs * (1.0f - frac), 1.0f));
-        const int r_lo = (int)floorf(rs - GM_NSIGMA * sg) - 1;       // sample ranks the bracket must enclose
-        const int r_hi = (int)ceilf(rs + GM_NSIGMA * sg) + 1;
+        const int r_lo = (int)floorf(rs - nsigma * sg) - 1;          // sample ranks the bracket must enclose
+        const int r_hi = (int)ceilf(rs + nsigma * sg) + 1;
         unsigned lo[16], hi[16];
         int tot = 0;
 #pragma unroll
@@ -723,7 +723,7 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 //   (C) warp per row: exact order statistics among the candidates -> percentile -> threshold
 //   rows that could not be bracketed (bracket miss, list overflow, tiny side B): the whole row exactly
 // =====================================================================================================================
-#define SP_POOL 6144                         // candidate entries per strip (flat: a row takes what it needs, at most SP_CAND_MAX)
+#define SP_POOL 3072                         // candidate entries per strip (flat: a row takes what it needs, at most SP_CAND_MAX)
 #define SP_CAND_MAX 96
 #define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * SP_POOL * 4 + SP_SEL_WARPS * 64 * 4)
 
@@ -799,26 +799,27 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 int* h = s_hist + warp * 64;
                 const int T = c_abr, p1 = c4r.x, p2 = p1 + c4r.y, p3 = p2 + c4r.z;
                 const int nI = (T + 31) >> 5;                                       // warp-uniform, <= SP_SEL_LPL
+                // every pass below walks the entries in blocks of four behind ONE warp-uniform branch per block (a per-entry guard is
+                // if-converted by the compiler and the empty entries then cost as much as the live ones); entries past T hold +inf
+#define SP_ENTRIES(i, ...)                                                                      \
+                _Pragma("unroll") for (int ib_ = 0; ib_ < SP_SEL_LPL; ib_ += 4)                 \
+                    if (ib_ < nI) { _Pragma("unroll") for (int i = ib_; i < ib_ + 4; ++i) { __VA_ARGS__ } }
                 float lx[SP_SEL_LPL];
                 int ly[SP_SEL_LPL];
 #pragma unroll
-                for (int i = 0; i < SP_SEL_LPL; ++i) {
-                    lx[i] = INFINITY; ly[i] = 0;
-                    if (i < nI) {
-                        const int e = 32 * i + lane;
-                        if (e < T) {
-                            const int seg = (e >= p1) + (e >= p2) + (e >= p3);
-                            const int sl = e - (seg == 0 ? 0 : seg == 1 ? p1 : seg == 2 ? p2 : p3);
-                            const float2 v = lst[seg * GM_SUBCAP + sl];
-                            lx[i] = v.x; ly[i] = __float_as_int(v.y);
-                        }
-                    }
-                }
+                for (int i = 0; i < SP_SEL_LPL; ++i) { lx[i] = INFINITY; ly[i] = 0; }
+                SP_ENTRIES(i,
+                    const int e = 32 * i + lane;
+                    if (e < T) {
+                        const int seg = (e >= p1) + (e >= p2) + (e >= p3);
+                        const int sl = e - (seg == 0 ? 0 : seg == 1 ? p1 : seg == 2 ? p2 : p3);
+                        const float2 v = lst[seg * GM_SUBCAP + sl];
+                        lx[i] = v.x; ly[i] = __float_as_int(v.y);
+                    })
                 float base = par, top = pbr;
                 if (par == plow || pbr == GM_PMAX) {                // open-ended bracket: the list's own value range
                     float vmn = INFINITY, vmx = -INFINITY;
-#pragma unroll
-                    for (int i = 0; i < SP_SEL_LPL; ++i) if (i < nI && lx[i] != INFINITY) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); }
+                    SP_ENTRIES(i, if (lx[i] != INFINITY) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); })
                     for (int o = 16; o > 0; o >>= 1) {
                         vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
                         vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
@@ -836,18 +837,15 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     const float bsc = (bw > 0.0f) ? 1.0f / bw : 0.0f;
                     h[lane] = 0; h[lane + 32] = 0;
                     __syncwarp();
-#pragma unroll
-                    for (int i = 0; i < SP_SEL_LPL; ++i)
-                        if (i < nI) {
-                            const uint32_t ob = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
-                            const bool in = round == 0 ? (lx[i] != INFINITY) : (ob != 0xFFu);
-                            uint32_t b = 0xFFu;
-                            if (in) {
-                                b = (uint32_t)min(63, max(0, (int)((lx[i] - base) * bsc)));
-                                atomicAdd(&h[b], 1);
-                            }
-                            binw[i >> 2] = (binw[i >> 2] & ~(0xFFu << (8 * (i & 3)))) | (b << (8 * (i & 3)));
+                    SP_ENTRIES(i,
+                        const uint32_t ob = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+                        const bool in = round == 0 ? (lx[i] != INFINITY) : (ob != 0xFFu);
+                        uint32_t b = 0xFFu;
+                        if (in) {
+                            b = (uint32_t)min(63, max(0, (int)((lx[i] - base) * bsc)));
+                            atomicAdd(&h[b], 1);
                         }
+                        binw[i >> 2] = (binw[i >> 2] & ~(0xFFu << (8 * (i & 3)))) | (b << (8 * (i & 3)));)
                     __syncwarp();
                     const int h0 = h[2 * lane], h1 = h[2 * lane + 1];
                     __syncwarp();
@@ -867,13 +865,10 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     const int n_upto_bin = incl_hi - ((b_hi & 1) ? 0 : h1_hi);
                     klo -= n_below_bin; khi -= n_below_bin;
                     float vmn = INFINITY, vmx = -INFINITY;
-#pragma unroll
-                    for (int i = 0; i < SP_SEL_LPL; ++i)
-                        if (i < nI) {
-                            const uint32_t b = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
-                            if (b - b_lo <= b_hi - b_lo) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); }     // 0xFF is never inside
-                            else binw[i >> 2] |= 0xFFu << (8 * (i & 3));
-                        }
+                    SP_ENTRIES(i,
+                        const uint32_t b = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+                        if (b - b_lo <= b_hi - b_lo) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); }     // 0xFF is never inside
+                        else binw[i >> 2] |= 0xFFu << (8 * (i & 3));)
                     for (int o = 16; o > 0; o >>= 1) {
                         vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
                         vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
@@ -890,12 +885,9 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     int my_c = 0;
                     if (okr) {
                         int my_below = 0;
-#pragma unroll
-                        for (int i = 0; i < SP_SEL_LPL; ++i)
-                            if (i < nI) {                               // empty entries hold +inf: neither below nor candidates
-                                my_below += lx[i] < c_min;
-                                my_c += (lx[i] >= c_min) && (lx[i] <= c_max);
-                            }
+                        SP_ENTRIES(i,                                   // empty entries hold +inf: neither below nor candidates
+                            my_below += lx[i] < c_min;
+                            my_c += (lx[i] >= c_min) && (lx[i] <= c_max);)
                         const int n_below = c_ar + __reduce_add_sync(0xffffffffu, my_below);
                         n_c = __reduce_add_sync(0xffffffffu, my_c);
                         kx = pr.lo - n_below;
@@ -913,15 +905,13 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                             for (int sl = off + lane; sl < min(off + n_c, SP_POOL); sl += 32) pool_col[sl] = -1;
                         } else {
                             int at = off + incl - my_c;
-#pragma unroll
-                            for (int i = 0; i < SP_SEL_LPL; ++i)
-                                if (i < nI) {
-                                    if ((lx[i] >= c_min) && (lx[i] <= c_max)) { pool_col[at] = (r << 24) | ly[i]; pool_dex[at] = lx[i]; ++at; }
-                                }
+                            SP_ENTRIES(i,
+                                if ((lx[i] >= c_min) && (lx[i] <= c_max)) { pool_col[at] = (r << 24) | ly[i]; pool_dex[at] = lx[i]; ++at; })
                             if (lane == 0) s_off[r] = off;
                         }
                     }
                 }
+#undef SP_ENTRIES
                 if (lane == 0) {
                     if (okr) { s_nc[r] = n_c; s_kx[r] = kx; }
                     else { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); atomicAdd(&counters[12], 1ull); }

@@ -147,7 +147,7 @@ __device__ __forceinline__ void dp_row_step(uint32_t (&Aprev)[NCH][G], uint32_t 
 }
 
 // One warp per pair.  ALIGN: 0 = serra09 (Qmax), 1 = chen17 (Dmax).
-// Requirements: pitch % (64*G) == 0, N <= NCH*64*G, min(M,N) small enough for
+// Requirements: pitch % 16 == 0 (16-byte aligned rows), N <= pitch, N <= NCH*64*G, min(M,N) small enough for
 // int16 half units (host checks: 4*min(M,N) < 32000).
 template <int G, int NCH, int ALIGN>
 __global__ void __launch_bounds__(128)
@@ -176,6 +176,10 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
         const int M = pd.M, N = pd.N, pitch = pd.pitch;
         const int nch = (N + CHUNK - 1) / CHUNK;
         const uint8_t* base = crp + pd.crp_off + (int64_t)lane * LB;
+        // the pitch is a multiple of 16 B (128 B from the pair pipeline), not of the chunk: in the last chunk the lanes past the
+        // pitch load nothing and keep the "no recurrence" fill, so no padding beyond the 128-byte line is ever streamed
+        const bool ok_last = (nch - 1) * CHUNK + (lane + 1) * LB <= pitch;
+#define DP_LD_OK(ch) ((ch) < nch - 1 || ((ch) == nch - 1 && ok_last))
 
         uint32_t A[NCH][G], B[NCH][G], carry[NCH];     // rows i-1, i-2 (roles alternate); carried (i-2) edge
         uint32_t Bon[NCH][G];                          // chen17: +R of row i-1 (unshifted)
@@ -206,13 +210,14 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
                 for (int ch = 0; ch < NCH; ++ch)
                     if (ch < nch) {
                         RowBytes<G> rb;
-                        rb.load(base + (int64_t)1 * pitch + ch * CHUNK);
+                        rb.fill(0xFFFFFFFFu);
+                        if (DP_LD_OK(ch)) rb.load(base + (int64_t)1 * pitch + ch * CHUNK);
                         StepUnroll<G, G - 1>::bonus(rb, Bon[ch]);
                     }
             }
 #pragma unroll
             for (int ch = 0; ch < NCH; ++ch)
-                if (ch < nch) r0[ch].load(base + (int64_t)2 * pitch + ch * CHUNK);
+                if (DP_LD_OK(ch)) r0[ch].load(base + (int64_t)2 * pitch + ch * CHUNK);
         }
         const int64_t pitch64 = pitch;
         const uint8_t* rp = base + 2 * pitch64;             // this lane's bytes of row i
@@ -224,14 +229,14 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
                 const uint8_t* p1 = rp + pitch64;
 #pragma unroll
                 for (int ch = 0; ch < NCH; ++ch)
-                    if (ch < nch) r1[ch].load(p1 + ch * CHUNK);
+                    if (DP_LD_OK(ch)) r1[ch].load(p1 + ch * CHUNK);
             }
             if (pf_lane && i + 7 < M) {
                 const uint8_t* p6 = rp + 4 * pitch64;
                 const uint8_t* p7 = p6 + pitch64;
 #pragma unroll
                 for (int ch = 0; ch < NCH; ++ch)
-                    if (ch < nch) {
+                    if (DP_LD_OK(ch)) {
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(p6 + ch * CHUNK));
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(p7 + ch * CHUNK));
                     }
@@ -242,7 +247,7 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
                     const uint8_t* p2 = rp + 2 * pitch64;
 #pragma unroll
                     for (int ch = 0; ch < NCH; ++ch)
-                        if (ch < nch) r0[ch].load(p2 + ch * CHUNK);
+                        if (DP_LD_OK(ch)) r0[ch].load(p2 + ch * CHUNK);
                 }
                 dp_row_step<G, NCH, ALIGN>(B, A, carry, Bon, r1, vmask, nch, lane, zmask, rm);  // row i+1 -> A
             }
@@ -251,6 +256,7 @@ dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
         best = __reduce_max_sync(0xffffffffu, best);
         if (lane == 0) out[pd.out_idx] = 0.5f * (float)best;
     }
+#undef DP_LD_OK
 }
 
 // ---- constrained Smith-Waterman on the same row-parallel DPX scheme ---------------------------------------------------

@@ -183,14 +183,101 @@ __device__ __forceinline__ uint32_t ef_warp_select(const uint32_t (&keys)[R], in
     return ans;
 }
 
+// Two order statistics of one row at once (ranks kA and, if wantB, kB; 0-based) without the 32-step bitwise descent (2 x 32 x R
+// compare-and-count instructions per row were 49 % of an EarlyFusion step): one 256-bin histogram over the row's key range in
+// shared memory (bins are linear in KEY space: (key - min) >> shift, exact and monotone), a scan that locates the bin of each
+// rank, and an exact ranking of that bin's members (usually 1 - 4 of them).  A bin with more than 32 members (long runs of equal
+// distances) falls back to the bitwise descent.  hist: 256 ints, cand: 64 keys, ccnt: 2 ints, all private to the warp.
+template <int R>
+__device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N, int kA, int kB, bool wantB,
+                                                int* hist, uint32_t* cand, int* ccnt, uint32_t& outA, uint32_t& outB)
+{
+    const int lane = threadIdx.x & 31;
+    uint32_t mn = 0xffffffffu, mx = 0u;
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+        mn = min(mn, keys[q]);                                   // padding keys are 0xffffffff
+        if (q * 32 + lane < N) mx = max(mx, keys[q]);
+    }
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    const uint32_t range = mx - mn;
+    const int shift = range >= 256u ? (32 - __clz(range)) - 8 : 0;       // (range >> shift) < 256
+    int4* h4 = reinterpret_cast<int4*>(hist);
+    h4[lane] = make_int4(0, 0, 0, 0); h4[lane + 32] = make_int4(0, 0, 0, 0);
+    if (lane < 2) ccnt[lane] = 0;
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < R; ++q)
+        if (q * 32 + lane < N) atomicAdd(&hist[(keys[q] - mn) >> shift], 1);
+    __syncwarp();
+    const int4 ca = h4[2 * lane], cb = h4[2 * lane + 1];             // bins 8 lane .. 8 lane + 7
+    const int c[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
+    int tot = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) tot += c[j];
+    int incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+    const int excl = incl - tot;
+    int bt[2] = {0, 0}, below[2] = {0, 0};
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+        const int k = w == 0 ? kA : kB;
+        const bool mine = k >= excl && k < incl;
+        int b_ = 0, bl = 0, run = excl;
+        bool found = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (mine && !found && k < run + c[j]) { b_ = 8 * lane + j; bl = run; found = true; }
+            run += c[j];
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, mine);
+        const int src = m ? __ffs(m) - 1 : 0;
+        bt[w] = __shfl_sync(0xffffffffu, b_, src);
+        below[w] = __shfl_sync(0xffffffffu, bl, src);
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q)
+        if (q * 32 + lane < N) {
+            const int b = (int)((keys[q] - mn) >> shift);
+            if (b == bt[0]) { const int p = atomicAdd(&ccnt[0], 1); if (p < 32) cand[p] = keys[q]; }
+            if (wantB && b == bt[1]) { const int p = atomicAdd(&ccnt[1], 1); if (p < 32) cand[32 + p] = keys[q]; }
+        }
+    __syncwarp();
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+        if (w == 1 && !wantB) { outB = 0; break; }
+        const int n_c = ccnt[w], want = (w == 0 ? kA : kB) - below[w];
+        uint32_t res;
+        if (n_c <= 32) {
+            const uint32_t mykey = lane < n_c ? cand[32 * w + lane] : 0xffffffffu;
+            int rank = 0;
+            for (int j = 0; j < n_c; ++j) {
+                const uint32_t o = __shfl_sync(0xffffffffu, mykey, j);
+                rank += (o < mykey) || (o == mykey && j < lane);
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, lane < n_c && rank == want);
+            res = __shfl_sync(0xffffffffu, mykey, m ? __ffs(m) - 1 : 0);
+        } else {
+            res = ef_warp_select<R>(keys, w == 0 ? kA : kB);
+        }
+        if (w == 0) outA = res; else outB = res;
+    }
+    __syncwarp();
+}
+
 // One warp per (pair, matrix, row): binarise the k_bin smallest (ties -> lowest column) and, for the three
 // CSMs (want_mean), the mean of the K smallest.  Rows up to 32*R columns.  which = matrix index 0..3.
 template <int R>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, R >= 32 ? 2 : 3)
 ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_task_off, int n_pairs, int64_t n_rows_total,
               int first_mat, int n_mats, int K, const float* __restrict__ csm, uint8_t* __restrict__ bin,
               float* __restrict__ rowmean)
 {
+    __shared__ __align__(16) int s_hist[8 * 256];
+    __shared__ uint32_t s_cand[8 * 64];
+    __shared__ int s_ccnt[8 * 2];
     const int lane = threadIdx.x & 31;
     const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -209,6 +296,18 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
         for (int q = 0; q < R; ++q) { const int j = q * 32 + lane; keys[q] = (j < N) ? ef_key(row[j]) : 0xffffffffu; }
         uint8_t* brow = bin + pd.bin_off + ((int64_t)mat * pd.M + i) * pd.pitch;
         for (int j = N + lane; j < pd.pitch; j += 32) brow[j] = 0;
+        // both order statistics of the row in one go: the kb-th smallest (binarisation) and the K-th smallest (neighbourhood mean)
+        const bool want_bin = pd.k_bin > 0 && pd.k_bin < N;
+        const bool want_mean = mat < 3 && rowmean != nullptr;
+        const int Ke = K < N ? K : N;
+        uint32_t selA = 0, selB = 0;
+        {
+            int* wh = s_hist + (threadIdx.x >> 5) * 256;
+            uint32_t* wc = s_cand + (threadIdx.x >> 5) * 64;
+            int* wn = s_ccnt + (threadIdx.x >> 5) * 2;
+            if (want_bin) ef_warp_select2<R>(keys, N, pd.k_bin - 1, Ke - 1, want_mean, wh, wc, wn, selA, selB);
+            else if (want_mean) ef_warp_select2<R>(keys, N, Ke - 1, 0, false, wh, wc, wn, selB, selA);
+        }
         const int kb = pd.k_bin;
         if (kb <= 0) {
 #pragma unroll
@@ -217,7 +316,7 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
 #pragma unroll
             for (int q = 0; q < R; ++q) { const int j = q * 32 + lane; if (j < N) brow[j] = 1; }
         } else {
-            const uint32_t kk = ef_warp_select<R>(keys, kb - 1);          // kb-th smallest
+            const uint32_t kk = selA;                                     // kb-th smallest
             int less = 0;
 #pragma unroll
             for (int q = 0; q < R; ++q) less += (keys[q] < kk);
@@ -235,8 +334,7 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
         }
         if (mat < 3 && rowmean) {
             // np.mean(np.partition(C, K, 1)[:, 0:K], 1): mean of the K smallest (float32)
-            const int Ke = K < N ? K : N;
-            const uint32_t kk = ef_warp_select<R>(keys, Ke - 1);
+            const uint32_t kk = selB;
             float s = 0.f;
             int less = 0;
 #pragma unroll

@@ -377,7 +377,10 @@ def run_ours(args, rank, world, local_rank):
     crp_flop = 2.0 * 108 * st["crp_cells"] + 5.0 * st["crp_cells"]
     crp_tflops = crp_flop / (ms_crp * 1e-3) / 1e12
     tr = measured_traffic() or {}
-    n_crp_launch = max(1, 2 * st["n_batches"])
+    split = "split" in st.get("crp_kernels", [])
+    # CRP launches of one step: two strip launches per batch (monolithic kernels) or the phase-split pipeline's
+    # pivot / count / select per chunk + edges + binarise (everything acoss_serra09_pairs launched except the DP and OTI kernels)
+    n_crp_launch = max(1, (st["n_launches"] - n_dp_launch - st["n_batches"]) if split else 2 * st["n_batches"])
     dp_traffic = tr["dp_dram_bytes_per_crp_byte"] * st["crp_bytes"] / n_dp_launch if "dp_dram_bytes_per_crp_byte" in tr else None
     crp_traffic = tr["crp_dram_bytes_per_cell"] * st["crp_cells"] / n_crp_launch if "crp_dram_bytes_per_cell" in tr else None
     kernels = [
@@ -385,12 +388,13 @@ def run_ours(args, rank, world, local_rank):
          "frac": dp_gbs / pk["hbm"], "traffic": dp_traffic, "ms_per_step": ms_dp, "launches_per_step": n_dp_launch,
          "streamed_bytes_per_launch": dp_streamed / n_dp_launch, "streamed_over_algorithmic": dp_streamed / dp_bytes,
          "gcups": gcups, "share_of_step": ms_dp / ms_tot},
-        {"kernel": "crp_strip_gemm_kernel x2 (cross-similarity + thresholds + binarise)" if args.crp_mode in (0, 4)
-                   else "crp_strip kernels (cross-similarity + thresholds + binarise)",
+        {"kernel": ("crp_pivot / crp_stream<0> / crp_select / crp_stream<1> kernels (phase-split: cross-similarity + thresholds + binarise)" if split
+                    else "crp_strip_gemm_kernel x2 (cross-similarity + thresholds + binarise)" if "gemm" in st.get("crp_kernels", [])
+                    else "crp_strip kernels (cross-similarity + thresholds + binarise)"),
          "bound": "tensor", "achieved": crp_tflops,
          "peak": pk["bf16_sus"], "unit": "TFLOP/s", "frac": crp_tflops / pk["bf16_sus"], "traffic": crp_traffic,
-         "traffic_note": "DRAM bytes per launch (2 launches per batch): ncu dram bytes per CRP cell (profiles/traffic.json) x cells per launch; "
-                         "the CRP itself is 1 B per cell and pass, the rest is list spill written back from L2",
+         "traffic_note": "DRAM bytes per launch: ncu dram bytes per CRP cell over all CRP launches (profiles/traffic.json) x cells / launches per step; "
+                         "the CRP itself is 1 B per cell, the rest is the list scratch between the count and the selection kernels",
          "launches_per_step": n_crp_launch, "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
          # what the tensor pipe actually executes: three streaming passes (column count, row count, binarise) of 41 TF32 MMAs
          # of 128x256x8 per 128x256 tile = 656 flop per cell and pass (tile padding and the sample MMAs not counted), against
@@ -472,16 +476,19 @@ def run_e2e(args, ctx, ds, tracks, all_pairs, mine, world, rank, local_rank):
             for w, t in zip(ds["work_ids"], ds["track_ids"]):
                 f.write("%s,%s\n" % (w, t))
         sink = io.StringIO()
+        chen = args.config == "C4"
+        cls = acoss_b200.ChenFusion if chen else acoss_b200.Serra09
         with contextlib.redirect_stdout(sink):
-            s = acoss_b200.Serra09(csv, os.path.join(tmp, "feat") + "/", shortname="bench", downsample_fac=ds["fac"],
-                                   cachedir=os.path.join(tmp, "cache"), device=local_rank)
+            s = cls(csv, os.path.join(tmp, "feat") + "/", shortname="bench", downsample_fac=ds["fac"],
+                    cachedir=os.path.join(tmp, "cache"), device=local_rank)
         s._ctx = ctx
         for k, t in enumerate(tracks):
             s.all_feats[k] = t
             s.cliques.setdefault(ds["labels"][k], set([])).add(k)
         n = len(tracks)
-        h2d = sum(t.nbytes for t in tracks) + 8 * (n + 1) + all_pairs[mine].nbytes + 2 * 4 * n * n + 4 * n
-        d2h = 4 * len(mine) + 4 * n * n + 8 * n
+        nm = 2 if chen else 1               # score matrices
+        h2d = sum(t.nbytes for t in tracks) + 8 * (n + 1) + all_pairs[mine].nbytes + nm * 2 * 4 * n * n + 4 * n + (nm * 4 * n * n if chen else 0)
+        d2h = nm * 4 * len(mine) + nm * 4 * n * n + 8 * n + (8 * n * n if chen else 0)
         times = []
         for it in range(1 + args.steps):          # 1 warm-up
             if world > 1:
@@ -490,10 +497,17 @@ def run_e2e(args, ctx, ds, tracks, all_pairs, mine, world, rank, local_rank):
             t0 = time.perf_counter()
             with contextlib.redirect_stdout(sink):
                 s._uploaded = False
-                s.Ds["main"][:, :] = 0
+                if chen:
+                    s.Ds.pop("Late", None)
+                    for key in ("qmax", "dmax"):
+                        s.Ds[key][:, :] = 0
+                else:
+                    s.Ds["main"][:, :] = 0
                 s.all_pairwise(1, symmetric=True)
                 s.normalize_by_length()
-                res = s.getEvalStatistics("main")
+                if chen:
+                    s.do_late_fusion()
+                res = s.getEvalStatistics("Late" if chen else "main")
             torch.cuda.synchronize(dev)
             if world > 1:
                 dist.barrier()
@@ -505,7 +519,9 @@ def run_e2e(args, ctx, ds, tracks, all_pairs, mine, world, rank, local_rank):
         sec = float(tt[0])
         s.cleanup_memmap()
         return {"value": len(all_pairs) / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": sec * 1e3, "api": "Serra09.all_pairwise + normalize_by_length + getEvalStatistics",
+                "ms_per_step": sec * 1e3,
+                "api": ("ChenFusion.all_pairwise + normalize_by_length + do_late_fusion + getEvalStatistics('Late')" if chen
+                        else "Serra09.all_pairwise + normalize_by_length + getEvalStatistics"),
                 "MAP": res[3]}
     finally:
         os.chdir(cwd)

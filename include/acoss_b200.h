@@ -106,7 +106,10 @@ int acoss_ctx_synchronize(acoss_ctx *ctx);
 /* Tuning / test knobs of a context.  Keys:
  *   "crp_budget_bytes"       per-batch CRP working set of acoss_serra09_pairs* (default: a quarter of the free HBM,
  *                            at most 32 GiB; also settable by the environment variable ACOSS_CRP_BUDGET_MB at creation)
- *   "auto_split"             1: crp_mode 0 (auto) picks the phase-split CRP pipeline (crp_mode 5) where it applies
+ *   "auto_split"             1 (default): crp_mode 0 (auto) picks the phase-split CRP pipeline (crp_mode 5) for batches whose reference
+ *                            tracks have >= 1024 embedded rows; 0: auto never uses it
+ *   "piv_nsigma_x10"         bracket half-width of the phase-split pivots in tenths of a binomial sigma (default 25)
+ *   "split_overlap"          1: selection kernels on a second stream beside the next chunk's streaming kernels (default 0: no gain measured)
  *   "count_hh"               1: the phase-split count pass multiplies the TF32 hi parts only (a third of the tensor work, a wider
  *                            candidate band in the selection); results are bit-identical either way
  *   "ef_simt_csm"            1: acoss_earlyfusion_upload skips the tensor-core operand planes (the CSMs then run on the

@@ -18,6 +18,13 @@ def main():
     for L in lens:
         labels, works, tids, hp = synth.make_tracks(n // 2, 2, 0, 5, L, L)
         hp = [h[:L] for h in hp]
+        if os.environ.get("ACOSS_PROBE_IID"):        # frames without any temporal structure (the worst case for the spread sample)
+            rng = np.random.default_rng(7)
+            base = rng.random((L + 50, 12)).astype(np.float32)
+            hp = []
+            for k in range(n):
+                x = np.roll(base[k % 7: k % 7 + L], k % 12, axis=1) + 0.08 * rng.random((L, 12)).astype(np.float32)
+                hp.append(np.ascontiguousarray(x / x.max(axis=1, keepdims=True), np.float32))
         ctx.upload_tracks(hp)
         i, j = np.triu_indices(n, 1)
         pairs = np.stack([i, j], 1).astype(np.int32)
