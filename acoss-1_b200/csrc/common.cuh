@@ -1,6 +1,7 @@
 // common.cuh -- shared device/host definitions of the acoss_b200 hot path (sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_bf16.h>
 #include <stdint.h>
 
 #define ACOSS_NBINS 12

@@ -112,6 +112,20 @@ __device__ __forceinline__ void gm_mma(uint32_t d_tmem, uint32_t adesc_lo, uint3
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
         "}\n" ::"r"(d_tmem), "r"(adesc_lo), "r"(bdesc_lo), "r"((uint32_t)GM_IDESC), "r"(accumulate), "r"((uint32_t)GM_DESC_HI) : "memory");
 }
+// Same for bf16 operands (kind::f16, K = 16 per instruction = two 16-byte chunks of eight values), fp32 accumulation in the same TMEM tile
+#define GM_IDESC_BF16 ((1u << 4) | (1u << 7) | (1u << 10) | ((GM_TN >> 3) << 17) | ((GM_ROWS >> 4) << 24))
+__device__ __forceinline__ void gm_mma_bf16(uint32_t d_tmem, uint32_t adesc_lo, uint32_t bdesc_lo, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b64 da, {%1, %5};\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem), "r"(adesc_lo), "r"(bdesc_lo), "r"((uint32_t)GM_IDESC_BF16), "r"(accumulate), "r"((uint32_t)GM_DESC_HI) : "memory");
+}
 // low descriptor word of (base + byte offset, LBO): additive in the offset because shared memory addresses stay below 256 KB
 #define GM_DLO(base_lo, off, lbo) ((base_lo) + (((uint32_t)(off)) >> 4) + ((((uint32_t)(lbo)) >> 4) << 16))
 // barrier over the 16 consumer warps only (the producer warp never joins it)

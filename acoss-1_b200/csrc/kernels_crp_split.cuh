@@ -44,12 +44,27 @@
 #define SP_SEL_LPL (SP_LIST_STRIDE / 32)     // list entries per lane in the selection kernel
 
 // ---- per-track operand store (built once at upload, m = 9, tau = 1) -------------------------------------------------
-// planes:  [6][P][16 B], P = 256 * n_tiles + 8 entries, plane order L0 L1 L2 H0 H1 H2 (the side-B order of gm_issue_tile):
-//          entry e = bins 4 c3 .. 4 c3 + 3 of frame e, TF32 hi / lo parts; zero past the end of the track
+// planes:  [6][P][16 B], P = 256 * n_tiles + 8 entries, entry e = frame e, zero past the end of the track:
+//          planes 3 4 5 = H0 H1 H2: bins 4 c3 .. 4 c3 + 3 as TF32 hi parts (the hi.hi product, 14 tf32 MMAs per tile)
+//          planes 0 1 2 = the CROSS-PRODUCT operands in bf16 (x_hi y_lo + x_lo y_hi needs 8 bits of either factor: the error
+//          this adds is 2^-18 (xx + yy), 3 % of E), laid out so that 14 kind::f16 MMAs (K = 16) replace 27 tf32 ones:
+//            plane 0 = bf16(y_lo) bins 0..7, plane 1 = bf16(y_hi) bins 0..7      (K = [x_hi 0..7 | x_lo 0..7] . [y_lo | y_hi], one MMA per delay)
+//            plane 2 = [bf16(y_lo) bins 8..11 | bf16(y_hi) bins 8..11]           (against [x_hi 8..11 | x_lo 8..11], two delays per MMA)
 // norms:   [12 rotations][256 * n_tiles][16 B] = (1, 1, |y|^2 hi, |y|^2 lo) from the exact self-dot table of that rotation;
 //          padding columns get (1, 1, GM_BIG, 0): rho~ huge, never below a pivot or an edge
 // sdmax:   [12] max of the self-dot table per rotation (the strip kernels' error bound uses a per-pair E)
 __host__ __device__ __forceinline__ int sp_tiles(int emb) { return emb > 0 ? (emb + GM_TN - 1) / GM_TN : 0; }
+
+// eight floats -> eight bf16 (round to nearest even) in one 16-byte operand chunk, K order = argument order
+__device__ __forceinline__ uint4 sp_bf16x8(float a0, float a1, float a2, float a3, float a4, float a5, float a6, float a7)
+{
+    const __nv_bfloat162 p0 = __floats2bfloat162_rn(a0, a1), p1 = __floats2bfloat162_rn(a2, a3);
+    const __nv_bfloat162 p2 = __floats2bfloat162_rn(a4, a5), p3 = __floats2bfloat162_rn(a6, a7);
+    uint4 r;
+    r.x = *reinterpret_cast<const uint32_t*>(&p0); r.y = *reinterpret_cast<const uint32_t*>(&p1);
+    r.z = *reinterpret_cast<const uint32_t*>(&p2); r.w = *reinterpret_cast<const uint32_t*>(&p3);
+    return r;
+}
 
 __global__ void sp_planes_kernel(const float* __restrict__ frames, const int64_t* __restrict__ offs, const int32_t* __restrict__ emb_len,
                                  const int64_t* __restrict__ op_off, unsigned char* __restrict__ opb, int track0)
@@ -69,14 +84,19 @@ __global__ void sp_planes_kernel(const float* __restrict__ frames, const int64_t
         x[0] = x[1] = x[2] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     unsigned char* base = opb + op_off[2 * track];
+    float h[12], l[12];
 #pragma unroll
     for (int c3 = 0; c3 < 3; ++c3) {
         float4 hi, lo;
         tf32_split(x[c3].x, hi.x, lo.x); tf32_split(x[c3].y, hi.y, lo.y);
         tf32_split(x[c3].z, hi.z, lo.z); tf32_split(x[c3].w, hi.w, lo.w);
-        *reinterpret_cast<float4*>(base + ((size_t)c3 * P + e) * 16) = lo;
         *reinterpret_cast<float4*>(base + ((size_t)(3 + c3) * P + e) * 16) = hi;
+        h[4 * c3] = hi.x; h[4 * c3 + 1] = hi.y; h[4 * c3 + 2] = hi.z; h[4 * c3 + 3] = hi.w;
+        l[4 * c3] = lo.x; l[4 * c3 + 1] = lo.y; l[4 * c3 + 2] = lo.z; l[4 * c3 + 3] = lo.w;
     }
+    *reinterpret_cast<uint4*>(base + ((size_t)0 * P + e) * 16) = sp_bf16x8(l[0], l[1], l[2], l[3], l[4], l[5], l[6], l[7]);
+    *reinterpret_cast<uint4*>(base + ((size_t)1 * P + e) * 16) = sp_bf16x8(h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+    *reinterpret_cast<uint4*>(base + ((size_t)2 * P + e) * 16) = sp_bf16x8(l[8], l[9], l[10], l[11], h[8], h[9], h[10], h[11]);
 }
 
 __global__ void sp_norms_kernel(const int32_t* __restrict__ emb_len, const int64_t* __restrict__ sd_off, const float* __restrict__ selfdot,
@@ -127,24 +147,44 @@ __device__ __forceinline__ SpPairBound sp_pair_bound(const PairDesc& pd, const f
     return b;
 }
 
-// stage the side-A planes of a strip (entry e = frame row0 + e: -2 x rotated bins as TF32 hi / lo; norm plane), optionally
-// only the hi planes (the sample GEMM)
+// stage the side-A planes of a strip (entry e = frame row0 + e of -2 x the rotated bins: planes 0 1 2 = TF32 hi parts per chunk of
+// four bins; planes 3 4 5 = the bf16 cross-product operands [hi 0..7], [lo 0..7], [hi 8..11 | lo 8..11], see the operand store;
+// norm plane), optionally only the hi planes (the sample GEMM)
 __device__ __forceinline__ void sp_stage_a(unsigned char* Apl, const float* __restrict__ fr_a, const float* __restrict__ sdA,
                                            int row0, int nrows, int na_frames, int rot_a, int tid, bool hi_only)
 {
-    for (int e = tid; e < (GM_ROWS + 8) * 3; e += GM_THREADS) {
-        const int fe = e / 3, c3 = e - 3 * fe;
-        const int f = row0 + fe;
-        float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
-        if (f < na_frames) {
-            const float* fp = fr_a + (int64_t)f * ACOSS_NBINS;
-            tf32_split(-2.0f * fp[rot_src(4 * c3 + 0, rot_a)], hi.x, lo.x);
-            tf32_split(-2.0f * fp[rot_src(4 * c3 + 1, rot_a)], hi.y, lo.y);
-            tf32_split(-2.0f * fp[rot_src(4 * c3 + 2, rot_a)], hi.z, lo.z);
-            tf32_split(-2.0f * fp[rot_src(4 * c3 + 3, rot_a)], hi.w, lo.w);
+    if (hi_only) {
+        for (int e = tid; e < (GM_ROWS + 8) * 3; e += GM_THREADS) {
+            const int fe = e / 3, c3 = e - 3 * fe;
+            const int f = row0 + fe;
+            float4 hi = make_float4(0.f, 0.f, 0.f, 0.f), lo = hi;
+            if (f < na_frames) {
+                const float* fp = fr_a + (int64_t)f * ACOSS_NBINS;
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 0, rot_a)], hi.x, lo.x);
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 1, rot_a)], hi.y, lo.y);
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 2, rot_a)], hi.z, lo.z);
+                tf32_split(-2.0f * fp[rot_src(4 * c3 + 3, rot_a)], hi.w, lo.w);
+            }
+            *reinterpret_cast<float4*>(Apl + c3 * GM_APLANE + fe * 16) = hi;
         }
-        *reinterpret_cast<float4*>(Apl + c3 * GM_APLANE + fe * 16) = hi;
-        if (!hi_only) *reinterpret_cast<float4*>(Apl + (3 + c3) * GM_APLANE + fe * 16) = lo;
+    } else {
+        for (int fe = tid; fe < GM_ROWS + 8; fe += GM_THREADS) {
+            const int f = row0 + fe;
+            float h[12], l[12];
+#pragma unroll
+            for (int c = 0; c < 12; ++c) { h[c] = 0.f; l[c] = 0.f; }
+            if (f < na_frames) {
+                const float* fp = fr_a + (int64_t)f * ACOSS_NBINS;
+#pragma unroll
+                for (int c = 0; c < 12; ++c) tf32_split(-2.0f * fp[rot_src(c, rot_a)], h[c], l[c]);
+            }
+#pragma unroll
+            for (int c3 = 0; c3 < 3; ++c3)
+                *reinterpret_cast<float4*>(Apl + c3 * GM_APLANE + fe * 16) = make_float4(h[4 * c3], h[4 * c3 + 1], h[4 * c3 + 2], h[4 * c3 + 3]);
+            *reinterpret_cast<uint4*>(Apl + 3 * GM_APLANE + fe * 16) = sp_bf16x8(h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+            *reinterpret_cast<uint4*>(Apl + 4 * GM_APLANE + fe * 16) = sp_bf16x8(l[0], l[1], l[2], l[3], l[4], l[5], l[6], l[7]);
+            *reinterpret_cast<uint4*>(Apl + 5 * GM_APLANE + fe * 16) = sp_bf16x8(h[8], h[9], h[10], h[11], l[8], l[9], l[10], l[11]);
+        }
     }
     if (tid < GM_ROWS) {
         float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -168,6 +208,28 @@ __device__ __forceinline__ void sp_issue_tile_hh(uint32_t d_tmem, uint32_t a0, u
         }
     gm_mma(d_tmem, GM_DLO(al, 128, GM_APLANE), GM_DLO(bl, 3 * GM_BPLANE + 128, GM_BPLANE), 1);                                        // (H0,H0) (H1,H1), offset 8
     gm_mma(d_tmem, GM_DLO(al, 2 * GM_APLANE + 128, 4 * GM_APLANE - 128), GM_DLO(bl, 5 * GM_BPLANE + 128, GM_BPLANE - 128), 1);        // (H2,H2) norms
+}
+
+// The 28 MMAs of one 128 x 256 tile of the streaming passes: the hi.hi product in TF32 (14) + both cross products in bf16 (14).
+// Measured: an MMA whose two K chunks are ADJACENT entries of one plane (LBO = 16 B: the Hankel case, the chunks of neighbouring
+// rows overlap in shared memory) takes ~153 clk, one whose chunks come from two planes ~260 clk -- the operand fetch, not the
+// arithmetic, sets the pace.  So the cross products pair consecutive delays wherever they can:
+//   bins 0..7:  x_hi . y_lo (A plane 3, B plane 0) and x_lo . y_hi (A plane 4, B plane 1): two delays per MMA, 4 + 4;
+//               delay 8 of both in ONE MMA, K = [x_hi | x_lo] . [y_lo | y_hi] (LBO = one plane)
+//   bins 8..11: the [hi | lo] chunk of two consecutive delays per MMA (A plane 5 against B plane 2), 4; delay 8 alone pairs
+//               with a chunk of zeros on the A side (`zero_saddr`, 128 x 16 bytes) so that whatever B holds there drops out
+__device__ __forceinline__ void sp_issue_tile_mixed(uint32_t d_tmem, uint32_t a0, uint32_t b0, uint32_t zero_saddr)
+{
+    sp_issue_tile_hh(d_tmem, a0, b0);
+    const uint32_t al = (a0 & 0x3FFFFu) >> 4, bl = (b0 & 0x3FFFFu) >> 4;
+#pragma unroll
+    for (int pl = 0; pl < 3; ++pl)
+#pragma unroll
+        for (int kp = 0; kp < 4; ++kp)
+            gm_mma_bf16(d_tmem, GM_DLO(al, (3 + pl) * GM_APLANE + 32 * kp, 16), GM_DLO(bl, pl * GM_BPLANE + 32 * kp, 16), 1);
+    gm_mma_bf16(d_tmem, GM_DLO(al, 3 * GM_APLANE + 128, GM_APLANE), GM_DLO(bl, 128, GM_BPLANE), 1);
+    const uint32_t a8 = a0 + 5 * GM_APLANE + 128;                          // delay 8 of plane 5; its K partner is the zero chunk
+    gm_mma_bf16(d_tmem, ((a8 & 0x3FFFFu) >> 4) + (((zero_saddr - a8) >> 4) << 16), GM_DLO(bl, 2 * GM_BPLANE + 128, 16), 1);
 }
 
 // geometry of one strip task, shared by all kernels
@@ -383,7 +445,8 @@ template <int MODE> struct SpStreamSmem {
     static constexpr int ARAW_OFF = EDGE_OFF + (MODE == 1 ? SP_EDGE_SLOTS * GM_TN * 4 : 0);
     static constexpr int AMB_OFF = ARAW_OFF + (MODE == 1 ? GM_ARAW_BYTES : 0);
     static constexpr int ROWV_OFF = AMB_OFF + (MODE == 1 ? SP_AMB_CAP * 4 : 0);
-    static constexpr int MBAR_OFF = ROWV_OFF + 4 * GM_ROWV_BYTES;           // s_xx s_th s_loq + spare
+    static constexpr int ZERO_OFF = ROWV_OFF + 4 * GM_ROWV_BYTES;           // s_xx s_th s_loq + spare; then 128 x 16 bytes of zeros
+    static constexpr int MBAR_OFF = ZERO_OFF + GM_ROWS * 16;
     static constexpr int BYTES = MBAR_OFF + 16 * 8 + 64;
 };
 
@@ -418,6 +481,8 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     unsigned long long n_exact = 0;
 
     if (warp == 0) gm_tmem_alloc(tmem_holder);
+    for (int e = tid; e < GM_ROWS * 4; e += SP_BLOCK) reinterpret_cast<uint32_t*>(gsm + L::ZERO_OFF)[e] = 0u;
+    fence_proxy_async_smem();              // the zero chunk is read by the tensor core (async proxy)
     if (tid == 0) {
         mbar_init(mb_tfull, 1); mbar_init(mb_tfull + 1, 1);
         mbar_init(mb_tempty, GM_WARPS); mbar_init(mb_tempty + 1, GM_WARPS);
@@ -491,7 +556,7 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 tc_fence_after();
                 if (gm_elect_one()) {
                     if (MODE == 2) sp_issue_tile_hh(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES);
-                    else gm_issue_tile(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES);
+                    else sp_issue_tile_mixed(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES, smem_u32(gsm + L::ZERO_OFF));
                     umma_commit(mb_tfull + buf);
                     umma_commit(mb_bempty + sb);
                 }

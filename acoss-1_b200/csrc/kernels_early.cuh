@@ -183,6 +183,13 @@ __device__ __forceinline__ uint32_t ef_warp_select(const uint32_t (&keys)[R], in
     return ans;
 }
 
+// R-loops over a row's keys (element q * 32 + lane): blocks of four q behind ONE warp-uniform branch, so that a row shorter than
+// 32 R pays for the blocks it has (a per-element guard is if-converted and the padding then costs as much as the data).
+// Needs `N` (the row length) in scope.
+#define EF_Q(q, ...)                                                             \
+    _Pragma("unroll") for (int qb_ = 0; qb_ < R; qb_ += 4)                         \
+        if (qb_ * 32 < N) { _Pragma("unroll") for (int q = qb_; q < qb_ + 4 && q < R; ++q) { __VA_ARGS__ } }
+
 // Two order statistics of one row at once (ranks kA and, if wantB, kB; 0-based) without the 32-step bitwise descent (2 x 32 x R
 // compare-and-count instructions per row were 49 % of an EarlyFusion step): one 256-bin histogram over the row's key range in
 // shared memory (bins are linear in KEY space: (key - min) >> shift, exact and monotone), a scan that locates the bin of each
@@ -194,11 +201,9 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
 {
     const int lane = threadIdx.x & 31;
     uint32_t mn = 0xffffffffu, mx = 0u;
-#pragma unroll
-    for (int q = 0; q < R; ++q) {
+    EF_Q(q,
         mn = min(mn, keys[q]);                                   // padding keys are 0xffffffff
-        if (q * 32 + lane < N) mx = max(mx, keys[q]);
-    }
+        if (q * 32 + lane < N) mx = max(mx, keys[q]);)
     mn = __reduce_min_sync(0xffffffffu, mn);
     mx = __reduce_max_sync(0xffffffffu, mx);
     const uint32_t range = mx - mn;
@@ -207,9 +212,7 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
     h4[lane] = make_int4(0, 0, 0, 0); h4[lane + 32] = make_int4(0, 0, 0, 0);
     if (lane < 2) ccnt[lane] = 0;
     __syncwarp();
-#pragma unroll
-    for (int q = 0; q < R; ++q)
-        if (q * 32 + lane < N) atomicAdd(&hist[(keys[q] - mn) >> shift], 1);
+    EF_Q(q, if (q * 32 + lane < N) atomicAdd(&hist[(keys[q] - mn) >> shift], 1);)
     __syncwarp();
     const int4 ca = h4[2 * lane], cb = h4[2 * lane + 1];             // bins 8 lane .. 8 lane + 7
     const int c[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
@@ -237,13 +240,12 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
         bt[w] = __shfl_sync(0xffffffffu, b_, src);
         below[w] = __shfl_sync(0xffffffffu, bl, src);
     }
-#pragma unroll
-    for (int q = 0; q < R; ++q)
+    EF_Q(q,
         if (q * 32 + lane < N) {
             const int b = (int)((keys[q] - mn) >> shift);
             if (b == bt[0]) { const int p = atomicAdd(&ccnt[0], 1); if (p < 32) cand[p] = keys[q]; }
             if (wantB && b == bt[1]) { const int p = atomicAdd(&ccnt[1], 1); if (p < 32) cand[32 + p] = keys[q]; }
-        }
+        })
     __syncwarp();
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
@@ -270,7 +272,7 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
 // One warp per (pair, matrix, row): binarise the k_bin smallest (ties -> lowest column) and, for the three
 // CSMs (want_mean), the mean of the K smallest.  Rows up to 32*R columns.  which = matrix index 0..3.
 template <int R>
-__global__ void __launch_bounds__(256, R >= 32 ? 2 : 3)
+__global__ void __launch_bounds__(256, R >= 64 ? 2 : 3)
 ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_task_off, int n_pairs, int64_t n_rows_total,
               int first_mat, int n_mats, int K, const float* __restrict__ csm, uint8_t* __restrict__ bin,
               float* __restrict__ rowmean)
@@ -293,7 +295,8 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
         const float* row = csm + pd.csm_off + ((int64_t)mat * pd.M + i) * N;
         uint32_t keys[R];
 #pragma unroll
-        for (int q = 0; q < R; ++q) { const int j = q * 32 + lane; keys[q] = (j < N) ? ef_key(row[j]) : 0xffffffffu; }
+        for (int q = 0; q < R; ++q) keys[q] = 0xffffffffu;
+        EF_Q(q, const int j = q * 32 + lane; if (j < N) keys[q] = ef_key(row[j]);)
         uint8_t* brow = bin + pd.bin_off + ((int64_t)mat * pd.M + i) * pd.pitch;
         for (int j = N + lane; j < pd.pitch; j += 32) brow[j] = 0;
         // both order statistics of the row in one go: the kb-th smallest (binarisation) and the K-th smallest (neighbourhood mean)
@@ -310,35 +313,29 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
         }
         const int kb = pd.k_bin;
         if (kb <= 0) {
-#pragma unroll
-            for (int q = 0; q < R; ++q) { const int j = q * 32 + lane; if (j < N) brow[j] = 0; }
+            EF_Q(q, const int j = q * 32 + lane; if (j < N) brow[j] = 0;)
         } else if (kb >= N) {
-#pragma unroll
-            for (int q = 0; q < R; ++q) { const int j = q * 32 + lane; if (j < N) brow[j] = 1; }
+            EF_Q(q, const int j = q * 32 + lane; if (j < N) brow[j] = 1;)
         } else {
             const uint32_t kk = selA;                                     // kb-th smallest
             int less = 0;
-#pragma unroll
-            for (int q = 0; q < R; ++q) less += (keys[q] < kk);
+            EF_Q(q, less += (keys[q] < kk);)
             less = __reduce_add_sync(0xffffffffu, less);
             int ties_left = kb - less;
-#pragma unroll
-            for (int q = 0; q < R; ++q) {
+            EF_Q(q,
                 const int j = q * 32 + lane;
                 const bool eq = (j < N) && keys[q] == kk;
                 const unsigned meq = __ballot_sync(0xffffffffu, eq);
                 const bool one = (j < N) && (keys[q] < kk || (eq && __popc(meq & ((1u << lane) - 1u)) < ties_left));
                 ties_left -= __popc(meq);
-                if (j < N) brow[j] = one ? 1 : 0;
-            }
+                if (j < N) brow[j] = one ? 1 : 0;)
         }
         if (mat < 3 && rowmean) {
             // np.mean(np.partition(C, K, 1)[:, 0:K], 1): mean of the K smallest (float32)
             const uint32_t kk = selB;
             float s = 0.f;
             int less = 0;
-#pragma unroll
-            for (int q = 0; q < R; ++q) if (keys[q] < kk) { s += ef_key_inv(keys[q]); ++less; }
+            EF_Q(q, if (keys[q] < kk) { s += ef_key_inv(keys[q]); ++less; })
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
             less = __reduce_add_sync(0xffffffffu, less);
             s += (float)(Ke - less) * ef_key_inv(kk);

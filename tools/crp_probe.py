@@ -35,7 +35,9 @@ def main():
         st = ctx.pair_stats()
         if c0 is not None:
             c1 = ctx.debug_counters_ext(16)
-            print("  counters", [int(b) for b in c1])
+            import struct
+            err = struct.unpack("f", struct.pack("I", int(c1[14]) & 0xFFFFFFFF))[0]
+            print("  counters", [int(b) for b in c1], " max |rho~ - rho| / (xx + yy) on the exact cells = %.1f u (bound 2048 u)" % (err * 2.0 ** 24))
         print("L=%d mode=%d pairs=%d crp %.1f ms  %.3e cells/s   dp %.2f ms %.0f GCUPS  exact %.4f fallback %d" % (
             L, mode, len(pairs), st["ms_crp"], st["crp_cells"] / st["ms_crp"] * 1e3, st["ms_dp"],
             st["dp_cells"] / st["ms_dp"] / 1e6, st["n_exact_cells"] / (2.0 * st["crp_cells"]), st["n_fallback_rows"]))
