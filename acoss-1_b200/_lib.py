@@ -53,6 +53,7 @@ SYMBOLS = {
     "acoss_version": (ctypes.c_char_p, []),
     "acoss_ctx_stream": (c_vp, [c_vp]),
     "acoss_ctx_synchronize": (ctypes.c_int, [c_vp]),
+    "acoss_ctx_set_stream": (ctypes.c_int, [c_vp, c_vp]),
     "acoss_ctx_set_option": (ctypes.c_int, [c_vp, ctypes.c_char_p, ctypes.c_int64]),
     "acoss_upload_tracks": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
     "acoss_median_downsample": (ctypes.c_int, [c_vp, c_f32p, c_i64p, ctypes.c_int32, ctypes.c_int32, c_f32p, c_i64p]),
@@ -225,6 +226,11 @@ class Context(object):
         pairs = _np(pairs, np.int32).reshape(-1, 2)
         self._ck(self.lib.acoss_serra09_pairs_dev(self.h, _ptr(pairs, ctypes.c_int32), pairs.shape[0], ctypes.byref(params),
                                                   c_vp(out_q_ptr or 0), c_vp(out_d_ptr or 0)))
+
+    def set_stream(self, cuda_stream):
+        """Order every later call on the caller's stream (an int cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream);
+        None / 0 returns to the context's own stream."""
+        self._ck(self.lib.acoss_ctx_set_stream(self.h, c_vp(cuda_stream or 0)))
 
     def serra09_topk(self, queries, db, k, params=None, which="qmax", norm="serra09"):
         """Per-query top-k of queries x db (track indices of the uploaded store) without the Q x N matrix: returns

@@ -49,9 +49,17 @@ struct DevBuf {
 
 struct acoss_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;    // the stream every call of this context is ordered on (own_stream, or the caller's: acoss_ctx_set_stream)
+    cudaStream_t own_stream = nullptr;
     cudaStream_t stream2 = nullptr;   // phase-split pipeline: the selection kernels run beside the next chunk's streaming kernels
     cudaEvent_t ev_cnt[2] = {}, ev_sel[2] = {};
+    // pair pipeline: the per-batch descriptors / strip tasks / DP order go up on a copy stream from pinned staging, into the set
+    // (batch parity) the running batch does not use, so that the device never waits for the host between batches
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_up[2] = {}, ev_done[2] = {};
+    void* h_pin[2] = {nullptr, nullptr};
+    size_t h_pin_cap[2] = {0, 0};
+    DevBuf d_descs_alt, d_tasks_alt, d_dp_order_alt;
     float piv_nsigma = 2.5f;          // bracket half-width of the phase-split pivots in binomial sigmas ("piv_nsigma_x10")
     int split_overlap = 0;            // "split_overlap": 0 = all phase-split kernels on one stream
     std::string err;
@@ -126,11 +134,15 @@ extern "C" int acoss_ctx_create(int device, acoss_ctx** out)
     ctx->device = device;
     e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); delete ctx; return ACOSS_ERR_CUDA; }
+    ctx->own_stream = ctx->stream;
     for (auto& ev : ctx->ev) cudaEventCreate(&ev);
     if (cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess) ctx->stream2 = nullptr;
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) ctx->copy_stream = nullptr;
     for (int i = 0; i < 2; ++i) {
         cudaEventCreateWithFlags(&ctx->ev_cnt[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&ctx->ev_sel[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_up[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming);
     }
     cudaDeviceGetAttribute(&ctx->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
@@ -154,7 +166,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->d_frames, &ctx->d_offs, &ctx->d_emb, &ctx->d_sd_off, &ctx->d_selfdot,
-                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_dp_order, &ctx->d_descs, &ctx->d_tasks, &ctx->d_thr, &ctx->d_crp,
+                      &ctx->d_gchroma, &ctx->d_fnorm, &ctx->d_smpop, &ctx->d_dp_order, &ctx->d_descs, &ctx->d_tasks, &ctx->d_descs_alt, &ctx->d_tasks_alt, &ctx->d_dp_order_alt, &ctx->d_thr, &ctx->d_crp,
                       &ctx->d_scores, &ctx->d_misc, &ctx->d_misc2, &ctx->d_counters, &ctx->d_lists,
                       &ctx->d_opb, &ctx->d_opn, &ctx->d_op_off, &ctx->d_sdmax, &ctx->d_piv, &ctx->d_cnt4, &ctx->d_lcnt, &ctx->d_slists,
                       &ctx->d_edges, &ctx->d_fb,
@@ -164,9 +176,16 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
                       &ctx->d_ef_planes[0], &ctx->d_ef_planes[1], &ctx->d_ef_planes[2], &ctx->d_ef_poff[0], &ctx->d_ef_poff[1], &ctx->d_ef_poff[2]};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
-    for (int i = 0; i < 2; ++i) { if (ctx->ev_cnt[i]) cudaEventDestroy(ctx->ev_cnt[i]); if (ctx->ev_sel[i]) cudaEventDestroy(ctx->ev_sel[i]); }
+    for (int i = 0; i < 2; ++i) {
+        if (ctx->ev_cnt[i]) cudaEventDestroy(ctx->ev_cnt[i]);
+        if (ctx->ev_sel[i]) cudaEventDestroy(ctx->ev_sel[i]);
+        if (ctx->ev_up[i]) cudaEventDestroy(ctx->ev_up[i]);
+        if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+        if (ctx->h_pin[i]) cudaFreeHost(ctx->h_pin[i]);
+    }
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
-    cudaStreamDestroy(ctx->stream);
+    cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
 
@@ -193,6 +212,15 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
 }
 
 extern "C" void* acoss_ctx_stream(acoss_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" int acoss_ctx_set_stream(acoss_ctx* ctx, void* stream)
+{
+    if (!ctx) return ACOSS_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));                 // nothing of this context is left in flight on the stream it leaves
+    ctx->stream = stream ? (cudaStream_t)stream : ctx->own_stream;
+    return ACOSS_OK;
+}
 
 extern "C" int acoss_ctx_synchronize(acoss_ctx* ctx)
 {

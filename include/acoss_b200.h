@@ -102,6 +102,10 @@ const char *acoss_version(void);
 void *acoss_ctx_stream(acoss_ctx *ctx);
 /* Blocks until all work queued on the context's stream has finished. */
 int acoss_ctx_synchronize(acoss_ctx *ctx);
+/* Orders every later call of this context on the caller's stream (a cudaStream_t of the context's device, e.g.
+ * torch.cuda.current_stream().cuda_stream); NULL returns to the context's own stream.  The stream the context leaves is
+ * synchronised first.  The `_dev` entry points then need no extra synchronisation against the caller's own kernels. */
+int acoss_ctx_set_stream(acoss_ctx *ctx, void *stream);
 
 /* Tuning / test knobs of a context.  Keys:
  *   "crp_budget_bytes"       per-batch CRP working set of acoss_serra09_pairs* (default: a quarter of the free HBM,

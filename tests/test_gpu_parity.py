@@ -974,3 +974,28 @@ def test_serra09_topk_vs_full_matrix(ctx):
         ctx.serra09_topk([0], [1], 1001, prm)
     with pytest.raises(acoss_b200.AcossError):
         ctx.serra09_topk([n], [1], 3, prm)
+
+
+def test_caller_stream(ctx, oracle):
+    """acoss_ctx_set_stream: the context works on a stream the caller owns (a torch stream here): device-output scores written by
+    acoss_serra09_pairs_dev are visible to a torch kernel enqueued on the same stream without any synchronisation in between."""
+    import torch
+    rng = np.random.default_rng(8)
+    tracks = _tracks(rng, [70, 95, 120, 64])
+    ctx.upload_tracks(tracks)
+    pairs = np.array([(0, 1), (0, 2), (1, 3), (2, 3), (1, 2)], np.int32)
+    exp, _, _ = oracle.serra09_pairs(tracks, pairs)
+    st = torch.cuda.Stream(device=0)
+    out = torch.zeros(len(pairs), dtype=torch.float32, device="cuda:0")
+    try:
+        ctx.set_stream(st.cuda_stream)
+        with torch.cuda.stream(st):
+            ctx.serra09_pairs_dev(pairs, ctx.params(), out.data_ptr(), 0)
+            doubled = out * 2.0                                  # same stream: ordered after the library's kernels
+        st.synchronize()
+        assert np.array_equal(out.cpu().numpy(), exp)
+        assert np.array_equal(doubled.cpu().numpy(), 2.0 * exp)
+    finally:
+        ctx.set_stream(None)
+    q, _ = ctx.serra09_pairs(pairs)                              # back on the context's own stream
+    assert np.array_equal(q, exp)
