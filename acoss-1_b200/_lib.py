@@ -61,6 +61,7 @@ SYMBOLS = {
     "acoss_serra09_pairs_dev": (ctypes.c_int, [c_vp, c_i32p, ctypes.c_int64, ctypes.POINTER(CrpParams), c_vp, c_vp]),
     "acoss_get_pair_stats": (ctypes.c_int, [c_vp, ctypes.POINTER(PairStats)]),
     "acoss_debug_counters": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64)]),
+    "acoss_debug_mma_probe": (ctypes.c_int, [c_vp, ctypes.c_int32, c_i64p]),
     "acoss_debug_counters_ext": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int32]),
     "acoss_crp_pair": (ctypes.c_int, [c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(CrpParams), c_u8p,
                                       c_i32p, c_i32p, c_f32p, c_f32p, c_i32p]),

@@ -625,18 +625,21 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     const uint32_t buf = g & 1;
                     mbar_wait(mb_tfull + buf, (g >> 1) & 1u);
                     tc_fence_after();
+                    uint32_t rr[2][16];                       // two batches of 16 columns: one in flight while the other is processed
+                    tmem_ld16_issue(my_taddr + buf * GM_TN, rr[0]);
 #pragma unroll
                     for (int q4 = 0; q4 < 4; ++q4) {
-                        float v[16];
-                        tmem_ld16(my_taddr + buf * GM_TN + 64 * q4, v);
+                        tmem_ld_wait16(rr[q4 & 1]);
+                        if (q4 < 3) tmem_ld16_issue(my_taddr + buf * GM_TN + 64 * (q4 + 1), rr[(q4 + 1) & 1]);
                         if (rowvalid) {
                             const int jbase = t * GM_TN + 64 * q4 + 16 * cg;
 #pragma unroll
                             for (int q = 0; q < 16; ++q) {
-                                const uint32_t u = __float_as_uint(v[q] - pa);
+                                const float vq = __uint_as_float(rr[q4 & 1][q]);
+                                const uint32_t u = __float_as_uint(vq - pa);
                                 ca += u >> 31;
                                 if (u < wbits) {
-                                    ml[min(ln, GM_SUBCAP - 1)] = make_float2(v[q], __int_as_float(jbase + q));     // overflow is detected from ln
+                                    ml[min(ln, GM_SUBCAP - 1)] = make_float2(vq, __int_as_float(jbase + q));     // overflow is detected from ln
                                     ++ln;
                                 }
                             }
@@ -663,10 +666,15 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     mbar_wait(mb_tfull + buf, (g >> 1) & 1u);
                     tc_fence_after();
                     const float* lcs = loC + (g % SP_EDGE_SLOTS) * GM_TN;
+                    uint32_t rr[2][16];
+                    tmem_ld16_issue(my_taddr + buf * GM_TN, rr[0]);
 #pragma unroll
                     for (int q4 = 0; q4 < 4; ++q4) {
+                        tmem_ld_wait16(rr[q4 & 1]);
+                        if (q4 < 3) tmem_ld16_issue(my_taddr + buf * GM_TN + 64 * (q4 + 1), rr[(q4 + 1) & 1]);
                         float v[16];
-                        tmem_ld16(my_taddr + buf * GM_TN + 64 * q4, v);
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) v[q] = __uint_as_float(rr[q4 & 1][q]);
                         const int cbase = 64 * q4 + 16 * cg, jbase = t * GM_TN + cbase;
                         const float4* lc = reinterpret_cast<const float4*>(lcs + cbase);
                         uint32_t w[4], amask = 0;
@@ -1079,4 +1087,55 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     }
     if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
     if (lane == 0 && max_err > 0.0f) atomicMax(&counters[14], (unsigned long long)__float_as_uint(max_err));
+}
+
+// ---- measurement aid: clocks per MMA of the instruction mixes the streaming kernels issue (one CTA, operands = zeros) --------------
+// out[v] = clock64 ticks of `reps` back-to-back tiles of variant v: 0 = 14 TF32 (hi.hi), 1 = 41 TF32 (three-product tile),
+// 2 = 28 mixed (14 TF32 + 14 bf16), 3 = 14 bf16 with both K chunks adjacent (LBO 16), 4 = 14 bf16 with the K chunks in two planes.
+__global__ void __launch_bounds__(128, 1) sp_mma_probe_kernel(long long* __restrict__ out, int reps)
+{
+    extern __shared__ __align__(128) unsigned char psm[];
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(psm + GM_A_BYTES + GM_B_BYTES + GM_ROWS * 16);
+    uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 1);
+    for (int e = threadIdx.x; e < (GM_A_BYTES + GM_B_BYTES + GM_ROWS * 16) / 4; e += blockDim.x) reinterpret_cast<uint32_t*>(psm)[e] = 0u;
+    fence_proxy_async_smem();
+    if (threadIdx.x < 32) gm_tmem_alloc(tmem_holder);
+    if (threadIdx.x == 0) { mbar_init(mbar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_holder;
+    const uint32_t a0 = smem_u32(psm), b0 = a0 + GM_A_BYTES, z0 = b0 + GM_B_BYTES;
+    if (threadIdx.x < 32) {
+        uint32_t ph = 0;
+        for (int v = 0; v < 5; ++v) {
+            long long t0 = 0;
+            for (int warm = 0; warm < 2; ++warm) {
+                t0 = clock64();
+                if (gm_elect_one()) {
+                    for (int r = 0; r < reps; ++r) {
+                        const uint32_t d = tmem_base + (r & 1) * GM_TN;
+                        if (v == 0) sp_issue_tile_hh(d, a0, b0);
+                        else if (v == 1) gm_issue_tile(d, a0, b0);
+                        else if (v == 2) sp_issue_tile_mixed(d, a0, b0, z0);
+                        else {
+                            const uint32_t al = (a0 & 0x3FFFFu) >> 4, bl = (b0 & 0x3FFFFu) >> 4;
+                            for (int k = 0; k < 14; ++k) {
+                                if (v == 3) gm_mma_bf16(d, GM_DLO(al, 3 * GM_APLANE + 16 * (k % 8), 16), GM_DLO(bl, 16 * (k % 8), 16), k ? 1u : 0u);
+                                else gm_mma_bf16(d, GM_DLO(al, 3 * GM_APLANE + 16 * (k % 8), GM_APLANE), GM_DLO(bl, 16 * (k % 8), GM_BPLANE), k ? 1u : 0u);
+                            }
+                        }
+                    }
+                    umma_commit(mbar);
+                }
+                __syncwarp();
+                mbar_wait(mbar, ph); ph ^= 1;
+                tc_fence_after();
+            }
+            if (threadIdx.x == 0) out[v] = clock64() - t0;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) gm_tmem_free(tmem_base);
 }

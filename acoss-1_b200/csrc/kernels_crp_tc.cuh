@@ -142,6 +142,27 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
     for (int q = 0; q < 16; ++q) v[q] = __uint_as_float(r[q]);
 }
 
+// The same load split in two, so that the next 16 columns are in flight while the previous ones are processed: the registers
+// of `r` are written asynchronously and may only be read after tmem_ld_wait16(r) (tcgen05.wait::ld waits for EVERY load of the
+// thread still in flight, so the wait for one batch goes before the issue of the next).
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait16(uint32_t (&r)[16])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                   "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :
+                 : "memory");
+}
+
 // shared-memory operand layouts (bytes), rows 16 B apart inside a chunk column
 //   OpB (side-B frames, MMA A operand): [block q (2)][chunk c (8)][row m (128)][16 B]          = 32 768 B
 //   OpA (strip frames,  MMA B operand): [slice s (6)][chunk (2)][row n (32)][16 B]             =  6 144 B

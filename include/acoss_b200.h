@@ -186,6 +186,9 @@ int acoss_debug_counters(acoss_ctx *ctx, uint64_t *out16);
 /* Same, the first n of the extended set (slots 16.. hold the sub-phase cycle probes of
  * crp_strip_gemm_kernel; layout in kernels_crp_gemm.cuh). */
 int acoss_debug_counters_ext(acoss_ctx *ctx, uint64_t *out, int32_t n);
+/* Measurement aid: clock ticks of `reps` back-to-back 128 x 256 tiles of the streaming kernels' MMA mixes on one SM
+ * (0: 14 TF32, 1: 41 TF32, 2: 14 TF32 + 14 bf16, 3: 14 bf16 adjacent K chunks, 4: 14 bf16 K chunks in two planes). */
+int acoss_debug_mma_probe(acoss_ctx *ctx, int32_t reps, int64_t *out5);
 
 /* Test hook: the binary cross-recurrence plot of ONE pair, (M, N) uint8 0/1,
  * rows = query frames (ChromaCrossSimilarity output, rqa_serra09.py:66).
