@@ -633,14 +633,27 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                         if (q4 < 3) tmem_ld16_issue(my_taddr + buf * GM_TN + 64 * (q4 + 1), rr[(q4 + 1) & 1]);
                         if (rowvalid) {
                             const int jbase = t * GM_TN + 64 * q4 + 16 * cg;
+                            if (ln + 16 <= GM_SUBCAP) {
+                                // room for the whole batch: the write pointer just advances (no clamp in the dependency chain)
+                                float2* wp = ml + ln;
 #pragma unroll
-                            for (int q = 0; q < 16; ++q) {
-                                const float vq = __uint_as_float(rr[q4 & 1][q]);
-                                const uint32_t u = __float_as_uint(vq - pa);
-                                ca += u >> 31;
-                                if (u < wbits) {
-                                    ml[min(ln, GM_SUBCAP - 1)] = make_float2(vq, __int_as_float(jbase + q));     // overflow is detected from ln
-                                    ++ln;
+                                for (int q = 0; q < 16; ++q) {
+                                    const float vq = __uint_as_float(rr[q4 & 1][q]);
+                                    const uint32_t u = __float_as_uint(vq - pa);
+                                    ca += u >> 31;
+                                    if (u < wbits) { *wp = make_float2(vq, __int_as_float(jbase + q)); ++wp; }
+                                }
+                                ln = (int)(wp - ml);
+                            } else {
+#pragma unroll
+                                for (int q = 0; q < 16; ++q) {
+                                    const float vq = __uint_as_float(rr[q4 & 1][q]);
+                                    const uint32_t u = __float_as_uint(vq - pa);
+                                    ca += u >> 31;
+                                    if (u < wbits) {
+                                        ml[min(ln, GM_SUBCAP - 1)] = make_float2(vq, __int_as_float(jbase + q));     // overflow is detected from ln
+                                        ++ln;
+                                    }
                                 }
                             }
                         }
