@@ -150,7 +150,7 @@ __device__ __forceinline__ void dp_row_step(uint32_t (&Aprev)[NCH][G], uint32_t 
 // Requirements: pitch % 16 == 0 (16-byte aligned rows), N <= pitch, N <= NCH*64*G, min(M,N) small enough for
 // int16 half units (host checks: 4*min(M,N) < 32000).
 template <int G, int NCH, int ALIGN>
-__global__ void __launch_bounds__(128, ALIGN == 0 ? 4 : 1)
+__global__ void __launch_bounds__(128)
 dp_rowpar_kernel(const PairDesc* __restrict__ descs, int64_t n_pairs,
                  const uint8_t* __restrict__ crp, float* __restrict__ out,
                  const int32_t* __restrict__ order, unsigned* __restrict__ counter)

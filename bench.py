@@ -396,15 +396,17 @@ def run_ours(args, rank, world, local_rank):
          "traffic_note": "DRAM bytes per launch: ncu dram bytes per CRP cell over all CRP launches (profiles/traffic.json) x cells / launches per step; "
                          "the CRP itself is 1 B per cell, the rest is the list scratch between the count and the selection kernels",
          "launches_per_step": n_crp_launch, "ms_per_step": ms_crp, "share_of_step": ms_crp / ms_tot,
-         # what the tensor pipe actually executes: three streaming passes (column count, row count, binarise) of 41 TF32 MMAs
-         # of 128x256x8 per 128x256 tile = 656 flop per cell and pass (tile padding and the sample MMAs not counted), against
-         # the dense TF32 peak = half the measured bf16 figure
-         "executed_tflops": 3.0 * 656.0 * st["crp_cells"] / (ms_crp * 1e-3) / 1e12,
-         "executed_frac_of_tf32_peak": 3.0 * 656.0 * st["crp_cells"] / (ms_crp * 1e-3) / 1e12 / (0.5 * pk["bf16_sus"]),
-         "note": "algorithmic flop = (2*108+5)*M*N per pair (SURVEY 8(d)), peak = measured dense bf16. The kernel runs the "
-                 "contraction 2.5 times (column thresholds, row thresholds, binarise) as 3-product TF32 splits on tcgen05 "
-                 "(41 MMAs of 128x256x8 per tile = 664 executed flop per cell and pass, dense TF32 peak is half the bf16 "
-                 "figure) and decides everything near a threshold with exact fp32 chains; see DESIGN.md"},
+         # what the tensor pipe actually executes per cell and streaming pass (column count, row count, binarise; tile padding and
+         # the sample MMAs not counted): monolithic kernel 41 TF32 MMAs of 128x256x8 per 128x256 tile = 656 flop; phase-split
+         # pipeline 14 TF32 MMAs + 14 bf16 MMAs of 128x256x16 = 672 flop.  MMA instructions issue at 128 clk each at best
+         # (tools/mma_probe.py), so the tensor pipe's own floor for the three passes is mma_floor_ms.
+         "executed_tflops": 3.0 * (672.0 if split else 656.0) * st["crp_cells"] / (ms_crp * 1e-3) / 1e12,
+         "mma_per_tile_and_pass": 28 if split else 41,
+         "mma_floor_ms": 3.0 * (28 if split else 41) * 128.0 * (st["crp_cells"] / (128.0 * 256.0)) / (148.0 * (clocks.get("sm_mhz") or 1965.0) * 1e3),
+         "note": "algorithmic flop = (2*108+5)*M*N per pair (SURVEY 8(d)), peak = measured dense bf16. The kernels run the "
+                 "contraction three times (column thresholds, row thresholds, binarise) on tcgen05 -- hi.hi in TF32, the cross "
+                 "products x_hi.y_lo + x_lo.y_hi in bf16 (phase-split pipeline) or TF32 (monolithic kernel) -- and decide "
+                 "everything near a threshold with exact fp32 chains; see DESIGN.md 4.1"},
     ]
     dominant = max(kernels, key=lambda k: k["ms_per_step"])
     roofline = {k: dominant[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")}
