@@ -811,9 +811,9 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 // =====================================================================================================================
 #define SP_POOL 3072                         // candidate entries per strip (flat: a row takes what it needs, at most SP_CAND_MAX)
 #define SP_CAND_MAX 96
-#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 8 + 2 * SP_POOL * 4 + SP_SEL_WARPS * 64 * 4)
+#define SP_SEL_SMEM (GM_ARAW_BYTES + 6 * GM_ROWS * 4 + 8 + 2 * SP_POOL * 4 + SP_SEL_WARPS * 64 * 4)
 
-__global__ void __launch_bounds__(SP_SEL_THREADS, 3)
+__global__ void __launch_bounds__(SP_SEL_THREADS, 4)
 crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
                   const float* __restrict__ frames, const float* __restrict__ selfdot, const float* __restrict__ sdmax,
                   float* __restrict__ thr, int side_a_is_query, float qf,
@@ -832,6 +832,7 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     int* pool_col = s_off + GM_ROWS + 2;                                    // [SP_POOL] (row << 24) | column
     float* pool_dex = reinterpret_cast<float*>(pool_col + SP_POOL);         // [SP_POOL] approximate radicand, then the exact distance
     int* s_hist = reinterpret_cast<int*>(pool_dex + SP_POOL);               // [SP_SEL_WARPS][64]
+    int* s_pk = s_hist + SP_SEL_WARPS * 64;                                 // [GM_ROWS] sub-list boundaries of the row's compacted list
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_exact = 0;
     float max_err = 0.0f;
@@ -884,6 +885,7 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 const float2* lst = lists + srow * SP_LIST_STRIDE;
                 int* h = s_hist + warp * 64;
                 const int T = c_abr, p1 = c4r.x, p2 = p1 + c4r.y, p3 = p2 + c4r.z;
+                if (lane == 0) s_pk[r] = p1 | (p2 << 10) | (p3 << 20);
                 const int nI = (T + 31) >> 5;                                       // warp-uniform, <= SP_SEL_LPL
                 // every pass below walks the entries in blocks of four behind ONE warp-uniform branch per block (a per-entry guard is
                 // if-converted by the compiler and the empty entries then cost as much as the live ones); entries past T hold +inf
@@ -891,16 +893,15 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 _Pragma("unroll") for (int ib_ = 0; ib_ < SP_SEL_LPL; ib_ += 4)                 \
                     if (ib_ < nI) { _Pragma("unroll") for (int i = ib_; i < ib_ + 4; ++i) { __VA_ARGS__ } }
                 float lx[SP_SEL_LPL];
-                int ly[SP_SEL_LPL];
 #pragma unroll
-                for (int i = 0; i < SP_SEL_LPL; ++i) { lx[i] = INFINITY; ly[i] = 0; }
+                for (int i = 0; i < SP_SEL_LPL; ++i) lx[i] = INFINITY;
                 SP_ENTRIES(i,
                     const int e = 32 * i + lane;
                     if (e < T) {
                         const int seg = (e >= p1) + (e >= p2) + (e >= p3);
                         const int sl = e - (seg == 0 ? 0 : seg == 1 ? p1 : seg == 2 ? p2 : p3);
                         const float2 v = lst[seg * GM_SUBCAP + sl];
-                        lx[i] = v.x; ly[i] = __float_as_int(v.y);
+                        lx[i] = v.x;
                     })
                 float base = par, top = pbr;
                 if (par == plow || pbr == GM_PMAX) {                // open-ended bracket: the list's own value range
@@ -992,7 +993,7 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                         } else {
                             int at = off + incl - my_c;
                             SP_ENTRIES(i,
-                                if ((lx[i] >= c_min) && (lx[i] <= c_max)) { pool_col[at] = (r << 24) | ly[i]; pool_dex[at] = lx[i]; ++at; })
+                                if ((lx[i] >= c_min) && (lx[i] <= c_max)) { pool_col[at] = (r << 24) | (32 * i + lane); pool_dex[at] = lx[i]; ++at; })
                             if (lane == 0) s_off[r] = off;
                         }
                     }
@@ -1011,7 +1012,15 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
             for (int idx = tid; idx < n_tasks_c; idx += SP_SEL_THREADS) {
                 const int code = pool_col[idx];
                 if (code < 0) continue;
-                const int r = (code >> 24) & 0xFF, jj = code & 0xFFFFFF;
+                const int r = (code >> 24) & 0xFF, e = code & 0xFFFFFF;
+                int jj;
+                {   // entry e of the row's compacted list -> its column (second word of the list entry; the selection pass keeps
+                    // only the values in registers: 16 registers less per thread = four CTAs per SM instead of three)
+                    const int pk = s_pk[r], q1 = pk & 1023, q2 = (pk >> 10) & 1023, q3 = (pk >> 20) & 1023;
+                    const int seg = (e >= q1) + (e >= q2) + (e >= q3);
+                    const int sl = e - (seg == 0 ? 0 : seg == 1 ? q1 : seg == 2 ? q2 : q3);
+                    jj = __float_as_int(lists[((size_t)task * GM_ROWS + r) * SP_LIST_STRIDE + seg * GM_SUBCAP + sl].y);
+                }
                 const float4* bp = reinterpret_cast<const float4*>(g.fr_b + (int64_t)jj * ACOSS_NBINS);
                 const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
                 float acc = 0.0f;

@@ -197,8 +197,10 @@ __device__ __forceinline__ uint32_t ef_warp_select(const uint32_t (&keys)[R], in
 // distances) falls back to the bitwise descent.  hist: 256 ints, cand: 64 keys, ccnt: 2 ints, all private to the warp.
 template <int R>
 __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N, int kA, int kB, bool wantB,
-                                                int* hist, uint32_t* cand, int* ccnt, uint32_t& outA, uint32_t& outB)
+                                                int* hist, uint32_t* cand, int* ccnt, uint32_t& outA, uint32_t& outB,
+                                                int (&less)[2], int (&equal)[2])
 {
+    // less[w] = number of keys below the w-th result, equal[w] = number of keys equal to it (-1: unknown, the caller counts)
     const int lane = threadIdx.x & 31;
     uint32_t mn = 0xffffffffu, mx = 0u;
     EF_Q(q,
@@ -249,7 +251,7 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
     __syncwarp();
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
-        if (w == 1 && !wantB) { outB = 0; break; }
+        if (w == 1 && !wantB) { outB = 0; less[1] = -1; equal[1] = -1; break; }
         const int n_c = ccnt[w], want = (w == 0 ? kA : kB) - below[w];
         uint32_t res;
         if (n_c <= 32) {
@@ -261,8 +263,11 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
             }
             const unsigned m = __ballot_sync(0xffffffffu, lane < n_c && rank == want);
             res = __shfl_sync(0xffffffffu, mykey, m ? __ffs(m) - 1 : 0);
+            less[w] = below[w] + __popc(__ballot_sync(0xffffffffu, lane < n_c && mykey < res));
+            equal[w] = __popc(__ballot_sync(0xffffffffu, lane < n_c && mykey == res));
         } else {
             res = ef_warp_select<R>(keys, w == 0 ? kA : kB);
+            less[w] = -1; equal[w] = -1;
         }
         if (w == 0) outA = res; else outB = res;
     }
@@ -304,12 +309,17 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
         const bool want_mean = mat < 3 && rowmean != nullptr;
         const int Ke = K < N ? K : N;
         uint32_t selA = 0, selB = 0;
+        int sel_less[2] = {-1, -1}, sel_eq[2] = {-1, -1};       // [0] binarisation rank, [1] mean rank
         {
             int* wh = s_hist + (threadIdx.x >> 5) * 256;
             uint32_t* wc = s_cand + (threadIdx.x >> 5) * 64;
             int* wn = s_ccnt + (threadIdx.x >> 5) * 2;
-            if (want_bin) ef_warp_select2<R>(keys, N, pd.k_bin - 1, Ke - 1, want_mean, wh, wc, wn, selA, selB);
-            else if (want_mean) ef_warp_select2<R>(keys, N, Ke - 1, 0, false, wh, wc, wn, selB, selA);
+            if (want_bin) ef_warp_select2<R>(keys, N, pd.k_bin - 1, Ke - 1, want_mean, wh, wc, wn, selA, selB, sel_less, sel_eq);
+            else if (want_mean) {
+                int l2[2], e2[2];
+                ef_warp_select2<R>(keys, N, Ke - 1, 0, false, wh, wc, wn, selB, selA, l2, e2);
+                sel_less[1] = l2[0]; sel_eq[1] = e2[0];
+            }
         }
         const int kb = pd.k_bin;
         if (kb <= 0) {
@@ -318,17 +328,22 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
             EF_Q(q, const int j = q * 32 + lane; if (j < N) brow[j] = 1;)
         } else {
             const uint32_t kk = selA;                                     // kb-th smallest
-            int less = 0;
-            EF_Q(q, less += (keys[q] < kk);)
-            less = __reduce_add_sync(0xffffffffu, less);
-            int ties_left = kb - less;
-            EF_Q(q,
-                const int j = q * 32 + lane;
-                const bool eq = (j < N) && keys[q] == kk;
-                const unsigned meq = __ballot_sync(0xffffffffu, eq);
-                const bool one = (j < N) && (keys[q] < kk || (eq && __popc(meq & ((1u << lane) - 1u)) < ties_left));
-                ties_left -= __popc(meq);
-                if (j < N) brow[j] = one ? 1 : 0;)
+            if (sel_eq[0] == 1) {
+                // the kb-th smallest is unique (the rule for distances in general position): the kb smallest are the keys <= it
+                EF_Q(q, const int j = q * 32 + lane; if (j < N) brow[j] = keys[q] <= kk ? 1 : 0;)
+            } else {
+                int less = 0;
+                EF_Q(q, less += (keys[q] < kk);)
+                less = __reduce_add_sync(0xffffffffu, less);
+                int ties_left = kb - less;
+                EF_Q(q,
+                    const int j = q * 32 + lane;
+                    const bool eq = (j < N) && keys[q] == kk;
+                    const unsigned meq = __ballot_sync(0xffffffffu, eq);
+                    const bool one = (j < N) && (keys[q] < kk || (eq && __popc(meq & ((1u << lane) - 1u)) < ties_left));
+                    ties_left -= __popc(meq);
+                    if (j < N) brow[j] = one ? 1 : 0;)
+            }
         }
         if (mat < 3 && rowmean) {
             // np.mean(np.partition(C, K, 1)[:, 0:K], 1): mean of the K smallest (float32)
