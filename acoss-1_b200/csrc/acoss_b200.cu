@@ -90,6 +90,7 @@ struct acoss_ctx {
     DevBuf d_ef_planes[3], d_ef_poff[3];   // tensor-core operand planes of the three features + per-track byte offsets
     int ef_nkc[3] = {0, 0, 0};
     bool have_ef_planes = false;
+    int ef_cluster = 0;                   // "ef_cluster": CSM GEMM as clusters of two CTAs sharing the reference operand by TMA multicast
     int ef_force_simt = 0;                // acoss_ctx_set_option "ef_simt_csm": keep the fp32 SIMT tile kernel (comparison / fallback)
     int ef_csm_kernel_used = 0;           // 1 = SIMT tiles, 2 = tcgen05 GEMM (last acoss_earlyfusion_pairs call)
     double ef_ms[3] = {0, 0, 0}, ef_flop = 0;
@@ -152,6 +153,7 @@ extern "C" int acoss_ctx_create(int device, acoss_ctx** out)
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && free_b > 0)
             ctx->crp_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)32 << 30, free_b / 4));
     }
+    if (const char* s = getenv("ACOSS_EF_CLUSTER")) ctx->ef_cluster = atoi(s) != 0;      // measurement switch, same as option "ef_cluster"
     if (const char* s = getenv("ACOSS_CRP_BUDGET_MB")) {
         long mb = atol(s);
         if (mb > 0) ctx->crp_budget = (size_t)mb << 20;
@@ -200,6 +202,7 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
     }
     if (k == "piv_nsigma_x10") { if (value < 1 || value > 100) return ACOSS_ERR_ARG; ctx->piv_nsigma = 0.1f * (float)value; return ACOSS_OK; }
     if (k == "split_overlap") { ctx->split_overlap = value != 0; return ACOSS_OK; }
+    if (k == "ef_cluster") { ctx->ef_cluster = value != 0; return ACOSS_OK; }
     if (k == "count_hh") { ctx->count_hh = value != 0; return ACOSS_OK; }
     if (k == "auto_split") { ctx->auto_split = value != 0; return ACOSS_OK; }
     if (k == "ef_simt_csm") { ctx->ef_force_simt = value != 0; return ACOSS_OK; }

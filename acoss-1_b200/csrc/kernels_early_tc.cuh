@@ -42,7 +42,31 @@
 
 __host__ __device__ __forceinline__ int eg_chunks(int d) { return ((d + 7) / 8) * 2; }     // 16-byte chunks, padded to whole K = 8 steps
 
-struct EgTile { int32_t pair, feat, m0, n0; };
+struct EgTile { int32_t pair, feat, m0, n0; };      // m0 < 0: no tile (the odd partner of a cluster pair, see ef_gemm_kernel<2>)
+
+// ---- cluster helpers (ef_gemm_kernel<2>: two CTAs share every reference-side operand stage through TMA multicast) ----
+__device__ __forceinline__ uint32_t eg_cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void eg_cluster_sync()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void eg_mbar_arrive_remote(uint64_t* bar, uint32_t rank)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
+        "}\n" ::"r"(smem_u32(bar)), "r"(rank) : "memory");
+}
+// MMA completion -> one arrival on the mbarrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void eg_umma_commit_mc(uint64_t* bar, uint16_t mask)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
 
 // planes of one feature of all tracks: thread per (row, chunk); variant v rolls the 12 bins of every chroma frame by v and is
 // only built for the cosine feature (n_var = 4), whose rows are also normalised
@@ -89,10 +113,18 @@ struct EgFeat {
     int nkc;                          // chunks per row (even)
 };
 
+// CL = 1: one CTA per tile.  CL = 2 (launched as clusters of two CTAs): tiles[2 c] and tiles[2 c + 1] are two 128-row query
+// tiles against the SAME 256 reference rows; each CTA fetches its own query operand and HALF of the reference operand, the
+// latter multicast into both CTAs' shared memory, so a stage costs 32 KB instead of 48 KB of L2 reads per CTA (the GEMM is bound
+// by L2 -> SM operand delivery, not by the tensor pipe).  A stage buffer is refilled once BOTH CTAs' MMAs have consumed it.
+template <int CL>
 __global__ void __launch_bounds__(EG_THREADS, 1)
 ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tiles, int n_tiles,
                EgFeat f0, EgFeat f1, EgFeat f2, float* __restrict__ csm)
 {
+    const uint32_t crank = CL == 2 ? eg_cluster_rank() : 0u;
+    const int t_first = CL == 2 ? 2 * (int)(blockIdx.x >> 1) + (int)crank : (int)blockIdx.x;
+    const int t_step = CL == 2 ? 2 * (int)(gridDim.x >> 1) : (int)gridDim.x;
     extern __shared__ __align__(128) unsigned char esm[];
     unsigned char* stage0 = esm;
     float* s_yy = reinterpret_cast<float*>(esm + EG_STAGES * EG_STAGE_BYTES);          // [EG_TN] norms of the tile's reference rows
@@ -103,26 +135,33 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
 
     if (warp == 0) gm_tmem_alloc(tmem_holder);
     if (tid == 0) {
-        for (int s = 0; s < EG_STAGES; ++s) { mbar_init(mb_full + s, 1); mbar_init(mb_empty + s, 1); }
+        for (int s = 0; s < EG_STAGES; ++s) { mbar_init(mb_full + s, 1); mbar_init(mb_empty + s, CL); }
         mbar_init(mb_tfull, 1); mbar_init(mb_tfull + 1, 1); mbar_init(mb_tempty, EG_EPI_WARPS); mbar_init(mb_tempty + 1, EG_EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
+    if (CL == 2) eg_cluster_sync();              // the partner's barriers exist before anything is sent to them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_holder;
     const uint32_t st_saddr = smem_u32(stage0);
 
     if (warp == EG_EPI_WARPS) {
         // ================= TMA producer =================
-        if (lane == 0) {
+        // The 16 bulk copies of a stage (4 K chunks x hi / lo x query / reference side) are issued by 16 LANES at once: one
+        // elected lane issuing them in turn took longer per stage than the stage's six MMAs.
+        {
             uint32_t g = 0;                       // running stage count
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            const int c = lane >> 2, h = (lane >> 1) & 1, side_b = lane & 1;      // this lane's copy of a stage (lanes 0..15)
+            for (int t = t_first; t < n_tiles; t += t_step) {
                 const EgTile tl = tiles[t];
                 const EfPair pd = pairs[tl.pair];
                 const EgFeat F = tl.feat == 0 ? f0 : (tl.feat == 1 ? f1 : f2);
                 const int nkc = F.nkc;
-                const int ra = min(EG_TM, pd.M - tl.m0), rb = min(EG_TN, pd.N - tl.n0);      // valid rows: only those are copied
+                const int ra = tl.m0 >= 0 ? min(EG_TM, pd.M - tl.m0) : 0, rb = min(EG_TN, pd.N - tl.n0);      // valid rows: only those are copied
+                // reference rows this CTA fetches (CL = 2: its half, multicast to both CTAs)
+                const int b_lo = CL == 2 ? (int)crank * (EG_TN / 2) : 0;
+                const int b_cnt = CL == 2 ? max(0, min(EG_TN / 2, rb - b_lo)) : rb;
                 const int oti = tl.feat == 2 ? pd.oti % ACOSS_NBINS : 0;
                 const int var = oti & 3, qrot = oti >> 2;
                 const unsigned char* pa = F.planes + F.plane_off[pd.ta] + (size_t)var * 2 * nkc * pd.M * 16;
@@ -133,34 +172,55 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
                     const int nch = min(EG_STAGE_CH, nkc - k0);
                     unsigned char* dst = stage0 + s * EG_STAGE_BYTES;
                     const uint32_t bar = smem_u32(mb_full + s);
-                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(nch * 2 * 16 * (ra + rb))) : "memory");
-                    for (int c = 0; c < nch; ++c) {
+                    if (lane == 0)
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(nch * 2 * 16 * (ra + rb))) : "memory");
+                    __syncwarp();
+                    if (lane < 16 && c < nch) {
                         const int kc = k0 + c;
-                        // query side: a roll by 4 q permutes the three chunks of a 12-bin frame (chunk c3 of the rolled row is
-                        // chunk (c3 - q) mod 3 of the stored variant)
-                        int kca = kc;
-                        if (qrot) { const int gfr = kc / 3, c3 = kc - 3 * gfr; kca = 3 * gfr + (c3 + 3 - qrot) % 3; }
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                         ::"r"(smem_u32(dst + (h * EG_STAGE_CH + c) * EG_A_CH)),
-                                           "l"(pa + ((size_t)(h * nkc + kca) * pd.M + tl.m0) * 16), "r"((uint32_t)(ra * 16)), "r"(bar) : "memory");
+                        if (!side_b) {
+                            // query side: a roll by 4 q permutes the three chunks of a 12-bin frame (chunk c3 of the rolled row is
+                            // chunk (c3 - q) mod 3 of the stored variant)
+                            int kca = kc;
+                            if (qrot) { const int gfr = kc / 3, c3 = kc - 3 * gfr; kca = 3 * gfr + (c3 + 3 - qrot) % 3; }
+                            if (ra > 0)
+                                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                             ::"r"(smem_u32(dst + (h * EG_STAGE_CH + c) * EG_A_CH)),
+                                               "l"(pa + ((size_t)(h * nkc + kca) * pd.M + tl.m0) * 16), "r"((uint32_t)(ra * 16)), "r"(bar) : "memory");
+                        } else if (CL == 2) {
+                            if (b_cnt > 0)
+                                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+                                             ::"r"(smem_u32(dst + 2 * EG_STAGE_CH * EG_A_CH + (h * EG_STAGE_CH + c) * EG_B_CH + b_lo * 16)),
+                                               "l"(pb + ((size_t)(h * nkc + kc) * pd.N + tl.n0 + b_lo) * 16), "r"((uint32_t)(b_cnt * 16)), "r"(bar),
+                                               "h"((uint16_t)3) : "memory");
+                        } else {
                             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                                          ::"r"(smem_u32(dst + 2 * EG_STAGE_CH * EG_A_CH + (h * EG_STAGE_CH + c) * EG_B_CH)),
                                            "l"(pb + ((size_t)(h * nkc + kc) * pd.N + tl.n0) * 16), "r"((uint32_t)(rb * 16)), "r"(bar) : "memory");
                         }
                     }
+                    __syncwarp();
                 }
             }
         }
     } else if (warp == EG_EPI_WARPS + 1) {
         // ================= MMA issuer =================
         uint32_t g = 0, u = 0;                   // running stage / span counts
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int t = t_first; t < n_tiles; t += t_step) {
             const EgTile tl = tiles[t];
             const EgFeat F = tl.feat == 0 ? f0 : (tl.feat == 1 ? f1 : f2);
             const int nkc = F.nkc;
             int sidx = 0;
+            if (CL == 2 && tl.m0 < 0) {
+                // no tile on this side of the pair: the stages still arrive here (the partner's half is multicast into this CTA
+                // as well); hand every one straight back to both producers
+                for (int k0 = 0; k0 < nkc; k0 += EG_STAGE_CH, ++g) {
+                    const uint32_t s = g % EG_STAGES;
+                    mbar_wait(mb_full + s, (g / EG_STAGES) & 1u);
+                    if (lane == 0) { mbar_arrive(mb_empty + s); eg_mbar_arrive_remote(mb_empty + s, crank ^ 1u); }
+                    __syncwarp();
+                }
+                continue;
+            }
             for (int k0 = 0; k0 < nkc; k0 += EG_STAGE_CH, ++g, ++sidx) {
                 const uint32_t s = g % EG_STAGES, buf = u & 1;
                 const bool first = (sidx % EG_SPAN) == 0, last = (sidx % EG_SPAN) == EG_SPAN - 1 || k0 + EG_STAGE_CH >= nkc;
@@ -181,7 +241,7 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
                         gm_mma(tmem_base + buf * EG_TN, GM_DLO(a_hi, c * EG_A_CH, EG_A_CH), GM_DLO(b_hi, c * EG_B_CH, EG_B_CH), 1);
                         acc = 1;
                     }
-                    umma_commit(mb_empty + s);
+                    if (CL == 2) eg_umma_commit_mc(mb_empty + s, (uint16_t)3); else umma_commit(mb_empty + s);
                     if (last) umma_commit(mb_tfull + buf);
                 }
                 __syncwarp();
@@ -193,8 +253,9 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
         uint32_t u = 0;
         const int lq = warp & 3, half = warp >> 2;
         const int row = 32 * lq + lane;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int t = t_first; t < n_tiles; t += t_step) {
             const EgTile tl = tiles[t];
+            if (CL == 2 && tl.m0 < 0) continue;
             const EfPair pd = pairs[tl.pair];
             const EgFeat F = tl.feat == 0 ? f0 : (tl.feat == 1 ? f1 : f2);
             const bool cosine = tl.feat == 2;
@@ -254,5 +315,6 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
     }
     tc_fence_before();
     __syncthreads();
+    if (CL == 2) eg_cluster_sync();              // nothing of the partner is still on its way into this CTA
     if (warp == 0) gm_tmem_free(tmem_base);
 }
