@@ -90,6 +90,8 @@ struct acoss_ctx {
     DevBuf d_ef_planes[3], d_ef_poff[3];   // tensor-core operand planes of the three features + per-track byte offsets
     int ef_nkc[3] = {0, 0, 0};
     bool have_ef_planes = false;
+    int ef_dynamic_tiles = 1;             // CSM GEMM tiles handed out from a global counter ("ef_dynamic_tiles")
+    DevBuf d_ef_cnt;
     int ef_cluster = 0;                   // "ef_cluster": CSM GEMM as clusters of two CTAs sharing the reference operand by TMA multicast
     int ef_force_simt = 0;                // acoss_ctx_set_option "ef_simt_csm": keep the fp32 SIMT tile kernel (comparison / fallback)
     int ef_csm_kernel_used = 0;           // 1 = SIMT tiles, 2 = tcgen05 GEMM (last acoss_earlyfusion_pairs call)
@@ -153,7 +155,8 @@ extern "C" int acoss_ctx_create(int device, acoss_ctx** out)
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && free_b > 0)
             ctx->crp_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)32 << 30, free_b / 4));
     }
-    if (const char* s = getenv("ACOSS_EF_CLUSTER")) ctx->ef_cluster = atoi(s) != 0;      // measurement switch, same as option "ef_cluster"
+    if (const char* s = getenv("ACOSS_EF_CLUSTER")) ctx->ef_cluster = atoi(s) != 0;
+    if (const char* s = getenv("ACOSS_EF_DYNAMIC")) ctx->ef_dynamic_tiles = atoi(s) != 0;      // measurement switch, same as option "ef_cluster"
     if (const char* s = getenv("ACOSS_CRP_BUDGET_MB")) {
         long mb = atol(s);
         if (mb > 0) ctx->crp_budget = (size_t)mb << 20;
@@ -174,7 +177,7 @@ extern "C" void acoss_ctx_destroy(acoss_ctx* ctx)
                       &ctx->d_edges, &ctx->d_fb,
                       &ctx->d_sp_feats, &ctx->d_sp_offs, &ctx->d_sp_prof,
                       &ctx->d_ef_x[0], &ctx->d_ef_x[1], &ctx->d_ef_x[2], &ctx->d_ef_sq[0], &ctx->d_ef_sq[1], &ctx->d_ef_sq[2],
-                      &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin,
+                      &ctx->d_ef_cmed, &ctx->d_ef_csm, &ctx->d_ef_bin, &ctx->d_ef_cnt,
                       &ctx->d_ef_planes[0], &ctx->d_ef_planes[1], &ctx->d_ef_planes[2], &ctx->d_ef_poff[0], &ctx->d_ef_poff[1], &ctx->d_ef_poff[2]};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -202,6 +205,7 @@ extern "C" int acoss_ctx_set_option(acoss_ctx* ctx, const char* key, int64_t val
     }
     if (k == "piv_nsigma_x10") { if (value < 1 || value > 100) return ACOSS_ERR_ARG; ctx->piv_nsigma = 0.1f * (float)value; return ACOSS_OK; }
     if (k == "split_overlap") { ctx->split_overlap = value != 0; return ACOSS_OK; }
+    if (k == "ef_dynamic_tiles") { ctx->ef_dynamic_tiles = value != 0; return ACOSS_OK; }
     if (k == "ef_cluster") { ctx->ef_cluster = value != 0; return ACOSS_OK; }
     if (k == "count_hh") { ctx->count_hh = value != 0; return ACOSS_OK; }
     if (k == "auto_split") { ctx->auto_split = value != 0; return ACOSS_OK; }
