@@ -61,6 +61,29 @@ __device__ __forceinline__ void eg_mbar_arrive_remote(uint64_t* bar, uint32_t ra
         "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
         "}\n" ::"r"(smem_u32(bar)), "r"(rank) : "memory");
 }
+// wait with cluster-scope acquire (the data guarded by the barrier was written from the partner CTA)
+__device__ __forceinline__ void eg_mbar_wait_cluster(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "EGW_LOOP:\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra EGW_DONE;\n\t"
+        "bra EGW_LOOP;\n\t"
+        "EGW_DONE:\n\t"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// store one word at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void eg_st_remote(int* p, uint32_t rank, int v)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "st.shared::cluster.b32 [ra], %2;\n\t"
+        "}\n" ::"r"(smem_u32(p)), "r"(rank), "r"(v) : "memory");
+}
 // MMA completion -> one arrival on the mbarrier at this offset in every CTA of `mask`
 __device__ __forceinline__ void eg_umma_commit_mc(uint64_t* bar, uint16_t mask)
 {
@@ -139,16 +162,19 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 2 * EG_STAGES + 12);
     int* s_tile = reinterpret_cast<int*>(tmem_holder + 2);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool dynamic = CL == 1 && tile_counter != nullptr;
-    auto next_tile = [&](uint32_t& it) -> int {              // MMA and epilogue warps
+    // CL = 2: the counter hands out tile PAIRS; the leader CTA (rank 0) draws, writes the index into both CTAs' rings and signals
+    // both; every reader of either CTA releases the slot on the LEADER's empty barrier.
+    const bool dynamic = tile_counter != nullptr;
+    auto next_tile = [&](uint32_t& it) -> int {              // MMA and epilogue warps (and the producer of the non-leader CTA)
         int t;
         if (!dynamic) { t = t_first + (int)it * t_step; if (t >= n_tiles) t = -1; }
         else {
             const uint32_t q = it & 3u;
-            mbar_wait(mb_tq_full + q, (it >> 2) & 1u);
+            if (CL == 2) eg_mbar_wait_cluster(mb_tq_full + q, (it >> 2) & 1u); else mbar_wait(mb_tq_full + q, (it >> 2) & 1u);
             t = s_tile[q];
             __syncwarp();
-            if (lane == 0) mbar_arrive(mb_tq_empty + q);
+            if (lane == 0) { if (CL == 2 && crank != 0) eg_mbar_arrive_remote(mb_tq_empty + q, 0u); else mbar_arrive(mb_tq_empty + q); }
+            if (CL == 2 && t >= 0) t += (int)crank;
         }
         ++it;
         return t;
@@ -158,7 +184,7 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
     if (tid == 0) {
         for (int s = 0; s < EG_STAGES; ++s) { mbar_init(mb_full + s, 1); mbar_init(mb_empty + s, CL); }
         mbar_init(mb_tfull, 1); mbar_init(mb_tfull + 1, 1); mbar_init(mb_tempty, EG_EPI_WARPS); mbar_init(mb_tempty + 1, EG_EPI_WARPS);
-        for (int q = 0; q < 4; ++q) { mbar_init(mb_tq_full + q, 1); mbar_init(mb_tq_empty + q, EG_EPI_WARPS + 1); }
+        for (int q = 0; q < 4; ++q) { mbar_init(mb_tq_full + q, 1); mbar_init(mb_tq_empty + q, CL == 2 ? 2 * (EG_EPI_WARPS + 1) + 1 : EG_EPI_WARPS + 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     tc_fence_before();
@@ -182,14 +208,18 @@ ef_gemm_kernel(const EfPair* __restrict__ pairs, const EgTile* __restrict__ tile
             for (uint32_t it = 0;;) {
                 int t;
                 if (!dynamic) { t = t_first + (int)it * t_step; if (t >= n_tiles) t = -1; }
-                else {
+                else if (CL == 2 && crank != 0) {
+                    t = next_tile(it);          // advances it
+                    --it;
+                } else {
                     t = 0;
                     if (lane == 0) {
                         const uint32_t q = it & 3u;
                         if (it >= 4) mbar_wait(mb_tq_empty + q, ((it >> 2) - 1) & 1u);
-                        t = atomicAdd(tile_counter, 1);
+                        t = atomicAdd(tile_counter, 1) * CL;
                         if (t >= n_tiles) t = -1;
                         s_tile[q] = t;
+                        if (CL == 2) { eg_st_remote(s_tile + q, 1u, t); eg_mbar_arrive_remote(mb_tq_full + q, 1u); }
                         mbar_arrive(mb_tq_full + q);
                     }
                     t = __shfl_sync(0xffffffffu, t, 0);
