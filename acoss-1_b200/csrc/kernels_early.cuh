@@ -226,20 +226,22 @@ __device__ __forceinline__ void ef_warp_select2(const uint32_t (&keys)[R], int N
     for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
     const int excl = incl - tot;
     int bt[2] = {0, 0}, below[2] = {0, 0};
+    int cum[8];                                   // inclusive prefix of this lane's eight bins, from the start of the row
+    {
+        int run = excl;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { run += c[j]; cum[j] = run; }
+    }
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
         const int k = w == 0 ? kA : kB;
         const bool mine = k >= excl && k < incl;
-        int b_ = 0, bl = 0, run = excl;
-        bool found = false;
+        int nb_ = 0, bl = excl;                   // bins of this lane that end at or before rank k, and how many keys they hold
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            if (mine && !found && k < run + c[j]) { b_ = 8 * lane + j; bl = run; found = true; }
-            run += c[j];
-        }
+        for (int j = 0; j < 7; ++j) if (k >= cum[j]) { ++nb_; bl = cum[j]; }
         const unsigned m = __ballot_sync(0xffffffffu, mine);
         const int src = m ? __ffs(m) - 1 : 0;
-        bt[w] = __shfl_sync(0xffffffffu, b_, src);
+        bt[w] = __shfl_sync(0xffffffffu, 8 * lane + nb_, src);
         below[w] = __shfl_sync(0xffffffffu, bl, src);
     }
     EF_Q(q,
@@ -285,17 +287,14 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
     __shared__ __align__(16) int s_hist[8 * 256];
     __shared__ uint32_t s_cand[8 * 64];
     __shared__ int s_ccnt[8 * 2];
-    const int lane = threadIdx.x & 31;
-    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t task = wid; task < n_rows_total * n_mats; task += nw) {
-        const int mat = first_mat + (int)(task / n_rows_total);
-        const int64_t rr = task - (int64_t)(mat - first_mat) * n_rows_total;
-        // binary search the pair owning global row rr (row_task_off = prefix sums of M)
-        int lo = 0, hi = n_pairs - 1;
-        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (row_task_off[mid] <= rr) lo = mid; else hi = mid - 1; }
-        const EfPair pd = pairs[lo];
-        const int i = (int)(rr - row_task_off[lo]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    (void)row_task_off; (void)n_rows_total;
+    // block = (pair, matrix) [x] x row slice [y]: no search for the pair that owns a row (a 12-step binary search through global
+    // memory per row was 7 % of the kernel's instructions and a chain of dependent loads)
+    for (int64_t bp = blockIdx.x; bp < (int64_t)n_pairs * n_mats; bp += gridDim.x) {
+      const int mat = first_mat + (int)(bp % n_mats);
+      const EfPair pd = pairs[bp / n_mats];
+      for (int i = blockIdx.y * 8 + warp; i < pd.M; i += 8 * gridDim.y) {
         const int N = pd.N;
         const float* row = csm + pd.csm_off + ((int64_t)mat * pd.M + i) * N;
         uint32_t keys[R];
@@ -356,6 +355,7 @@ ef_row_kernel(const EfPair* __restrict__ pairs, const int64_t* __restrict__ row_
             s += (float)(Ke - less) * ef_key_inv(kk);
             if (lane == 0) rowmean[pd.row_off + (int64_t)mat * pd.M + i] = s / (float)Ke;
         }
+      }
     }
 }
 
