@@ -116,6 +116,9 @@ int acoss_ctx_set_stream(acoss_ctx *ctx, void *stream);
  *   "split_overlap"          1: selection kernels on a second stream beside the next chunk's streaming kernels (default 0: no gain measured)
  *   "count_hh"               1: the phase-split count pass multiplies the TF32 hi parts only (a third of the tensor work, a wider
  *                            candidate band in the selection); results are bit-identical either way
+ *   "ef_dynamic_tiles"       1 (default): the EarlyFusion CSM GEMM hands its tiles out in list order from a global counter
+ *   "ef_cluster"             1: the EarlyFusion CSM GEMM runs as clusters of two CTAs that share the reference-side operand stages
+ *                            by TMA multicast (bit-identical, measured slower: default 0)
  *   "ef_simt_csm"            1: acoss_earlyfusion_upload skips the tensor-core operand planes (the CSMs then run on the
  *                            fp32 SIMT tile kernel); set before the upload
  *   "inject_alloc_failures"  test hook: the next `value` device allocations of the pair pipeline's batch buffers
