@@ -352,7 +352,7 @@ crp_pivot_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict
         const float hscale = (smax > smin) ? 256.0f / (smax - smin) : 0.0f;
         const float hwidth = (smax - smin) * (1.0f / 256.0f);
         const float hoff = -smin * hscale;
-        unsigned char* hb = reinterpret_cast<unsigned char*>(hall + warp * 2048) + 4 * lane;     // bin b: byte b % 4 of word b / 4
+        unsigned* hw = hall + warp * 2048 + lane;                                                // bin b: byte b % 4 of word b / 4
 #pragma unroll
         for (int b = 0; b < GM_SHALVES; ++b)
 #pragma unroll
@@ -362,7 +362,9 @@ crp_pivot_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict
 #pragma unroll
                 for (int q = 0; q < 32; ++q) {
                     const int bin = min(255, (int)fmaf(v[q], hscale, hoff));
-                    hb[(bin >> 2) * 128 + (bin & 3)] += 1;
+                    // the histogram is private to the thread (bank = lane): the reduction instruction is used for its fire-and-forget
+                    // issue, not for atomicity -- a byte read-modify-write put a load-add-store chain on every one of the 128 samples
+                    atomicAdd(hw + (bin >> 2) * 32, 1u << (8 * (bin & 3)));
                 }
             }
         tc_fence_before();
