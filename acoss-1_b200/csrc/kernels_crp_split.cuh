@@ -34,6 +34,10 @@
 #define SP_EDGE_SLOTS 6                      // column-edge ring (see crp_stream_kernel: >= 5 slots make the reuse safe)
 #define SP_AMB_CAP 8192                      // ambiguous cells per strip before the exact-everything path
 #define SP_LIST_STRIDE (4 * GM_SUBCAP)       // float2 entries per row
+#define SP_LIDX(e) ((((uint32_t)(e) >> 2) << 11) | ((uint32_t)(e) & 3u))     // entry e of a sub-list, relative to the sub-list's first sector
+#define SP_LMID ((4u * GM_ROWS - 1u) << 2)       // the sub-list field of a list index (bits 2..10)
+static_assert(GM_ROWS == 128 && GM_SUBCAP == 128, "SP_LIDX: 2 + 9 + 5 index bits");
+#define SP_NO_ENTRY __int_as_float(0x7fc00000)   // filler of a batched list walk past the end of a sub-list: a NaN is neither below nor inside any window
 // crp_stream_kernel<2>: count pass on the hi.hi product alone (14 MMAs per tile instead of 41), see SP_EPS_REL_HH; context option "count_hh"
 // Error bound of the hi.hi-only radicand against the oracle's, relative to xx + yy: TF32 rounding of both operands (unit roundoff
 // 2^-11 each) gives |x_h.y_h - x.y| <= (2^-10 + 2^-22) sum |x_k y_k| <= 2^-11 (xx + yy); the radicand carries -2 x.y: 2^-10 (xx + yy);
@@ -621,7 +625,15 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 const float2 pv = rowvalid ? piv[srow] : make_float2(0.f, 0.f);
                 const float pa = pv.x;
                 const uint32_t wbits = __float_as_uint(pv.y - pv.x);
-                float2* ml = lists + (srow * 4 + cg) * GM_SUBCAP;
+                // sector-grouped lists: entry e of sub-list (row, cg) at SP_LIDX(e) of the strip's region, i.e. the four entries
+                // e & ~3 .. | 3 of a sub-list fill one 32-byte sector and the sectors of the 512 sub-lists of a group lie side by
+                // side (the selection kernel's lanes -- one sub-list each -- read 1 KB contiguous per step).  Entry-major order
+                // (one 8-byte entry per sub-list side by side) made the four warps of a row complete each sector at different
+                // times: ncu showed a DRAM read per sector (1.4 GB per launch, the list volume) and the kernel ran 30 % longer.
+                // The write cursor keeps the sub-list field of the index at all ones, so that + 1 carries from the entry's low two
+                // bits straight into the group number; the sub-list's own field is folded into the base pointer.
+                float2* mb = lists + (size_t)task * (GM_SUBCAP * 4 * GM_ROWS) + (myrow * 4 + cg) * 4;
+                float2* mc = mb - SP_LMID;
                 int ca = 0, ln = 0;
                 for (int t = 0; t < n_tiles; ++t, ++g) {
                     const uint32_t buf = g & 1;
@@ -637,15 +649,15 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                             const int jbase = t * GM_TN + 64 * q4 + 16 * cg;
                             if (ln + 16 <= GM_SUBCAP) {
                                 // room for the whole batch: the write pointer just advances (no clamp in the dependency chain)
-                                float2* wp = ml + ln;
+                                uint32_t c = SP_LIDX(ln) | SP_LMID;
 #pragma unroll
                                 for (int q = 0; q < 16; ++q) {
                                     const float vq = __uint_as_float(rr[q4 & 1][q]);
                                     const uint32_t u = __float_as_uint(vq - pa);
                                     ca += u >> 31;
-                                    if (u < wbits) { *wp = make_float2(vq, __int_as_float(jbase + q)); ++wp; }
+                                    if (u < wbits) { mc[c] = make_float2(vq, __int_as_float(jbase + q)); c = (c + 1) | SP_LMID; }
                                 }
-                                ln = (int)(wp - ml);
+                                ln = (int)((c & 3u) | ((c >> 11) << 2));
                             } else {
 #pragma unroll
                                 for (int q = 0; q < 16; ++q) {
@@ -653,7 +665,7 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                                     const uint32_t u = __float_as_uint(vq - pa);
                                     ca += u >> 31;
                                     if (u < wbits) {
-                                        ml[min(ln, GM_SUBCAP - 1)] = make_float2(vq, __int_as_float(jbase + q));     // overflow is detected from ln
+                                        mb[SP_LIDX(min(ln, GM_SUBCAP - 1))] = make_float2(vq, __int_as_float(jbase + q));     // overflow is detected from ln
                                         ++ln;
                                     }
                                 }
@@ -811,11 +823,9 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 //   (C) warp per row: exact order statistics among the candidates -> percentile -> threshold
 //   rows that could not be bracketed (bracket miss, list overflow, tiny side B): the whole row exactly
 // =====================================================================================================================
-#define SP_POOL 3072                         // candidate entries per strip (flat: a row takes what it needs, at most SP_CAND_MAX)
-#define SP_CAND_MAX 96
-#define SP_SEL_SMEM (GM_ARAW_BYTES + 6 * GM_ROWS * 4 + 8 + 2 * SP_POOL * 4 + SP_SEL_WARPS * 64 * 4)
+#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 16 + 2 * GM_ROWS * 32 * 4 + 16 * SP_SEL_THREADS * 4)
 
-__global__ void __launch_bounds__(SP_SEL_THREADS, 4)
+__global__ void __launch_bounds__(SP_SEL_THREADS, 3)
 crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
                   const float* __restrict__ frames, const float* __restrict__ selfdot, const float* __restrict__ sdmax,
                   float* __restrict__ thr, int side_a_is_query, float qf,
@@ -830,11 +840,9 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     int* s_kx = s_nc + GM_ROWS;
     int* s_flag = s_kx + GM_ROWS;
     int* s_off = s_flag + GM_ROWS;                                          // [GM_ROWS + 1]
-    int* s_used = s_off + GM_ROWS;                                          // pool entries handed out
-    int* pool_col = s_off + GM_ROWS + 2;                                    // [SP_POOL] (row << 24) | column
-    float* pool_dex = reinterpret_cast<float*>(pool_col + SP_POOL);         // [SP_POOL] approximate radicand, then the exact distance
-    int* s_hist = reinterpret_cast<int*>(pool_dex + SP_POOL);               // [SP_SEL_WARPS][64]
-    int* s_pk = s_hist + SP_SEL_WARPS * 64;                                 // [GM_ROWS] sub-list boundaries of the row's compacted list
+    int* pool_col = s_off + GM_ROWS + 4;                                    // [GM_ROWS][32] candidate columns
+    float* pool_dex = reinterpret_cast<float*>(pool_col + GM_ROWS * 32);    // [GM_ROWS][32] approximate radicand, then the exact distance
+    unsigned* s_hq = reinterpret_cast<unsigned*>(pool_dex + GM_ROWS * 32);  // [16 words][SP_SEL_THREADS] private 64-bin byte histograms
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_exact = 0;
     float max_err = 0.0f;
@@ -857,172 +865,211 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         }
         if (tid < GM_ROWS) {
             s_xx[tid] = (tid < tk.nrows) ? g.sdA[tk.row0 + tid] : 0.0f;
-            s_nc[tid] = 0; s_kx[tid] = 0; s_off[tid] = 0;
-            if (tid == 0) *s_used = 0;
+            s_nc[tid] = 0; s_kx[tid] = 0;
             s_flag[tid] = (tid < tk.nrows && tiny) ? 1 : 0;
         }
         __syncthreads();
-        // ---- (A)
-        if (!tiny)
-            for (int r = warp; r < tk.nrows; r += SP_SEL_WARPS) {
-                const size_t srow = (size_t)task * GM_ROWS + r;
-                const int4 c4r = *reinterpret_cast<const int4*>(lcnt + srow * 4);
-                const int4 a4r = *reinterpret_cast<const int4*>(cnt4 + srow * 4);
-                const int cseg[4] = {c4r.x, c4r.y, c4r.z, c4r.w};
-                const int c_ar = a4r.x + a4r.y + a4r.z + a4r.w, c_abr = c4r.x + c4r.y + c4r.z + c4r.w;
+        // ---- (A) a QUAD of lanes per row -- one lane per sub-list -- eight rows per warp.  With a warp per row every pass paid ~30
+        //      warp-wide instructions for 5 list entries per lane plus scans, ballots and reductions per row (ncu: 770 warp
+        //      instructions per row in this part, 39 % of the CRP stage).  Here a lane walks its own sub-list (~42 entries; the lists
+        //      are sector-grouped, so the 32 lanes of a warp read 1 KB contiguous per pair of loads), bins it into a private 64-bin byte
+        //      histogram (shared memory, bank = thread), the quad adds its four histograms, finds the bin(s) of the wanted ranks,
+        //      and a second walk counts what lies below the candidate window and appends the candidates to the row's pool.
+        if (!tiny) {
+            const int sub = lane & 3, rw = lane >> 2, qb = lane & ~3;
+            unsigned* hq = s_hq + tid;                                      // word w of this thread's histogram: hq[w * SP_SEL_THREADS]
+            for (int r0 = 8 * warp; r0 < tk.nrows; r0 += 8 * SP_SEL_WARPS) {
+                const int r = r0 + rw;
+                const bool live = r < tk.nrows;
+                const size_t srow = (size_t)task * GM_ROWS + (live ? r : r0);
+                const int n_s = live ? lcnt[srow * 4 + sub] : 0, a_s = live ? cnt4[srow * 4 + sub] : 0;
+                int c_ar = a_s, c_abr = n_s, n_mx = n_s;
+                c_ar += __shfl_xor_sync(0xffffffffu, c_ar, 1); c_ar += __shfl_xor_sync(0xffffffffu, c_ar, 2);
+                c_abr += __shfl_xor_sync(0xffffffffu, c_abr, 1); c_abr += __shfl_xor_sync(0xffffffffu, c_abr, 2);
+                n_mx = max(n_mx, __shfl_xor_sync(0xffffffffu, n_mx, 1)); n_mx = max(n_mx, __shfl_xor_sync(0xffffffffu, n_mx, 2));
                 const float2 pv = piv[srow];
                 const float par = pv.x, pbr = pv.y;
-                const bool ovf = max(max(c4r.x, c4r.y), max(c4r.z, c4r.w)) > GM_SUBCAP;
-                bool okr = (c_ar <= pr.lo) && (c_ar + c_abr >= pr.hi + 1) && !ovf;
-                if (!okr) {
-                    if (lane == 0) { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); if (ovf) atomicAdd(&counters[15], 1ull); else atomicAdd(&counters[13], 1ull); }
-                    continue;
+                const bool ovf = n_mx > GM_SUBCAP;
+                bool okr = live && (c_ar <= pr.lo) && (c_ar + c_abr >= pr.hi + 1) && !ovf;
+                if (live && !okr && sub == 0) {
+                    s_flag[r] = 1; atomicAdd(&counters[1], 1ull);
+                    if (ovf) atomicAdd(&counters[15], 1ull); else atomicAdd(&counters[13], 1ull);
                 }
-                // The row's list (four sub-lists, <= 512 entries of [pa, pb) in all, ~200 typically) is read COMPACTED: entry
-                // e = 32 i + lane for i < ceil(T / 32), so every later pass costs per entry in use, not per slot of the 16 x 32
-                // layout (ncu, source view: the slot-wise passes cost 1600 warp instructions per row, nine tenths on empty slots).
-                // One 64-bin histogram over the bracket (shared-memory atomics) + a prefix scan find the bin(s) holding the wanted
-                // ranks; the window shrinks to the extremes of those bins (again if it still holds more than 8 entries); everything
-                // within 2E of the window is a candidate for the exact chains.
-                const float2* lst = lists + srow * SP_LIST_STRIDE;
-                int* h = s_hist + warp * 64;
-                const int T = c_abr, p1 = c4r.x, p2 = p1 + c4r.y, p3 = p2 + c4r.z;
-                if (lane == 0) s_pk[r] = p1 | (p2 << 10) | (p3 << 20);
-                const int nI = (T + 31) >> 5;                                       // warp-uniform, <= SP_SEL_LPL
-                // every pass below walks the entries in blocks of four behind ONE warp-uniform branch per block (a per-entry guard is
-                // if-converted by the compiler and the empty entries then cost as much as the live ones); entries past T hold +inf
-#define SP_ENTRIES(i, ...)                                                                      \
-                _Pragma("unroll") for (int ib_ = 0; ib_ < SP_SEL_LPL; ib_ += 4)                 \
-                    if (ib_ < nI) { _Pragma("unroll") for (int i = ib_; i < ib_ + 4; ++i) { __VA_ARGS__ } }
-                float lx[SP_SEL_LPL];
-#pragma unroll
-                for (int i = 0; i < SP_SEL_LPL; ++i) lx[i] = INFINITY;
-                SP_ENTRIES(i,
-                    const int e = 32 * i + lane;
-                    if (e < T) {
-                        const int seg = (e >= p1) + (e >= p2) + (e >= p3);
-                        const int sl = e - (seg == 0 ? 0 : seg == 1 ? p1 : seg == 2 ? p2 : p3);
-                        const float2 v = lst[seg * GM_SUBCAP + sl];
-                        lx[i] = v.x;
-                    })
+                if (!__any_sync(0xffffffffu, okr)) continue;
+                // entry e of this lane's sub-list: lists[(task * GM_SUBCAP + e) * (4 GM_ROWS) + 4 row + sub]
+                const float2* ml = lists + (size_t)task * GM_SUBCAP * (4 * GM_ROWS) + ((live ? r : r0) * 4 + sub) * 4;
+                const int n_e = okr ? n_s : 0;
+                const int n_w = __reduce_max_sync(0xffffffffu, n_e);          // walk length of the warp
                 float base = par, top = pbr;
-                if (par == plow || pbr == GM_PMAX) {                // open-ended bracket: the list's own value range
+                const bool open_ended = okr && (par == plow || pbr == GM_PMAX);
+                if (__any_sync(0xffffffffu, open_ended)) {                    // open-ended bracket: the list's own value range
                     float vmn = INFINITY, vmx = -INFINITY;
-                    SP_ENTRIES(i, if (lx[i] != INFINITY) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); })
-                    for (int o = 16; o > 0; o >>= 1) {
-                        vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
-                        vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
-                    }
-                    base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
+#pragma unroll 8
+                    for (int e = 0; e < n_w; ++e)
+                        if (e < n_e) { const float v = ml[SP_LIDX(e)].x; vmn = fminf(vmn, v); vmx = fmaxf(vmx, v); }
+                    vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, 1)); vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, 2));
+                    vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, 1)); vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, 2));
+                    if (open_ended) { base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f; }
                 }
-                int klo = pr.lo - c_ar, khi = klo + (pr.hi - pr.lo);                // ranks wanted among the entries in the window
-                float w_lo = base, w_hi = top;
-                uint32_t binw[SP_SEL_LPL / 4];                                      // bin of entry i: byte i % 4 of word i / 4; 0xFF = outside
-#pragma unroll
-                for (int q = 0; q < SP_SEL_LPL / 4; ++q) binw[q] = 0xFFFFFFFFu;
-                okr = true;
+                // walk 1 (up to three rounds): histogram of the entries inside the current value interval [lo_v, hi_v] over [base, top);
+                // the bin(s) of the wanted ranks become the next interval while they still hold more than 12 entries (runs of
+                // near-equal distances).  Membership is by VALUE and the entries below the interval are re-counted in every walk,
+                // so the rounds need no per-entry state.
+                float lo_v = -INFINITY, hi_v = INFINITY;
+                bool refining = okr;
                 for (int round = 0; round < 3; ++round) {
+                    if (!__any_sync(0xffffffffu, refining)) break;
                     const float bw = (top - base) * (1.0f / 64.0f);
                     const float bsc = (bw > 0.0f) ? 1.0f / bw : 0.0f;
-                    h[lane] = 0; h[lane + 32] = 0;
-                    __syncwarp();
-                    SP_ENTRIES(i,
-                        const uint32_t ob = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
-                        const bool in = round == 0 ? (lx[i] != INFINITY) : (ob != 0xFFu);
-                        uint32_t b = 0xFFu;
-                        if (in) {
-                            b = (uint32_t)min(63, max(0, (int)((lx[i] - base) * bsc)));
-                            atomicAdd(&h[b], 1);
+#pragma unroll
+                    for (int w = 0; w < 16; ++w) hq[w * SP_SEL_THREADS] = 0u;
+                    int below = 0;
+                    // eight entries in flight per lane (one load per step left every step waiting for the L2 round trip)
+                    for (int e0 = 0; e0 < n_w; e0 += 8) {
+                        float v8[8];
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) {                                   // two sectors of the sub-list, two entries per load
+                            const bool in = (e0 + 2 * h < n_e) && refining;
+                            const float4 t4 = in ? *reinterpret_cast<const float4*>(ml + SP_LIDX(e0 + 2 * h)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            v8[2 * h] = in ? t4.x : SP_NO_ENTRY;
+                            v8[2 * h + 1] = (in && e0 + 2 * h + 1 < n_e) ? t4.z : SP_NO_ENTRY;
                         }
-                        binw[i >> 2] = (binw[i >> 2] & ~(0xFFu << (8 * (i & 3)))) | (b << (8 * (i & 3)));)
-                    __syncwarp();
-                    const int h0 = h[2 * lane], h1 = h[2 * lane + 1];
-                    __syncwarp();
-                    int incl = h0 + h1;
 #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
-                    const int excl = incl - h0 - h1;
-                    const int my_lo = (klo >= excl && klo < incl) ? (klo < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
-                    const int my_hi = (khi >= excl && khi < incl) ? (khi < excl + h0 ? 2 * lane : 2 * lane + 1) : -1;
-                    const unsigned m_lo = __ballot_sync(0xffffffffu, my_lo >= 0), m_hi = __ballot_sync(0xffffffffu, my_hi >= 0);
-                    if (m_lo == 0 || m_hi == 0) { okr = false; break; }
-                    const int l_lo = __ffs(m_lo) - 1, l_hi = __ffs(m_hi) - 1;
-                    const uint32_t b_lo = (uint32_t)__shfl_sync(0xffffffffu, my_lo, l_lo), b_hi = (uint32_t)__shfl_sync(0xffffffffu, my_hi, l_hi);
-                    const int below_pair = __shfl_sync(0xffffffffu, excl, l_lo), h0_lo = __shfl_sync(0xffffffffu, h0, l_lo);
-                    const int n_below_bin = below_pair + ((b_lo & 1) ? h0_lo : 0);
-                    const int incl_hi = __shfl_sync(0xffffffffu, incl, l_hi), h1_hi = __shfl_sync(0xffffffffu, h1, l_hi);
-                    const int n_upto_bin = incl_hi - ((b_hi & 1) ? 0 : h1_hi);
-                    klo -= n_below_bin; khi -= n_below_bin;
-                    float vmn = INFINITY, vmx = -INFINITY;
-                    SP_ENTRIES(i,
-                        const uint32_t b = (binw[i >> 2] >> (8 * (i & 3))) & 0xFFu;
-                        if (b - b_lo <= b_hi - b_lo) { vmn = fminf(vmn, lx[i]); vmx = fmaxf(vmx, lx[i]); }     // 0xFF is never inside
-                        else binw[i >> 2] |= 0xFFu << (8 * (i & 3));)
-                    for (int o = 16; o > 0; o >>= 1) {
-                        vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, o));
-                        vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, o));
+                        for (int u = 0; u < 8; ++u) {
+                            const float v = v8[u];
+                            if (v < lo_v) ++below;
+                            else if (v <= hi_v) {                                   // a NaN (no entry) fails both compares
+                                const int b = min(63, max(0, (int)((v - base) * bsc)));
+                                atomicAdd(hq + (b >> 2) * SP_SEL_THREADS, 1u << (8 * (b & 3)));      // private counter: the reduction is fire-and-forget
+                            }
+                        }
                     }
-                    w_lo = vmn; w_hi = vmx;
-                    if (n_upto_bin - n_below_bin <= 8 || !(vmx > vmn)) break;
-                    base = vmn; top = vmx + fabsf(vmx) * 1.0e-6f + 1.0e-30f;
-                }
-                int n_c = 0, kx = 0;
-                if (okr) {
-                    const float c_min = w_lo - 2.0f * E, c_max = w_hi + 2.0f * E;
-                    // the candidate window must lie strictly inside the list's value range [pa, pb)
-                    okr = (c_min > par || par == plow) && (c_max < pbr || pbr == GM_PMAX);
-                    int my_c = 0;
-                    if (okr) {
-                        int my_below = 0;
-                        SP_ENTRIES(i,                                   // empty entries hold +inf: neither below nor candidates
-                            my_below += lx[i] < c_min;
-                            my_c += (lx[i] >= c_min) && (lx[i] <= c_max);)
-                        const int n_below = c_ar + __reduce_add_sync(0xffffffffu, my_below);
-                        n_c = __reduce_add_sync(0xffffffffu, my_c);
-                        kx = pr.lo - n_below;
-                        if (n_c > SP_CAND_MAX || kx < 0 || kx + (pr.hi - pr.lo) >= n_c) okr = false;
-                    }
-                    if (okr) {
-                        int incl = my_c;
+                    __syncwarp();
+                    below += __shfl_xor_sync(0xffffffffu, below, 1); below += __shfl_xor_sync(0xffffffffu, below, 2);
+                    // the quad's histogram: lane `sub` adds bins 16 sub .. 16 sub + 15 of the four lanes (16-bit pairs: bins 0 | 2 and 1 | 3 of a word)
+                    unsigned lo2[4], hi2[4];
+                    int tot = 0;
 #pragma unroll
-                        for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
-                        int off = 0;
-                        if (lane == 0) off = atomicAdd(s_used, n_c);
-                        off = __shfl_sync(0xffffffffu, off, 0);
-                        if (off + n_c > SP_POOL) {                  // pool exhausted: the row goes the exact way; its slots stay marked empty
-                            okr = false;
-                            for (int sl = off + lane; sl < min(off + n_c, SP_POOL); sl += 32) pool_col[sl] = -1;
-                        } else {
-                            int at = off + incl - my_c;
-                            SP_ENTRIES(i,
-                                if ((lx[i] >= c_min) && (lx[i] <= c_max)) { pool_col[at] = (r << 24) | (32 * i + lane); pool_dex[at] = lx[i]; ++at; })
-                            if (lane == 0) s_off[r] = off;
+                    for (int w = 0; w < 4; ++w) {
+                        unsigned l = 0, h = 0;
+#pragma unroll
+                        for (int o = 0; o < 4; ++o) {
+                            const unsigned x = s_hq[(4 * sub + w) * SP_SEL_THREADS + (tid & ~3) + o];
+                            l += x & 0x00ff00ffu; h += (x >> 8) & 0x00ff00ffu;
+                        }
+                        lo2[w] = l; hi2[w] = h;
+                        tot += (int)((l & 0xffffu) + (l >> 16) + (h & 0xffffu) + (h >> 16));
+                    }
+                    __syncwarp();
+                    int excl = 0;
+#pragma unroll
+                    for (int o = 0; o < 3; ++o) { const int t_ = __shfl_sync(0xffffffffu, tot, qb + o); if (o < sub) excl += t_; }
+                    const int klo = pr.lo - c_ar - below, khi = klo + (pr.hi - pr.lo);      // ranks wanted among the entries of the interval
+                    int b_lo = -1, b_hi = -1, n_lo = 0, n_hi = 0;                            // bins of the ranks, entries before b_lo / through b_hi
+                    {
+                        int run = excl;
+#pragma unroll
+                        for (int w = 0; w < 4; ++w)
+#pragma unroll
+                            for (int f = 0; f < 4; ++f) {
+                                const int cnt = (int)(f == 0 ? (lo2[w] & 0xffffu) : f == 1 ? (hi2[w] & 0xffffu) : f == 2 ? (lo2[w] >> 16) : (hi2[w] >> 16));
+                                if (klo >= run && klo < run + cnt) { b_lo = 16 * sub + 4 * w + f; n_lo = run; }
+                                if (khi >= run && khi < run + cnt) { b_hi = 16 * sub + 4 * w + f; n_hi = run + cnt; }
+                                run += cnt;
+                            }
+                    }
+                    b_lo = max(b_lo, __shfl_xor_sync(0xffffffffu, b_lo, 1)); b_lo = max(b_lo, __shfl_xor_sync(0xffffffffu, b_lo, 2));
+                    b_hi = max(b_hi, __shfl_xor_sync(0xffffffffu, b_hi, 1)); b_hi = max(b_hi, __shfl_xor_sync(0xffffffffu, b_hi, 2));
+                    n_lo = max(n_lo, __shfl_xor_sync(0xffffffffu, n_lo, 1)); n_lo = max(n_lo, __shfl_xor_sync(0xffffffffu, n_lo, 2));
+                    n_hi = max(n_hi, __shfl_xor_sync(0xffffffffu, n_hi, 1)); n_hi = max(n_hi, __shfl_xor_sync(0xffffffffu, n_hi, 2));
+                    if (refining) {
+                        if (b_lo < 0 || b_hi < 0) { okr = false; refining = false; }
+                        else {
+                            // the next interval: the bins of the ranks, 2 % of a bin wider for the rounding of the binning map
+                            lo_v = fmaxf(lo_v, base + ((float)b_lo - 0.02f) * bw);
+                            hi_v = fminf(hi_v, base + ((float)b_hi + 1.02f) * bw);
+                            if (n_hi - n_lo <= 12 || !(hi_v > lo_v) || bw <= 0.0f) refining = false;
+                            else { base = lo_v; top = hi_v; }
                         }
                     }
                 }
-#undef SP_ENTRIES
-                if (lane == 0) {
-                    if (okr) { s_nc[r] = n_c; s_kx[r] = kx; }
-                    else { s_flag[r] = 1; atomicAdd(&counters[1], 1ull); atomicAdd(&counters[12], 1ull); }
+                float c_min = lo_v - 2.0f * E, c_max = hi_v + 2.0f * E;
+                {
+                    // a window that reaches over an end of the bracket by its BIN EDGE may still lie inside by its entries (the wanted
+                    // rank sits in the first or the last bin for ~3 % of the rows): those rows take the extremes of the entries
+                    const bool e_lo = okr && !(c_min > par || par == plow), e_hi = okr && !(c_max < pbr || pbr == GM_PMAX);
+                    if (__any_sync(0xffffffffu, e_lo || e_hi)) {
+                        float vmn = INFINITY, vmx = -INFINITY;
+                        for (int e = 0; e < n_w; ++e)
+                            if (e < n_e && (e_lo || e_hi)) {
+                                const float v = ml[SP_LIDX(e)].x;
+                                if (v >= lo_v && v <= hi_v) { vmn = fminf(vmn, v); vmx = fmaxf(vmx, v); }
+                            }
+                        vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, 1)); vmn = fminf(vmn, __shfl_xor_sync(0xffffffffu, vmn, 2));
+                        vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, 1)); vmx = fmaxf(vmx, __shfl_xor_sync(0xffffffffu, vmx, 2));
+                        if (e_lo) c_min = vmn - 2.0f * E;
+                        if (e_hi) c_max = vmx + 2.0f * E;
+                    }
+                }
+                okr = okr && (c_min > par || par == plow) && (c_max < pbr || pbr == GM_PMAX);
+                // walk 2: entries below the window, candidates appended to the row's pool
+                int my_below = 0, my_c = 0;
+                for (int e0 = 0; e0 < n_w; e0 += 8) {
+                    float2 e8[8];
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) {
+                        const bool in = (e0 + 2 * h < n_e) && okr;
+                        const float4 t4 = in ? *reinterpret_cast<const float4*>(ml + SP_LIDX(e0 + 2 * h)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        e8[2 * h] = make_float2(in ? t4.x : SP_NO_ENTRY, t4.y);
+                        e8[2 * h + 1] = make_float2((in && e0 + 2 * h + 1 < n_e) ? t4.z : SP_NO_ENTRY, t4.w);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const float2 ent = e8[u];
+                        if (ent.x < c_min) ++my_below;
+                        else if (ent.x <= c_max) {                                  // a NaN (no entry) fails both compares
+                            const int slot = atomicAdd(&s_nc[r], 1);
+                            if (slot < 32) { pool_col[r * 32 + slot] = __float_as_int(ent.y); pool_dex[r * 32 + slot] = ent.x; }
+                            ++my_c;
+                        }
+                    }
+                }
+                my_below += __shfl_xor_sync(0xffffffffu, my_below, 1); my_below += __shfl_xor_sync(0xffffffffu, my_below, 2);
+                my_c += __shfl_xor_sync(0xffffffffu, my_c, 1); my_c += __shfl_xor_sync(0xffffffffu, my_c, 2);
+                const int kx = pr.lo - (c_ar + my_below);
+                if (my_c > 32 || kx < 0 || kx + (pr.hi - pr.lo) >= my_c) okr = false;
+                __syncwarp();
+                if (live && sub == 0 && !s_flag[r]) {
+                    if (okr) { s_nc[r] = my_c; s_kx[r] = kx; }
+                    else { s_nc[r] = 0; s_flag[r] = 1; atomicAdd(&counters[1], 1ull); atomicAdd(&counters[12], 1ull); }
                 }
             }
+        }
         __syncthreads();
-        // ---- (B)
+        // offsets of the rows' candidates in the flat task list
+        if (warp == 0) {
+            int c[4], tot = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const int r = 4 * lane + q; c[q] = (r < tk.nrows) ? s_nc[r] : 0; tot += c[q]; }
+            int incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t_ = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t_; }
+            int run = incl - tot;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { s_off[4 * lane + q] = run; run += c[q]; }
+            if (lane == 31) s_off[GM_ROWS] = run;
+        }
+        __syncthreads();
+        // ---- (B) thread per candidate (all rows of the strip pooled): the exact 108-term chain in the oracle's op order
         {
             const int boff = side_a_is_query ? (ACOSS_NBINS - rot) % ACOSS_NBINS : 0;     // rot_src(c, rot) = (c + boff) % 12
-            const int n_tasks_c = min(*s_used, SP_POOL);             // entries of rows that did not fit are never written: their rows are flagged
+            const int n_tasks_c = s_off[GM_ROWS];
             for (int idx = tid; idx < n_tasks_c; idx += SP_SEL_THREADS) {
-                const int code = pool_col[idx];
-                if (code < 0) continue;
-                const int r = (code >> 24) & 0xFF, e = code & 0xFFFFFF;
-                int jj;
-                {   // entry e of the row's compacted list -> its column (second word of the list entry; the selection pass keeps
-                    // only the values in registers: 16 registers less per thread = four CTAs per SM instead of three)
-                    const int pk = s_pk[r], q1 = pk & 1023, q2 = (pk >> 10) & 1023, q3 = (pk >> 20) & 1023;
-                    const int seg = (e >= q1) + (e >= q2) + (e >= q3);
-                    const int sl = e - (seg == 0 ? 0 : seg == 1 ? q1 : seg == 2 ? q2 : q3);
-                    jj = __float_as_int(lists[((size_t)task * GM_ROWS + r) * SP_LIST_STRIDE + seg * GM_SUBCAP + sl].y);
-                }
+                int r = 0;                                            // last row with s_off[r] <= idx
+#pragma unroll
+                for (int st = 64; st > 0; st >>= 1) if (s_off[r + st] <= idx) r += st;
+                const int slot = idx - s_off[r];
+                const int jj = pool_col[r * 32 + slot];
                 const float4* bp = reinterpret_cast<const float4*>(g.fr_b + (int64_t)jj * ACOSS_NBINS);
                 const float4* as = reinterpret_cast<const float4*>(Araw + r * ACOSS_NBINS);
                 float acc = 0.0f;
@@ -1037,47 +1084,27 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 const float sa = s_xx[r], sb = __ldg(g.sdB + jj);
                 const float xx = side_a_is_query ? sa : sb, yy = side_a_is_query ? sb : sa;
                 float item = xadd(xsub(xx, xmul(2.0f, acc)), yy);
-                max_err = fmaxf(max_err, fabsf(item - pool_dex[idx]) / (sa + sb));
+                max_err = fmaxf(max_err, fabsf(item - pool_dex[r * 32 + slot]) / (sa + sb));
                 if (item < 0.0f) item = 0.0f;
-                pool_dex[idx] = __fsqrt_rn(item);
+                pool_dex[r * 32 + slot] = __fsqrt_rn(item);
                 ++n_exact;
             }
         }
         __syncthreads();
-        // ---- (C) warp per row: ranks kx and kx + 1 among the row's exact candidate distances (ties by slot); up to three
-        //      candidates per lane, the others read as shared-memory broadcasts
+        // ---- (C) warp per row: ranks kx and kx + 1 among the row's exact candidate distances (ties by slot)
         for (int r = warp; r < tk.nrows; r += SP_SEL_WARPS) {
             const int n_c = s_nc[r], kx = s_kx[r];
             if (n_c == 0) continue;
-            const float* dex = pool_dex + s_off[r];
-            float da[3];
-            int rank[3] = {0, 0, 0};
-#pragma unroll
-            for (int c = 0; c < 3; ++c) da[c] = (32 * c + lane < n_c) ? dex[32 * c + lane] : INFINITY;
-            if (n_c <= 32) {
-                for (int b_ = 0; b_ < n_c; ++b_) {
-                    const float db = dex[b_];
-                    rank[0] += (db < da[0]) || (db == da[0] && b_ < lane);
-                }
-            } else {
-                for (int b_ = 0; b_ < n_c; ++b_) {
-                    const float db = dex[b_];
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) rank[c] += (db < da[c]) || (db == da[c] && b_ < 32 * c + lane);
-                }
+            const float da = (lane < n_c) ? pool_dex[r * 32 + lane] : INFINITY;
+            int rank = 0;
+            for (int b_ = 0; b_ < n_c; ++b_) {
+                const float db = __shfl_sync(0xffffffffu, da, b_);
+                rank += (db < da) || (db == da && b_ < lane);
             }
-            float v_lo = 0.0f, v_hi = 0.0f;
-            bool have_hi = false;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                if (32 * c >= n_c) break;
-                const bool in = 32 * c + lane < n_c;
-                const unsigned m_lo = __ballot_sync(0xffffffffu, in && rank[c] == kx);
-                const unsigned m_hi = __ballot_sync(0xffffffffu, in && rank[c] == kx + 1);
-                if (m_lo) v_lo = __shfl_sync(0xffffffffu, da[c], __ffs(m_lo) - 1);
-                if (m_hi) { v_hi = __shfl_sync(0xffffffffu, da[c], __ffs(m_hi) - 1); have_hi = true; }
-            }
-            if (!have_hi) v_hi = v_lo;
+            const unsigned m_lo = __ballot_sync(0xffffffffu, lane < n_c && rank == kx);
+            const unsigned m_hi = __ballot_sync(0xffffffffu, lane < n_c && rank == kx + 1);
+            const float v_lo = __shfl_sync(0xffffffffu, da, __ffs(m_lo) - 1);
+            const float v_hi = m_hi ? __shfl_sync(0xffffffffu, da, __ffs(m_hi) - 1) : v_lo;
             if (lane == 0) thr_out[tk.row0 + r] = percentile_combine(pr, v_lo, v_hi);
         }
         // ---- rows that could not be bracketed (and tiny side B): the whole row exactly, one row at a time
