@@ -936,12 +936,13 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                         }
 #pragma unroll
                         for (int u = 0; u < 8; ++u) {
+                            // straight-line body (a branch per entry cost two reconvergence points in a divergent warp)
                             const float v = v8[u];
-                            if (v < lo_v) ++below;
-                            else if (v <= hi_v) {                                   // a NaN (no entry) fails both compares
-                                const int b = min(63, max(0, (int)((v - base) * bsc)));
-                                atomicAdd(hq + (b >> 2) * SP_SEL_THREADS, 1u << (8 * (b & 3)));      // private counter: the reduction is fire-and-forget
-                            }
+                            below += (v < lo_v);
+                            const unsigned b = min(63u, __float2uint_rz((v - base) * bsc));             // negative and NaN -> 0
+                            // private counter: the reduction is fire-and-forget.  Entries outside the interval (and the NaN of
+                            // "no entry", which fails the compares) add zero: the compiler keeps a conditional atomic behind a branch
+                            atomicAdd(hq + (b >> 2) * SP_SEL_THREADS, (v >= lo_v && v <= hi_v) ? 1u << ((8u * b) & 31u) : 0u);
                         }
                     }
                     __syncwarp();
