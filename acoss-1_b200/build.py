@@ -26,7 +26,8 @@ def build(force=False, verbose=False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     if not os.path.exists(nvcc):
         nvcc = "nvcc"
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "acoss_b200.cu")]
+    extra = os.environ.get("ACOSS_NVCC_EXTRA", "").split()          # e.g. -DSP_TIMING for the debug clocks of the streaming kernels
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "acoss_b200.cu")]
     subprocess.check_call(cmd, cwd=CSRC)
     return OUT
 

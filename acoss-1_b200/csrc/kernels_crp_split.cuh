@@ -37,6 +37,15 @@
 #define SP_LIDX(e) ((((uint32_t)(e) >> 2) << 11) | ((uint32_t)(e) & 3u))     // entry e of a sub-list, relative to the sub-list's first sector
 #define SP_LMID ((4u * GM_ROWS - 1u) << 2)       // the sub-list field of a list index (bits 2..10)
 static_assert(GM_ROWS == 128 && GM_SUBCAP == 128, "SP_LIDX: 2 + 9 + 5 index bits");
+#ifdef SP_TIMING        // debug build: where the MMA issuer of the streaming kernels waits (clocks summed over the CTAs into counters[2..5] / [8..11])
+#define SP_TDECL(x) long long x = 0
+#define SP_T0(x) const long long x = clock64()
+#define SP_T1(x, acc) acc += clock64() - x
+#else
+#define SP_TDECL(x)
+#define SP_T0(x)
+#define SP_T1(x, acc)
+#endif
 #define SP_NO_ENTRY __int_as_float(0x7fc00000)   // filler of a batched list walk past the end of a sub-list: a NaN is neither below nor inside any window
 // crp_stream_kernel<2>: count pass on the hi.hi product alone (14 MMAs per tile instead of 41), see SP_EPS_REL_HH; context option "count_hh"
 // Error bound of the hi.hi-only radicand against the oracle's, relative to xx + yy: TF32 rounding of both operands (unit roundoff
@@ -547,6 +556,8 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     } else if (warp == GM_WARPS) {
         // ================= MMA issuer =================
         uint32_t g = 0, i = 0;
+        SP_TDECL(tm_a); SP_TDECL(tm_b); SP_TDECL(tm_e);
+        SP_T0(tm_all);
         for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
             const StripTask tk = tasks[task];
             const PairDesc pd = descs[tk.pair];
@@ -554,11 +565,17 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
             const int NB = side_a_is_query ? pd.N : pd.M;
             const int n_tiles = (NB + GM_TN - 1) / GM_TN;
             const uint32_t ab = i & 1;
+            SP_T0(ta);
             mbar_wait(mb_afull + ab, (i >> 1) & 1u);
+            SP_T1(ta, tm_a);
             for (int t = 0; t < n_tiles; ++t, ++g) {
                 const uint32_t sb = g % SP_NB_RING, buf = g & 1;
+                SP_T0(tb);
                 mbar_wait(mb_bfull + sb, (g / SP_NB_RING) & 1u);
+                SP_T1(tb, tm_b);
+                SP_T0(te);
                 if (g >= 2) mbar_wait(mb_tempty + buf, ((g >> 1) - 1) & 1u);
+                SP_T1(te, tm_e);
                 tc_fence_after();
                 if (gm_elect_one()) {
                     if (MODE == 2) sp_issue_tile_hh(tmem_base + buf * GM_TN, a_saddr + ab * GM_A_BYTES, b_saddr + sb * GM_B_BYTES);
@@ -570,10 +587,18 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
             }
             ++i;
         }
+#ifdef SP_TIMING
+        if (lane == 0 && counters) {
+            const int o = (MODE == 1) ? 8 : 2;
+            atomicAdd(&counters[o], (unsigned long long)tm_a); atomicAdd(&counters[o + 1], (unsigned long long)tm_b);
+            atomicAdd(&counters[o + 2], (unsigned long long)tm_e); atomicAdd(&counters[o + 3], (unsigned long long)(clock64() - tm_all));
+        }
+#endif
     } else if (warp < GM_WARPS) {
         // ================= epilogue warps =================
         const uint32_t my_taddr = tmem_base + ((uint32_t)(32 * lq) << 16) + 16 * cg;
         uint32_t g = 0, i = 0;
+        SP_TDECL(tm_f);
         // next non-skipped task at or after `from`
         auto next_task = [&](int from) {
             while (from < n_tasks && skip(descs[tasks[from].pair])) from += gridDim.x;
@@ -632,50 +657,49 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 // times: ncu showed a DRAM read per sector (1.4 GB per launch, the list volume) and the kernel ran 30 % longer.
                 // The write cursor keeps the sub-list field of the index at all ones, so that + 1 carries from the entry's low two
                 // bits straight into the group number; the sub-list's own field is folded into the base pointer.
-                float2* mb = lists + (size_t)task * (GM_SUBCAP * 4 * GM_ROWS) + (myrow * 4 + cg) * 4;
-                float2* mc = mb - SP_LMID;
-                int ca = 0, ln = 0;
+                float2* mc = lists + (size_t)task * (GM_SUBCAP * 4 * GM_ROWS) + (myrow * 4 + cg) * 4 - SP_LMID;
+                int ca = 0;
+                uint32_t c = SP_LMID;                         // write cursor: entry 0
+                constexpr uint32_t C_FULL = (uint32_t)((GM_SUBCAP - 16) >> 2) << 11;      // fewer than 16 free slots from this group on
+                // one batch of 16 columns.  A sub-list with fewer than 16 free slots counts as overflowed from there on (its row is
+                // then taken exactly by the selection kernel), so the epilogue carries one store sequence without a clamp.
+                auto batch = [&](const uint32_t (&r)[16], int jbase) {
+                    if (rowvalid && c < C_FULL) {
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) {
+                            const float vq = __uint_as_float(r[q]);
+                            const uint32_t u = __float_as_uint(vq - pa);
+                            ca += u >> 31;
+                            if (u < wbits) { mc[c] = make_float2(vq, __int_as_float(jbase + q)); c = (c + 1) | SP_LMID; }
+                        }
+                    }
+                };
                 for (int t = 0; t < n_tiles; ++t, ++g) {
                     const uint32_t buf = g & 1;
+                    SP_T0(tf);
                     mbar_wait(mb_tfull + buf, (g >> 1) & 1u);
+                    SP_T1(tf, tm_f);
                     tc_fence_after();
-                    uint32_t rr[2][16];                       // two batches of 16 columns: one in flight while the other is processed
-                    tmem_ld16_issue(my_taddr + buf * GM_TN, rr[0]);
-#pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4) {
-                        tmem_ld_wait16(rr[q4 & 1]);
-                        if (q4 < 3) tmem_ld16_issue(my_taddr + buf * GM_TN + 64 * (q4 + 1), rr[(q4 + 1) & 1]);
-                        if (rowvalid) {
-                            const int jbase = t * GM_TN + 64 * q4 + 16 * cg;
-                            if (ln + 16 <= GM_SUBCAP) {
-                                // room for the whole batch: the write pointer just advances (no clamp in the dependency chain)
-                                uint32_t c = SP_LIDX(ln) | SP_LMID;
-#pragma unroll
-                                for (int q = 0; q < 16; ++q) {
-                                    const float vq = __uint_as_float(rr[q4 & 1][q]);
-                                    const uint32_t u = __float_as_uint(vq - pa);
-                                    ca += u >> 31;
-                                    if (u < wbits) { mc[c] = make_float2(vq, __int_as_float(jbase + q)); c = (c + 1) | SP_LMID; }
-                                }
-                                ln = (int)((c & 3u) | ((c >> 11) << 2));
-                            } else {
-#pragma unroll
-                                for (int q = 0; q < 16; ++q) {
-                                    const float vq = __uint_as_float(rr[q4 & 1][q]);
-                                    const uint32_t u = __float_as_uint(vq - pa);
-                                    ca += u >> 31;
-                                    if (u < wbits) {
-                                        mb[SP_LIDX(min(ln, GM_SUBCAP - 1))] = make_float2(vq, __int_as_float(jbase + q));     // overflow is detected from ln
-                                        ++ln;
-                                    }
-                                }
-                            }
-                        }
+                    uint32_t r0[16], r1[16];                  // two batches of 16 columns: one in flight while the other is processed
+                    const uint32_t ta = my_taddr + buf * GM_TN;
+                    const int jb = t * GM_TN + 16 * cg;
+                    tmem_ld16_issue(ta, r0);
+                    // two rounds of (even batch, odd batch): half the code of the four-way unrolled loop -- the three warp roles of
+                    // this kernel run different code and ncu showed 10 % of the stall samples waiting for instructions
+#pragma unroll 1
+                    for (int h = 0; h < 2; ++h) {
+                        tmem_ld_wait16(r0);
+                        tmem_ld16_issue(ta + 128 * h + 64, r1);
+                        batch(r0, jb + 128 * h);
+                        tmem_ld_wait16(r1);
+                        if (h == 0) tmem_ld16_issue(ta + 128, r0);
+                        batch(r1, jb + 128 * h + 64);
                     }
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(mb_tempty + buf);
                 }
+                const int ln = (c >= C_FULL) ? GM_SUBCAP + 1 : (int)((c & 3u) | ((c >> 11) << 2));
                 cnt4[srow * 4 + cg] = ca;
                 lcnt[srow * 4 + cg] = ln;
             } else {
@@ -690,7 +714,9 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 const uint32_t wamb = __float_as_uint(2.2f * E);
                 for (int t = 0; t < n_tiles; ++t, ++g) {
                     const uint32_t buf = g & 1;
+                    SP_T0(tf);
                     mbar_wait(mb_tfull + buf, (g >> 1) & 1u);
+                    SP_T1(tf, tm_f);
                     tc_fence_after();
                     const float* lcs = loC + (g % SP_EDGE_SLOTS) * GM_TN;
                     uint32_t rr[2][16];
@@ -788,6 +814,9 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         }
         for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o);
         if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
+#ifdef SP_TIMING
+        if (tid == 0 && counters) atomicAdd(&counters[MODE == 1 ? 7 : 6], (unsigned long long)tm_f);
+#endif
     }
     tc_fence_before();
     __syncthreads();
