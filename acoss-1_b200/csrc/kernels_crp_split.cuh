@@ -37,7 +37,8 @@
 #define SP_LIDX(e) ((((uint32_t)(e) >> 2) << 11) | ((uint32_t)(e) & 3u))     // entry e of a sub-list, relative to the sub-list's first sector
 #define SP_LMID ((4u * GM_ROWS - 1u) << 2)       // the sub-list field of a list index (bits 2..10)
 static_assert(GM_ROWS == 128 && GM_SUBCAP == 128, "SP_LIDX: 2 + 9 + 5 index bits");
-#ifdef SP_TIMING        // debug build: where the MMA issuer of the streaming kernels waits (clocks summed over the CTAs into counters[2..5] / [8..11])
+#ifdef SP_TIMING        // debug build (ACOSS_NVCC_EXTRA=-DSP_TIMING): clocks of the count pass summed over the CTAs -- MMA issuer: counters[2..5] =
+                        // wait a_full, b_full, tmem_empty, total; epilogue warp 0: [6] = wait tmem_full, [8] = tcgen05.wait::ld, [9] = batch bodies, [10] = total
 #define SP_TDECL(x) long long x = 0
 #define SP_T0(x) const long long x = clock64()
 #define SP_T1(x, acc) acc += clock64() - x
@@ -589,16 +590,18 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         }
 #ifdef SP_TIMING
         if (lane == 0 && counters) {
-            const int o = (MODE == 1) ? 8 : 2;
-            atomicAdd(&counters[o], (unsigned long long)tm_a); atomicAdd(&counters[o + 1], (unsigned long long)tm_b);
-            atomicAdd(&counters[o + 2], (unsigned long long)tm_e); atomicAdd(&counters[o + 3], (unsigned long long)(clock64() - tm_all));
+            if (MODE != 1) {
+                atomicAdd(&counters[2], (unsigned long long)tm_a); atomicAdd(&counters[3], (unsigned long long)tm_b);
+                atomicAdd(&counters[4], (unsigned long long)tm_e); atomicAdd(&counters[5], (unsigned long long)(clock64() - tm_all));
+            }
         }
 #endif
     } else if (warp < GM_WARPS) {
         // ================= epilogue warps =================
         const uint32_t my_taddr = tmem_base + ((uint32_t)(32 * lq) << 16) + 16 * cg;
         uint32_t g = 0, i = 0;
-        SP_TDECL(tm_f);
+        SP_TDECL(tm_f); SP_TDECL(tm_w); SP_TDECL(tm_p);
+        SP_T0(tm_epi_all);
         // next non-skipped task at or after `from`
         auto next_task = [&](int from) {
             while (from < n_tasks && skip(descs[tasks[from].pair])) from += gridDim.x;
@@ -688,12 +691,20 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     // this kernel run different code and ncu showed 10 % of the stall samples waiting for instructions
 #pragma unroll 1
                     for (int h = 0; h < 2; ++h) {
+                        SP_T0(tw0);
                         tmem_ld_wait16(r0);
+                        SP_T1(tw0, tm_w);
                         tmem_ld16_issue(ta + 128 * h + 64, r1);
+                        SP_T0(tp0);
                         batch(r0, jb + 128 * h);
+                        SP_T1(tp0, tm_p);
+                        SP_T0(tw1);
                         tmem_ld_wait16(r1);
+                        SP_T1(tw1, tm_w);
                         if (h == 0) tmem_ld16_issue(ta + 128, r0);
+                        SP_T0(tp1);
                         batch(r1, jb + 128 * h + 64);
+                        SP_T1(tp1, tm_p);
                     }
                     tc_fence_before();
                     __syncwarp();
@@ -815,7 +826,13 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o);
         if (lane == 0 && n_exact) atomicAdd(&counters[0], n_exact);
 #ifdef SP_TIMING
-        if (tid == 0 && counters) atomicAdd(&counters[MODE == 1 ? 7 : 6], (unsigned long long)tm_f);
+        if (tid == 0 && counters) {
+            atomicAdd(&counters[MODE == 1 ? 7 : 6], (unsigned long long)tm_f);
+            if (MODE != 1) {            // count pass, epilogue warp 0: clocks in tcgen05.wait::ld, in the batch bodies, in total
+                atomicAdd(&counters[8], (unsigned long long)tm_w); atomicAdd(&counters[9], (unsigned long long)tm_p);
+                atomicAdd(&counters[10], (unsigned long long)(clock64() - tm_epi_all));
+            }
+        }
 #endif
     }
     tc_fence_before();
