@@ -114,8 +114,10 @@ int acoss_ctx_set_stream(acoss_ctx *ctx, void *stream);
  *                            tracks have >= 1024 embedded rows; 0: auto never uses it
  *   "piv_nsigma_x10"         bracket half-width of the phase-split pivots in tenths of a binomial sigma (default 25)
  *   "split_overlap"          1: selection kernels on a second stream beside the next chunk's streaming kernels (default 0: no gain measured)
- *   "count_hh"               1: the phase-split count pass multiplies the TF32 hi parts only (a third of the tensor work, a wider
- *                            candidate band in the selection); results are bit-identical either way
+ *   "count_hh"               1: the phase-split count pass multiplies the TF32 hi parts only (half of the tensor work, a ten times
+ *                            wider candidate band in the selection); results are bit-identical either way.  An experiment, not a
+ *                            setting: the band overflows the selection's 32-candidate pool on most rows, which then take the exact
+ *                            whole-row path (about 20 x slower at 2000-frame tracks)
  *   "ef_dynamic_tiles"       1 (default): the EarlyFusion CSM GEMM hands its tiles out in list order from a global counter
  *   "ef_cluster"             1: the EarlyFusion CSM GEMM runs as clusters of two CTAs that share the reference-side operand stages
  *                            by TMA multicast (bit-identical, measured slower: default 0)
