@@ -47,6 +47,11 @@ static_assert(GM_ROWS == 128 && GM_SUBCAP == 128, "SP_LIDX: 2 + 9 + 5 index bits
 #define SP_T0(x)
 #define SP_T1(x, acc)
 #endif
+#ifdef SP_TIMING_BIN    // debug build: clocks of the binarise pass's epilogue warp 0 -- counters[2..5] = before the tiles, tiles, after the tiles, total; [6] = ambiguous cells
+#define SB_T(x) const long long x = clock64()
+#else
+#define SB_T(x)
+#endif
 #define SP_NO_ENTRY __int_as_float(0x7fc00000)   // filler of a batched list walk past the end of a sub-list: a NaN is neither below nor inside any window
 // crp_stream_kernel<2>: count pass on the hi.hi product alone (14 MMAs per tile instead of 41), see SP_EPS_REL_HH; context option "count_hh"
 // Error bound of the hi.hi-only radicand against the oracle's, relative to xx + yy: TF32 rounding of both operands (unit roundoff
@@ -488,6 +493,11 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
     float* s_th = s_xx + GM_ROWS;
     float* s_loq = s_th + GM_ROWS;
     int* amb_cnt = reinterpret_cast<int*>(s_loq + GM_ROWS);
+    // binarise pass: `lists` / `lcnt`, unused by this pass, carry the batch's list of ambiguous cells (task, row << 24 | column) and
+    // its fill count when the host found room for it (crp_fix_kernel then decides the cells); null: the strip decides its own
+    int2* amb_g = reinterpret_cast<int2*>(lists);
+    unsigned long long* amb_gcnt = reinterpret_cast<unsigned long long*>(lcnt);
+    const bool deferred = MODE == 1 && lists != nullptr;
     uint64_t* mbar = reinterpret_cast<uint64_t*>(gsm + L::MBAR_OFF);
     uint64_t* mb_tfull = mbar, *mb_tempty = mbar + 2, *mb_bfull = mbar + 4, *mb_bempty = mbar + 7, *mb_afull = mbar + 10;
     uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(mbar + 12);
@@ -626,10 +636,11 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
             const bool rowvalid = myrow < tk.nrows;
             const int nxt = next_task(task + gridDim.x);
             float E = 0.0f;
+            SB_T(sb0);
             if (MODE == 1) {
                 E = sp_pair_bound(pd, sdmax).E;
                 gm_csync();                          // the previous strip's exact chains are done with Araw / amb / s_*
-                for (int e = tid; e < (GM_ROWS + 8) * ACOSS_NBINS; e += GM_THREADS) {
+                if (!deferred) for (int e = tid; e < (GM_ROWS + 8) * ACOSS_NBINS; e += GM_THREADS) {
                     const int fe = e / ACOSS_NBINS, c = e - fe * ACOSS_NBINS;
                     const int f = tk.row0 + fe;
                     Araw[e] = (f < ge.na_frames) ? ge.fr_a[(int64_t)f * ACOSS_NBINS + c] : 0.0f;       // pass 2: A = query, unrotated
@@ -723,6 +734,7 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 uint8_t* orow = crp + pd.crp_off + (int64_t)(tk.row0 + myrow) * pd.pitch;
                 const int pitch = pd.pitch;
                 const uint32_t wamb = __float_as_uint(2.2f * E);
+                SB_T(sb1);
                 for (int t = 0; t < n_tiles; ++t, ++g) {
                     const uint32_t buf = g & 1;
                     SP_T0(tf);
@@ -770,6 +782,7 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                     __syncwarp();
                     if (lane == 0) mbar_arrive(mb_tempty + buf);
                 }
+                SB_T(sb2);
                 // columns past the last tile up to the pitch
                 const int done = n_tiles * GM_TN;
                 if (done < pitch) {
@@ -793,6 +806,17 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                             ++n_exact;
                             out[j] = (dv <= s_th[r] && dv <= thB[j]) ? (uint8_t)CRP_DELTA_ONE : (uint8_t)CRP_DELTA_ZERO;
                         }
+                    }
+                } else if (deferred) {
+                    // the strip's ambiguous cells go to the batch's list (crp_fix_kernel decides them after this pass): resolving
+                    // them here kept all 16 epilogue warps of the CTA off the next strip's tiles for ~10 000 clocks per strip
+                    // (clock64 probes: a fifth of the pass), for ~140 cells.  Warp 0 copies; the others meet it at the next
+                    // strip's first barrier.
+                    if (warp == 0 && na > 0) {
+                        unsigned long long base = 0;
+                        if (lane == 0) base = atomicAdd(amb_gcnt, (unsigned long long)na);
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        for (int e = lane; e < na; e += 32) amb_g[base + e] = make_int2(task, amb[e]);
                     }
                 } else {
                     // side A = query (rows staged in Araw in the oracle's order), side B = reference, rotated by boff
@@ -819,6 +843,14 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                             crp[pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch + j] = (uint8_t)CRP_DELTA_ONE;
                     }
                 }
+#ifdef SP_TIMING_BIN
+                if (tid == 0 && counters) {
+                    const long long sb3 = clock64();
+                    atomicAdd(&counters[2], (unsigned long long)(sb1 - sb0)); atomicAdd(&counters[3], (unsigned long long)(sb2 - sb1));
+                    atomicAdd(&counters[4], (unsigned long long)(sb3 - sb2)); atomicAdd(&counters[5], (unsigned long long)(sb3 - sb0));
+                    atomicAdd(&counters[6], (unsigned long long)na);
+                }
+#endif
             }
             task = nxt;
             ++i;
@@ -862,15 +894,56 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 }
 
 // =====================================================================================================================
+// K4b: the ambiguous cells of the binarise pass, one thread per cell: the exact 108-term chain in the oracle's op order against both
+// thresholds (the cell's CRP byte was written as "out" by the pass).
+// =====================================================================================================================
+__global__ void __launch_bounds__(256)
+crp_fix_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, const float* __restrict__ frames,
+               const float* __restrict__ selfdot, const float* __restrict__ thr, uint8_t* __restrict__ crp,
+               const int2* __restrict__ amb_g, const unsigned long long* __restrict__ amb_gcnt, unsigned long long* __restrict__ counters)
+{
+    const unsigned long long n = *amb_gcnt;
+    unsigned long long n_exact = 0;
+    for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (unsigned long long)gridDim.x * blockDim.x) {
+        const int2 ent = amb_g[e];
+        const StripTask tk = tasks[ent.x];
+        const PairDesc pd = descs[tk.pair];
+        const SpGeom ge = sp_geom(pd, 1, frames, selfdot);                  // side A = query (unrotated), side B = reference
+        const int r = (ent.y >> 24) & 0xFF, j = ent.y & 0xFFFFFF, row = tk.row0 + r;
+        const int boff = (ACOSS_NBINS - ge.rot) % ACOSS_NBINS;
+        const float4* ap = reinterpret_cast<const float4*>(ge.fr_a + (int64_t)row * ACOSS_NBINS);
+        const float4* bp = reinterpret_cast<const float4*>(ge.fr_b + (int64_t)j * ACOSS_NBINS);
+        float acc = 0.0f;
+#pragma unroll 3
+        for (int s_ = 0; s_ < 9; ++s_) {
+            const float4 a0 = __ldg(ap + 3 * s_), a1 = __ldg(ap + 3 * s_ + 1), a2 = __ldg(ap + 3 * s_ + 2);
+            const float4 b0 = __ldg(bp + 3 * s_), b1 = __ldg(bp + 3 * s_ + 1), b2 = __ldg(bp + 3 * s_ + 2);
+            const float av[12] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w};
+            const float bv[12] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+            acc = gm_chain12_rot(acc, av, bv, boff);
+        }
+        float item = xadd(xsub(__ldg(ge.sdA + row), xmul(2.0f, acc)), __ldg(ge.sdB + j));
+        if (item < 0.0f) item = 0.0f;
+        const float dv = __fsqrt_rn(item);
+        ++n_exact;
+        if (dv <= __ldg(thr + pd.thr_q_off + row) && dv <= __ldg(thr + pd.thr_r_off + j))
+            crp[pd.crp_off + (int64_t)row * pd.pitch + j] = (uint8_t)CRP_DELTA_ONE;
+    }
+    for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o);
+    if ((threadIdx.x & 31) == 0 && n_exact && counters) atomicAdd(&counters[0], n_exact);
+}
+
+// =====================================================================================================================
+#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 16 + 2 * GM_ROWS * 32 * 4 + 16 * SP_SEL_THREADS * 4)
+
+// =====================================================================================================================
 // K3: selection.  256 threads per strip, four CTAs per SM.
-//   (A) warp per row: the row's list (<= 512 entries, 16 per lane, one coalesced load per 32 slots) -> value bisection until
-//       the window around the wanted rank holds at most three elements -> candidates = everything within 2E of the window
+//   (A) a quad of lanes per row (one lane per sub-list): 64-bin histogram of the list over the bracket, refined by value interval
+//       until the bins of the wanted ranks hold at most 12 entries -> candidates = everything within 2E of that window
 //   (B) thread per candidate (all rows of the strip pooled): the exact 108-term chain in the oracle's op order
 //   (C) warp per row: exact order statistics among the candidates -> percentile -> threshold
 //   rows that could not be bracketed (bracket miss, list overflow, tiny side B): the whole row exactly
 // =====================================================================================================================
-#define SP_SEL_SMEM (GM_ARAW_BYTES + 5 * GM_ROWS * 4 + 16 + 2 * GM_ROWS * 32 * 4 + 16 * SP_SEL_THREADS * 4)
-
 __global__ void __launch_bounds__(SP_SEL_THREADS, 3)
 crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, int n_tasks,
                   const float* __restrict__ frames, const float* __restrict__ selfdot, const float* __restrict__ sdmax,
