@@ -810,13 +810,25 @@ crp_stream_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 } else if (deferred) {
                     // the strip's ambiguous cells go to the batch's list (crp_fix_kernel decides them after this pass): resolving
                     // them here kept all 16 epilogue warps of the CTA off the next strip's tiles for ~10 000 clocks per strip
-                    // (clock64 probes: a fifth of the pass), for ~140 cells.  Warp 0 copies; the others meet it at the next
-                    // strip's first barrier.
+                    // (clock64 probes: a fifth of the pass), for ~140 cells.  Warp 0 copies while the others go on to the next strip
+                    // (they meet at its first barrier).  A strip that finds the list full has warp 0 decide its cells here,
+                    // straight from global memory, and void the slots it drew.
                     if (warp == 0 && na > 0) {
                         unsigned long long base = 0;
                         if (lane == 0) base = atomicAdd(amb_gcnt, (unsigned long long)na);
                         base = __shfl_sync(0xffffffffu, base, 0);
-                        for (int e = lane; e < na; e += 32) amb_g[base + e] = make_int2(task, amb[e]);
+                        const unsigned long long cap = amb_gcnt[1];
+                        const bool ok = base + (unsigned long long)na <= cap;
+                        for (int e = lane; e < na; e += 32) {
+                            const int code = amb[e];
+                            if (base + e < cap) amb_g[base + e] = ok ? make_int2(task, code) : make_int2(-1, 0);
+                            if (!ok) {
+                                const int r = (code >> 24) & 0xFF, j = code & 0xFFFFFF;
+                                const float dv = exact_dist(frames, pd, rot, selfdot, tk.row0 + r, j);
+                                ++n_exact;
+                                if (dv <= s_th[r] && dv <= thB[j]) crp[pd.crp_off + (int64_t)(tk.row0 + r) * pd.pitch + j] = (uint8_t)CRP_DELTA_ONE;
+                            }
+                        }
                     }
                 } else {
                     // side A = query (rows staged in Araw in the oracle's order), side B = reference, rotated by boff
@@ -902,10 +914,11 @@ crp_fix_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__
                const float* __restrict__ selfdot, const float* __restrict__ thr, uint8_t* __restrict__ crp,
                const int2* __restrict__ amb_g, const unsigned long long* __restrict__ amb_gcnt, unsigned long long* __restrict__ counters)
 {
-    const unsigned long long n = *amb_gcnt;
+    const unsigned long long n = min(amb_gcnt[0], amb_gcnt[1]);            // fill count, capacity
     unsigned long long n_exact = 0;
     for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (unsigned long long)gridDim.x * blockDim.x) {
         const int2 ent = amb_g[e];
+        if (ent.x < 0) continue;                                            // voided by a strip that found the list full
         const StripTask tk = tasks[ent.x];
         const PairDesc pd = descs[tk.pair];
         const SpGeom ge = sp_geom(pd, 1, frames, selfdot);                  // side A = query (unrotated), side B = reference

@@ -153,6 +153,23 @@ def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
             assert np.array_equal(R, Ro), (mode, a, b)
 
 
+@pytest.mark.parametrize("cap", [0, 7, 100])
+def test_crp_split_ambiguous_list_full(ctx, oracle, cap, monkeypatch):
+    """phase-split pipeline: the batch's list of ambiguous cells (decided by crp_fix_kernel after the binarise pass) with room
+    for `cap` cells only -- the strips that find it full decide their cells inside the pass; same bits as the oracle"""
+    monkeypatch.setenv("ACOSS_AMB_CAP", str(cap))
+    rng = np.random.default_rng(77)
+    lens = [300, 523, 700, 260]
+    tracks = _tracks(rng, lens, noise=0.1)
+    ctx.upload_tracks(tracks)
+    prm = ctx.params(kappa=0.095, crp_mode=5)
+    for (a, b) in [(0, 1), (1, 2), (2, 3), (3, 0)]:
+        R, tq, tr, o = ctx.crp_pair(a, b, prm)
+        Ro, info = oracle.chroma_cross_similarity(tracks[a], tracks[b], kappa=0.095, full=True)
+        assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]), (cap, a, b)
+        assert np.array_equal(R, Ro), (cap, a, b)
+
+
 @pytest.mark.parametrize("mode", [4, 5])
 @pytest.mark.parametrize("kappa", [0.004, 0.02, 0.5, 0.93, 1.0, 0.0])
 def test_crp_gemm_extreme_percentiles(ctx, oracle, kappa, mode):
