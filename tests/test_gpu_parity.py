@@ -153,6 +153,28 @@ def test_crp_modes_bit_exact_medium(ctx, oracle, mode):
             assert np.array_equal(R, Ro), (mode, a, b)
 
 
+@pytest.mark.parametrize("opt", ["count_hh", "split_overlap"])
+def test_crp_split_experimental_options_bit_exact(oracle, opt):
+    """the phase-split pipeline's experimental switches (hi.hi-only count pass, selection on a second stream) change the schedule
+    and the width of the candidate band, never the bits"""
+    import acoss_b200
+    rng = np.random.default_rng(91)
+    lens = [300, 523, 700, 260]
+    tracks = _tracks(rng, lens, noise=0.1)
+    c = acoss_b200.Context(0)
+    try:
+        c.set_option(opt, 1)
+        c.upload_tracks(tracks)
+        prm = c.params(kappa=0.095, crp_mode=5)
+        for (a, b) in [(0, 1), (1, 2), (2, 3)]:
+            R, tq, tr, o = c.crp_pair(a, b, prm)
+            Ro, info = oracle.chroma_cross_similarity(tracks[a], tracks[b], kappa=0.095, full=True)
+            assert np.array_equal(tq, info["thr_q"]) and np.array_equal(tr, info["thr_r"]), (opt, a, b)
+            assert np.array_equal(R, Ro), (opt, a, b)
+    finally:
+        c.close()
+
+
 @pytest.mark.parametrize("cap", [0, 7, 100])
 def test_crp_split_ambiguous_list_full(ctx, oracle, cap, monkeypatch):
     """phase-split pipeline: the batch's list of ambiguous cells (decided by crp_fix_kernel after the binarise pass) with room
