@@ -909,6 +909,8 @@ __global__ void crp_edges_kernel(const PairDesc* __restrict__ descs, int64_t n_p
 // K4b: the ambiguous cells of the binarise pass, one thread per cell: the exact 108-term chain in the oracle's op order against both
 // thresholds (the cell's CRP byte was written as "out" by the pass).
 // =====================================================================================================================
+__global__ void sp_amb_init_kernel(unsigned long long* amb_gcnt, unsigned long long cap) { amb_gcnt[0] = 0ull; amb_gcnt[1] = cap; }
+
 __global__ void __launch_bounds__(256)
 crp_fix_kernel(const PairDesc* __restrict__ descs, const StripTask* __restrict__ tasks, const float* __restrict__ frames,
                const float* __restrict__ selfdot, const float* __restrict__ thr, uint8_t* __restrict__ crp,
