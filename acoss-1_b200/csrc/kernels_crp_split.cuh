@@ -992,13 +992,20 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
         float* thr_out = thr + (side_a_is_query ? pd.thr_q_off : pd.thr_r_off);
         const bool tiny = NB < GM_MIN_NB;
         __syncthreads();
-        for (int e = tid; e < (GM_ROWS + 8) * ACOSS_NBINS; e += SP_SEL_THREADS) {
+        // the strip's frames and self-dots are only needed by part (B): their loads are issued here and land in shared memory after
+        // part (A), whose walks hide the latency (they used to sit in front of a barrier: 6 % of the kernel's stall samples)
+        constexpr int SP_ARAW_PER_THREAD = ((GM_ROWS + 8) * ACOSS_NBINS + SP_SEL_THREADS - 1) / SP_SEL_THREADS;
+        float areg[SP_ARAW_PER_THREAD], xreg = 0.0f;
+#pragma unroll
+        for (int k = 0; k < SP_ARAW_PER_THREAD; ++k) {
+            const int e = tid + k * SP_SEL_THREADS;
             const int fe = e / ACOSS_NBINS, c = e - fe * ACOSS_NBINS;
             const int f = tk.row0 + fe;
-            Araw[e] = (f < g.na_frames) ? g.fr_a[(int64_t)f * ACOSS_NBINS + (side_a_is_query ? c : rot_src(c, rot))] : 0.0f;
+            areg[k] = (e < (GM_ROWS + 8) * ACOSS_NBINS && f < g.na_frames)
+                          ? g.fr_a[(int64_t)f * ACOSS_NBINS + (side_a_is_query ? c : rot_src(c, rot))] : 0.0f;
         }
         if (tid < GM_ROWS) {
-            s_xx[tid] = (tid < tk.nrows) ? g.sdA[tk.row0 + tid] : 0.0f;
+            xreg = (tid < tk.nrows) ? g.sdA[tk.row0 + tid] : 0.0f;
             s_nc[tid] = 0; s_kx[tid] = 0;
             s_flag[tid] = (tid < tk.nrows && tiny) ? 1 : 0;
         }
@@ -1180,6 +1187,12 @@ crp_select_kernel(const PairDesc* __restrict__ descs, const StripTask* __restric
                 }
             }
         }
+#pragma unroll
+        for (int k = 0; k < SP_ARAW_PER_THREAD; ++k) {
+            const int e = tid + k * SP_SEL_THREADS;
+            if (e < (GM_ROWS + 8) * ACOSS_NBINS) Araw[e] = areg[k];
+        }
+        if (tid < GM_ROWS) s_xx[tid] = xreg;
         __syncthreads();
         // offsets of the rows' candidates in the flat task list
         if (warp == 0) {
